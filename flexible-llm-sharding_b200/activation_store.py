@@ -1,0 +1,172 @@
+"""Activation store: where the packed token rows live between shards.
+
+Replaces `store_intermediate_activation` / `fetch_intermediate_activation` (reference
+utils.py:159-213).  The reference keeps one `(prefix, suffix)` pair per prompt in a dict and
+round-trips it through `.cpu()` / `.to(device)` / `np.save` once per prompt per shard.  Here the
+rows of all prompts form one `[total_rows, H]` fp16 matrix and a tier decides where it lives:
+
+  gpu   one HBM tensor; fetch/store are views (no copies).  With 180 GB per B200 this holds
+        e.g. 1024 x 2048-token prompts of Llama-2-70B (34 GB).
+  cpu   a pinned host tensor; each micro-batch is copied in on an H2D stream while the previous
+        one computes and copied back on a D2H stream (three rotating HBM staging buffers).
+  disk  per-prompt `.npy` files with the reference's names and shapes
+        (`prefix{rank}-{idx:05d}.npy` [1,len_p,H], `suffix…` [S,len_s,H]; utils.py:171-177).
+
+`storage_location` names the tier the user allows; unless `force_tier` is set the store upgrades
+`cpu`/`disk` to `gpu` when the matrix fits the HBM budget ("HBM-resident where capacity allows").
+The scored rows after `model.norm` (S per prompt) are small and always stay in HBM.
+"""
+from __future__ import annotations
+
+import os
+
+import numpy as np
+import torch
+
+
+class ActivationStore:
+    def __init__(self, location: str, packed, hidden: int, device: torch.device, compute_stream,
+                 disk_folder: str = "./temp", rank_tag: str = "", hbm_budget_bytes: int | None = None,
+                 force_tier: bool = False, max_rows: int = 0):
+        assert location in ("gpu", "cpu", "disk"), location
+        self.packed = packed
+        self.H = hidden
+        self.device = device
+        self.compute_stream = compute_stream
+        self.disk_folder = disk_folder
+        self.rank_tag = rank_tag
+        total_bytes = packed.total_rows * hidden * 2
+        tier = location
+        if tier != "gpu" and not force_tier:
+            if hbm_budget_bytes is None:
+                free, _ = torch.cuda.mem_get_info(device)
+                hbm_budget_bytes = int(free * 0.8)
+            if total_bytes <= hbm_budget_bytes:
+                tier = "gpu"
+        self.tier = tier
+        self.requested = location
+        self.h2d_bytes = 0
+        self.d2h_bytes = 0
+        self.heads = torch.empty((packed.total_head_rows, hidden), dtype=torch.float16, device=device)
+        if tier == "gpu":
+            self.x_all = torch.empty((packed.total_rows, hidden), dtype=torch.float16, device=device)
+        else:
+            cap = max(mb.n_rows for mb in packed.micro_batches)
+            self.staging = [torch.empty((cap, hidden), dtype=torch.float16, device=device) for _ in range(3)]
+            self.h2d_stream = torch.cuda.Stream(device)
+            self.d2h_stream = torch.cuda.Stream(device)
+            self.h2d_done = [None] * 3
+            self.d2h_done = [None] * 3
+            self.loaded = {}     # micro-batch index -> staging slot holding it
+            if tier == "cpu":
+                self.x_host = torch.empty((packed.total_rows, hidden), dtype=torch.float16).pin_memory()
+            else:
+                os.makedirs(disk_folder, exist_ok=True)
+                self.host_stage = torch.empty((cap, hidden), dtype=torch.float16).pin_memory()
+
+    # ------------------------------------------------------------------ token-stage rows
+    def _slot(self, i: int) -> int:
+        return i % 3
+
+    def prefetch(self, i: int, has_input: bool):
+        """Start bringing micro-batch i into HBM (no-op for the gpu tier)."""
+        if self.tier == "gpu" or i >= len(self.packed.micro_batches) or i in self.loaded:
+            return
+        mb = self.packed.micro_batches[i]
+        s = self._slot(i)
+        buf = self.staging[s][:mb.n_rows]
+        if has_input:
+            with torch.cuda.stream(self.h2d_stream):
+                if self.d2h_done[s] is not None:           # previous tenant fully written back
+                    self.h2d_stream.wait_event(self.d2h_done[s])
+                if self.tier == "cpu":
+                    buf.copy_(self.x_host[mb.row_lo:mb.row_lo + mb.n_rows], non_blocking=True)
+                else:
+                    self._disk_load(mb, buf)
+                ev = torch.cuda.Event()
+                ev.record(self.h2d_stream)
+                self.h2d_done[s] = ev
+            self.h2d_bytes += mb.n_rows * self.H * 2
+        else:
+            if self.d2h_done[s] is not None:
+                self.compute_stream.wait_event(self.d2h_done[s])
+            self.h2d_done[s] = None
+        self.loaded[i] = s
+
+    def fetch(self, i: int, has_input: bool) -> torch.Tensor:
+        """Device tensor [n_rows, H] holding micro-batch i's rows (uninitialised if not has_input)."""
+        mb = self.packed.micro_batches[i]
+        if self.tier == "gpu":
+            return self.x_all[mb.row_lo:mb.row_lo + mb.n_rows]
+        self.prefetch(i, has_input)
+        s = self.loaded[i]
+        if self.h2d_done[s] is not None:
+            self.compute_stream.wait_event(self.h2d_done[s])
+        return self.staging[s][:mb.n_rows]
+
+    def store(self, i: int, x: torch.Tensor, keep_tokens: bool):
+        """Persist micro-batch i after a shard (`keep_tokens` False once model.norm has run)."""
+        if self.tier == "gpu":
+            return
+        s = self.loaded.pop(i)
+        mb = self.packed.micro_batches[i]
+        ev = torch.cuda.Event()
+        ev.record(self.compute_stream)
+        with torch.cuda.stream(self.d2h_stream):
+            self.d2h_stream.wait_event(ev)
+            if keep_tokens:
+                if self.tier == "cpu":
+                    self.x_host[mb.row_lo:mb.row_lo + mb.n_rows].copy_(x, non_blocking=True)
+                else:
+                    self._disk_save(mb, x)
+                self.d2h_bytes += mb.n_rows * self.H * 2
+            done = torch.cuda.Event()
+            done.record(self.d2h_stream)
+            self.d2h_done[s] = done
+
+    def end_shard(self):
+        if self.tier != "gpu":
+            self.loaded.clear()
+
+    # ------------------------------------------------------------------ scored rows
+    def heads_view(self, i: int) -> torch.Tensor:
+        mb = self.packed.micro_batches[i]
+        return self.heads[mb.head_lo:mb.head_lo + mb.n_head]
+
+    # ------------------------------------------------------------------ disk tier
+    def _names(self, prompt_idx: int):
+        f = self.disk_folder
+        return (f"{f}/prefix{self.rank_tag}-{prompt_idx:05d}.npy", f"{f}/suffix{self.rank_tag}-{prompt_idx:05d}.npy")
+
+    def _disk_save(self, mb, x: torch.Tensor):
+        host = self.host_stage[:mb.n_rows]
+        host.copy_(x, non_blocking=True)
+        self.d2h_stream.synchronize()
+        arr = host.numpy()
+        for p in range(mb.prompt_lo, mb.prompt_hi):
+            len_p, S, len_s = self.packed.shapes[p]
+            b = int(self.packed.prompt_row[p]) - mb.row_lo
+            pf, sf = self._names(p)
+            np.save(pf, arr[b:b + len_p].reshape(1, len_p, self.H))
+            np.save(sf, arr[b + len_p:b + len_p + S * len_s].reshape(S, len_s, self.H))
+
+    def _disk_load(self, mb, buf: torch.Tensor):
+        host = self.host_stage[:mb.n_rows]
+        self.h2d_stream.synchronize()
+        self.d2h_stream.synchronize()
+        arr = host.numpy()
+        for p in range(mb.prompt_lo, mb.prompt_hi):
+            len_p, S, len_s = self.packed.shapes[p]
+            b = int(self.packed.prompt_row[p]) - mb.row_lo
+            pf, sf = self._names(p)
+            arr[b:b + len_p] = np.load(pf).reshape(len_p, self.H)
+            arr[b + len_p:b + len_p + S * len_s] = np.load(sf).reshape(S * len_s, self.H)
+        buf.copy_(host, non_blocking=True)
+        self.h2d_stream.synchronize()
+
+    def cleanup(self):
+        if self.tier == "disk":
+            for p in range(len(self.packed.shapes)):
+                for fn in self._names(p):
+                    if os.path.exists(fn):
+                        os.remove(fn)

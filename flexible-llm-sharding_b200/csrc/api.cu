@@ -1,0 +1,623 @@
+// C-ABI entry points (include/fls_b200.h): context, weight slots + copy stream, layer orchestration.
+#include <cstdarg>
+#include <cstring>
+#include <memory>
+#include <string>
+#include <vector>
+
+#include "../../include/fls_b200.h"
+#include "common.cuh"
+#include "host_cache.h"
+
+namespace fls {
+
+char* tls_error_buffer() {
+    static thread_local char buf[512];
+    return buf;
+}
+int fail(int code, const char* fmt, ...) {
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(tls_error_buffer(), 512, fmt, ap);
+    va_end(ap);
+    return code;
+}
+
+namespace {
+
+struct DecoderView {
+    const __half *wqkv, *wo, *wgu, *wd, *ln1, *ln2;
+};
+struct LayerReg {
+    int kind = -1;
+    std::string path;
+    std::shared_ptr<HostLayerImage> img;  // loaded lazily
+    std::vector<TensorEntry> header;      // parsed at registration (shapes validated)
+    size_t slot_bytes = 0;
+};
+struct ResidentLayer {
+    int layer_idx = -1;
+    int kind = -1;
+    DecoderView dec{};
+    const __half* single = nullptr;  // embed table / norm gain / lm_head weight
+};
+struct Slot {
+    char* dev = nullptr;
+    size_t cap = 0;
+    cudaEvent_t ready = nullptr, freed = nullptr, copy_begin = nullptr, copy_end = nullptr;
+    bool in_use = false;       // copies enqueued, not yet released
+    bool freed_valid = false;  // `freed` has been recorded at least once since the last prefetch
+    bool timing_pending = false;
+    size_t pending_bytes = 0;
+    std::vector<ResidentLayer> layers;
+    std::vector<std::shared_ptr<HostLayerImage>> pins;  // keep host images alive while copies fly
+};
+
+}  // namespace
+}  // namespace fls
+
+using namespace fls;
+
+struct fls_ctx {
+    int device = 0;
+    int num_sms = 148;
+    fls_model_desc m{};
+    int q_dim = 0, kv_dim = 0, qkv_dim = 0;
+    std::vector<LayerReg> layers;
+    std::vector<Slot> slots;
+    cudaStream_t copy_stream = nullptr;
+    // workspace
+    int max_rows = 0, max_head_rows = 0;
+    __half *xn = nullptr, *qkv = nullptr, *attn = nullptr, *hmid = nullptr;
+    float2* lse_partial = nullptr;
+    float* lse = nullptr;
+    __half *rope_cos = nullptr, *rope_sin = nullptr;
+    int rope_n_pos = 0;
+    size_t workspace_bytes = 0;
+    fls_stats stats{};
+    char err[512] = {0};
+    bool cuda_poisoned = false;
+};
+
+namespace {
+
+int ctx_fail(fls_ctx* c, int code) {
+    if (c) {
+        strncpy(c->err, tls_error_buffer(), sizeof(c->err) - 1);
+        if (code == kErrCuda) c->cuda_poisoned = true;
+    }
+    return code;
+}
+#define CTX_TRY(c, expr)                      \
+    do {                                      \
+        int _s = (expr);                      \
+        if (_s != 0) return ctx_fail((c), _s); \
+    } while (0)
+#define CTX_CUDA(c, expr)                                                                                  \
+    do {                                                                                                   \
+        cudaError_t _e = (expr);                                                                           \
+        if (_e != cudaSuccess)                                                                             \
+            return ctx_fail((c), fail(kErrCuda, "%s failed: %s (%s:%d)", #expr, cudaGetErrorString(_e), __FILE__, \
+                                      __LINE__));                                                          \
+    } while (0)
+
+int enter(fls_ctx* c) {
+    if (!c) return fail(kErrInvalid, "null context");
+    if (c->cuda_poisoned) return fail(kErrCuda, "context is unusable after an earlier CUDA error: %s", c->err);
+    cudaError_t e = cudaSetDevice(c->device);
+    if (e != cudaSuccess) return fail(kErrCuda, "cudaSetDevice(%d): %s", c->device, cudaGetErrorString(e));
+    return kOk;
+}
+#define ENTER(c)                                 \
+    do {                                         \
+        int _s = enter(c);                       \
+        if (_s != 0) return ctx_fail((c), _s);   \
+    } while (0)
+
+inline size_t align256(size_t v) { return (v + 255) & ~size_t(255); }
+
+int expect_shape(const LayerReg& L, const char* suffix, long long d0, long long d1, size_t* bytes) {
+    for (auto& t : L.header) {
+        const size_t n = strlen(suffix);
+        if (t.name.size() >= n && t.name.compare(t.name.size() - n, n, suffix) == 0) {
+            const bool ok = d1 < 0 ? (t.shape.size() == 1 && t.shape[0] == d0)
+                                   : (t.shape.size() == 2 && t.shape[0] == d0 && t.shape[1] == d1);
+            if (!ok) return fail(kErrInvalid, "%s: tensor %s has an unexpected shape", L.path.c_str(), t.name.c_str());
+            *bytes += align256(t.numel * 2);
+            return kOk;
+        }
+    }
+    return fail(kErrIo, "%s: tensor *%s is missing", L.path.c_str(), suffix);
+}
+
+void free_workspace(fls_ctx* c) {
+    for (auto& s : c->slots) {
+        if (s.dev) cudaFree(s.dev);
+        if (s.ready) cudaEventDestroy(s.ready);
+        if (s.freed) cudaEventDestroy(s.freed);
+        if (s.copy_begin) cudaEventDestroy(s.copy_begin);
+        if (s.copy_end) cudaEventDestroy(s.copy_end);
+    }
+    c->slots.clear();
+    for (void* p : {static_cast<void*>(c->xn), static_cast<void*>(c->qkv), static_cast<void*>(c->attn),
+                    static_cast<void*>(c->hmid), static_cast<void*>(c->lse_partial), static_cast<void*>(c->lse)})
+        if (p) cudaFree(p);
+    c->xn = c->qkv = c->attn = c->hmid = nullptr;
+    c->lse_partial = nullptr;
+    c->lse = nullptr;
+    c->workspace_bytes = 0;
+}
+
+void harvest_copy_timing(fls_ctx* c, Slot& s) {
+    if (!s.timing_pending) return;
+    if (cudaEventQuery(s.copy_end) == cudaSuccess) {
+        float ms = 0.f;
+        if (cudaEventElapsedTime(&ms, s.copy_begin, s.copy_end) == cudaSuccess) {
+            c->stats.h2d_ms += ms;
+            c->stats.h2d_bytes += s.pending_bytes;
+        }
+        s.timing_pending = false;
+    } else {
+        cudaGetLastError();
+    }
+}
+
+const ResidentLayer* find_resident(fls_ctx* c, int slot, int layer_idx, int kind) {
+    if (slot < 0 || slot >= static_cast<int>(c->slots.size())) {
+        fail(kErrInvalid, "slot %d out of range", slot);
+        return nullptr;
+    }
+    for (auto& r : c->slots[slot].layers)
+        if (r.layer_idx == layer_idx) {
+            if (r.kind != kind) {
+                fail(kErrState, "layer %d is of kind %d, not %d", layer_idx, r.kind, kind);
+                return nullptr;
+            }
+            return &r;
+        }
+    fail(kErrState, "layer %d is not resident in slot %d (prefetch it first)", layer_idx, slot);
+    return nullptr;
+}
+
+inline cudaStream_t as_stream(void* s) { return reinterpret_cast<cudaStream_t>(s); }
+inline const __half* H(const uint16_t* p) { return reinterpret_cast<const __half*>(p); }
+inline __half* H(uint16_t* p) { return reinterpret_cast<__half*>(p); }
+
+int head_impl(fls_ctx* c, const __half* x, const __half* W, int n_rows, int V, int K, __half* probs,
+              const int32_t* answer_ids, int n_ids, float* logprob, float* lse_out, cudaStream_t st) {
+    if (n_rows > c->max_head_rows)
+        return fail(kErrCapacity, "lm_head: %d rows exceed the configured max_head_rows %d", n_rows, c->max_head_rows);
+    if (gemm_lse_blocks(V) > gemm_lse_blocks(c->m.vocab_size))
+        return fail(kErrCapacity, "lm_head: vocab %d exceeds the configured %d", V, c->m.vocab_size);
+    GemmArgs a{};
+    a.A = x, a.lda = K, a.B = W, a.ldb = K, a.b_rows = V, a.M = n_rows, a.N = V, a.K = K;
+    a.partial = c->lse_partial;
+    FLS_TRY(gemm_launch(kEpiLsePartial, a, c->num_sms, st));
+    FLS_TRY(lse_reduce_launch(c->lse_partial, n_rows, gemm_lse_blocks(V), c->lse, st));
+    c->stats.kernel_launches += 2;
+    if (probs) {
+        a.C = probs, a.ldc = V, a.lse = c->lse;
+        FLS_TRY(gemm_launch(kEpiProbs, a, c->num_sms, st));
+        c->stats.kernel_launches += 1;
+    }
+    if (logprob && n_ids > 0) {
+        FLS_TRY(gather_logprob_launch(x, K, W, K, K, answer_ids, n_ids, c->lse, n_rows, logprob, st));
+        c->stats.kernel_launches += 1;
+    }
+    if (lse_out) FLS_CUDA(cudaMemcpyAsync(lse_out, c->lse, sizeof(float) * n_rows, cudaMemcpyDeviceToDevice, st));
+    return kOk;
+}
+
+}  // namespace
+
+// =============================================================================================
+extern "C" {
+
+int fls_version(void) { return 1; }
+
+const char* fls_last_error(const fls_ctx* ctx) { return ctx ? ctx->err : tls_error_buffer(); }
+
+int fls_create(const fls_model_desc* d, int device, fls_ctx** out) {
+    if (!d || !out) return fail(kErrInvalid, "fls_create: null argument");
+    if (d->hidden_size <= 0 || d->hidden_size % 8 || d->intermediate_size % 8 || d->vocab_size % 8 ||
+        d->num_attention_heads <= 0 || d->num_key_value_heads <= 0 ||
+        d->num_attention_heads % d->num_key_value_heads || (d->head_dim != 64 && d->head_dim != 128))
+        return fail(kErrInvalid, "fls_create: unsupported model shape (hidden %d, inter %d, vocab %d, heads %d/%d, "
+                    "head_dim %d)", d->hidden_size, d->intermediate_size, d->vocab_size, d->num_attention_heads,
+                    d->num_key_value_heads, d->head_dim);
+    FLS_CUDA(cudaSetDevice(device));
+    cudaDeviceProp prop;
+    FLS_CUDA(cudaGetDeviceProperties(&prop, device));
+    if (prop.major != 10)
+        return fail(kErrCuda, "device %d is sm_%d%d; this library contains sm_100a code only", device, prop.major,
+                    prop.minor);
+    FLS_TRY(gemm_init());
+    FLS_TRY(attention_init());
+    auto c = new fls_ctx();
+    c->device = device;
+    c->num_sms = prop.multiProcessorCount;
+    c->m = *d;
+    c->q_dim = d->num_attention_heads * d->head_dim;
+    c->kv_dim = d->num_key_value_heads * d->head_dim;
+    c->qkv_dim = c->q_dim + 2 * c->kv_dim;
+    c->layers.resize(d->num_hidden_layers + 3);
+    cudaError_t e = cudaStreamCreateWithFlags(&c->copy_stream, cudaStreamNonBlocking);
+    if (e != cudaSuccess) {
+        delete c;
+        return fail(kErrCuda, "cudaStreamCreate: %s", cudaGetErrorString(e));
+    }
+    *out = c;
+    return kOk;
+}
+
+int fls_destroy(fls_ctx* c) {
+    if (!c) return kOk;
+    cudaSetDevice(c->device);
+    cudaDeviceSynchronize();
+    free_workspace(c);
+    if (c->rope_cos) cudaFree(c->rope_cos);
+    if (c->rope_sin) cudaFree(c->rope_sin);
+    if (c->copy_stream) cudaStreamDestroy(c->copy_stream);
+    delete c;
+    return kOk;
+}
+
+int fls_configure(fls_ctx* c, int n_slots, size_t slot_bytes, int max_rows, int max_head_rows) {
+    ENTER(c);
+    if (n_slots < 1 || n_slots > 8 || max_rows < 1 || max_head_rows < 1)
+        return ctx_fail(c, fail(kErrInvalid, "fls_configure: n_slots %d, max_rows %d, max_head_rows %d", n_slots,
+                                max_rows, max_head_rows));
+    CTX_CUDA(c, cudaDeviceSynchronize());
+    free_workspace(c);
+    c->slots.resize(n_slots);
+    size_t total = 0;
+    for (auto& s : c->slots) {
+        s.cap = align256(slot_bytes);
+        CTX_CUDA(c, cudaMalloc(reinterpret_cast<void**>(&s.dev), std::max<size_t>(s.cap, 256)));
+        CTX_CUDA(c, cudaEventCreateWithFlags(&s.ready, cudaEventDisableTiming));
+        CTX_CUDA(c, cudaEventCreateWithFlags(&s.freed, cudaEventDisableTiming));
+        CTX_CUDA(c, cudaEventCreate(&s.copy_begin));
+        CTX_CUDA(c, cudaEventCreate(&s.copy_end));
+        total += s.cap;
+    }
+    const size_t R = static_cast<size_t>(max_rows);
+    const size_t b_xn = R * c->m.hidden_size * 2, b_qkv = R * c->qkv_dim * 2, b_attn = R * c->q_dim * 2,
+                 b_h = R * c->m.intermediate_size * 2;
+    const size_t b_part = static_cast<size_t>(max_head_rows) * gemm_lse_blocks(c->m.vocab_size) * sizeof(float2);
+    CTX_CUDA(c, cudaMalloc(reinterpret_cast<void**>(&c->xn), b_xn));
+    CTX_CUDA(c, cudaMalloc(reinterpret_cast<void**>(&c->qkv), b_qkv));
+    CTX_CUDA(c, cudaMalloc(reinterpret_cast<void**>(&c->attn), b_attn));
+    CTX_CUDA(c, cudaMalloc(reinterpret_cast<void**>(&c->hmid), b_h));
+    CTX_CUDA(c, cudaMalloc(reinterpret_cast<void**>(&c->lse_partial), b_part));
+    CTX_CUDA(c, cudaMalloc(reinterpret_cast<void**>(&c->lse), sizeof(float) * max_head_rows));
+    c->max_rows = max_rows;
+    c->max_head_rows = max_head_rows;
+    c->workspace_bytes = total + b_xn + b_qkv + b_attn + b_h + b_part + sizeof(float) * max_head_rows;
+    return kOk;
+}
+
+int fls_set_rope_table(fls_ctx* c, const uint16_t* cos_host, const uint16_t* sin_host, int n_pos) {
+    ENTER(c);
+    if (!cos_host || !sin_host || n_pos < 1) return ctx_fail(c, fail(kErrInvalid, "fls_set_rope_table: bad argument"));
+    const size_t bytes = static_cast<size_t>(n_pos) * c->m.head_dim * 2;
+    CTX_CUDA(c, cudaDeviceSynchronize());
+    if (c->rope_cos) cudaFree(c->rope_cos);
+    if (c->rope_sin) cudaFree(c->rope_sin);
+    c->rope_cos = c->rope_sin = nullptr;
+    CTX_CUDA(c, cudaMalloc(reinterpret_cast<void**>(&c->rope_cos), bytes));
+    CTX_CUDA(c, cudaMalloc(reinterpret_cast<void**>(&c->rope_sin), bytes));
+    CTX_CUDA(c, cudaMemcpy(c->rope_cos, cos_host, bytes, cudaMemcpyHostToDevice));
+    CTX_CUDA(c, cudaMemcpy(c->rope_sin, sin_host, bytes, cudaMemcpyHostToDevice));
+    c->rope_n_pos = n_pos;
+    return kOk;
+}
+
+// --------------------------------------------------------------------------------- weight stream
+int fls_register_layer_file(fls_ctx* c, int layer_idx, int kind, const char* path, int load_now) {
+    ENTER(c);
+    if (layer_idx < 0 || layer_idx >= static_cast<int>(c->layers.size()) || !path || kind < 0 || kind > 3)
+        return ctx_fail(c, fail(kErrInvalid, "fls_register_layer_file: layer %d kind %d", layer_idx, kind));
+    LayerReg L;
+    L.kind = kind;
+    L.path = path;
+    size_t ds = 0, fs = 0;
+    CTX_TRY(c, parse_safetensors_header(L.path, &L.header, &ds, &fs));
+    for (auto& t : L.header)
+        if (t.dtype != "F16" && t.dtype != "BF16" && t.dtype != "F32")
+            return ctx_fail(c, fail(kErrInvalid, "%s: tensor %s has dtype %s; int8/quantised weights are not supported",
+                                    path, t.name.c_str(), t.dtype.c_str()));
+    const auto& m = c->m;
+    size_t bytes = 0;
+    if (kind == FLS_LAYER_EMBED) {
+        CTX_TRY(c, expect_shape(L, "embed_tokens.weight", m.vocab_size, m.hidden_size, &bytes));
+    } else if (kind == FLS_LAYER_NORM) {
+        CTX_TRY(c, expect_shape(L, "norm.weight", m.hidden_size, -1, &bytes));
+    } else if (kind == FLS_LAYER_HEAD) {
+        CTX_TRY(c, expect_shape(L, "lm_head.weight", m.vocab_size, m.hidden_size, &bytes));
+    } else {
+        CTX_TRY(c, expect_shape(L, "self_attn.q_proj.weight", c->q_dim, m.hidden_size, &bytes));
+        CTX_TRY(c, expect_shape(L, "self_attn.k_proj.weight", c->kv_dim, m.hidden_size, &bytes));
+        CTX_TRY(c, expect_shape(L, "self_attn.v_proj.weight", c->kv_dim, m.hidden_size, &bytes));
+        CTX_TRY(c, expect_shape(L, "self_attn.o_proj.weight", m.hidden_size, c->q_dim, &bytes));
+        CTX_TRY(c, expect_shape(L, "mlp.gate_proj.weight", m.intermediate_size, m.hidden_size, &bytes));
+        CTX_TRY(c, expect_shape(L, "mlp.up_proj.weight", m.intermediate_size, m.hidden_size, &bytes));
+        CTX_TRY(c, expect_shape(L, "mlp.down_proj.weight", m.hidden_size, m.intermediate_size, &bytes));
+        CTX_TRY(c, expect_shape(L, ".input_layernorm.weight", m.hidden_size, -1, &bytes));
+        CTX_TRY(c, expect_shape(L, "post_attention_layernorm.weight", m.hidden_size, -1, &bytes));
+    }
+    L.slot_bytes = bytes;
+    if (load_now) CTX_TRY(c, acquire_host_image(L.path, &L.img));
+    c->layers[layer_idx] = std::move(L);
+    return kOk;
+}
+
+int fls_layer_slot_bytes(fls_ctx* c, int layer_idx, size_t* out) {
+    if (!c || !out || layer_idx < 0 || layer_idx >= static_cast<int>(c->layers.size()) || c->layers[layer_idx].kind < 0)
+        return ctx_fail(c, fail(kErrInvalid, "fls_layer_slot_bytes: layer %d is not registered", layer_idx));
+    *out = c->layers[layer_idx].slot_bytes;
+    return kOk;
+}
+
+int fls_prefetch_shard(fls_ctx* c, int slot, const int32_t* layer_ids, int n) {
+    ENTER(c);
+    if (slot < 0 || slot >= static_cast<int>(c->slots.size()) || n < 0 || (n > 0 && !layer_ids))
+        return ctx_fail(c, fail(kErrInvalid, "fls_prefetch_shard: slot %d, n %d", slot, n));
+    Slot& s = c->slots[slot];
+    if (s.in_use) return ctx_fail(c, fail(kErrState, "slot %d is still in use: release it before prefetching", slot));
+    harvest_copy_timing(c, s);
+    size_t need = 0;
+    for (int i = 0; i < n; ++i) {
+        const int li = layer_ids[i];
+        if (li < 0 || li >= static_cast<int>(c->layers.size()) || c->layers[li].kind < 0)
+            return ctx_fail(c, fail(kErrInvalid, "fls_prefetch_shard: layer %d is not registered", li));
+        need += c->layers[li].slot_bytes;
+    }
+    if (need > s.cap)
+        return ctx_fail(c, fail(kErrCapacity, "shard needs %zu bytes but slots hold %zu", need, s.cap));
+    // host images first (may read files), so the copy stream is not stalled half-way through a shard
+    for (int i = 0; i < n; ++i) {
+        LayerReg& L = c->layers[layer_ids[i]];
+        if (!L.img) CTX_TRY(c, acquire_host_image(L.path, &L.img));
+    }
+    if (s.freed_valid) CTX_CUDA(c, cudaStreamWaitEvent(c->copy_stream, s.freed, 0));
+    s.layers.clear();
+    s.pins.clear();
+    CTX_CUDA(c, cudaEventRecord(s.copy_begin, c->copy_stream));
+    size_t off = 0;
+    auto put = [&](const HostLayerImage& img, const char* suffix, const __half** dst) -> int {
+        const TensorEntry* t = img.find(suffix);
+        if (!t) return fail(kErrIo, "%s: tensor *%s is missing", img.path.c_str(), suffix);
+        FLS_CUDA(cudaMemcpyAsync(s.dev + off, img.pinned + t->host_off, t->numel * 2, cudaMemcpyHostToDevice,
+                                 c->copy_stream));
+        *dst = reinterpret_cast<const __half*>(s.dev + off);
+        off += align256(t->numel * 2);
+        return kOk;
+    };
+    for (int i = 0; i < n; ++i) {
+        LayerReg& L = c->layers[layer_ids[i]];
+        ResidentLayer r;
+        r.layer_idx = layer_ids[i];
+        r.kind = L.kind;
+        const __half* tmp = nullptr;
+        if (L.kind == FLS_LAYER_DECODER) {
+            // q, k, v rows adjacent -> one [q_dim + 2 kv_dim, H] operand; gate, up adjacent -> [2I, H]
+            CTX_TRY(c, put(*L.img, "self_attn.q_proj.weight", &r.dec.wqkv));
+            CTX_TRY(c, put(*L.img, "self_attn.k_proj.weight", &tmp));
+            CTX_TRY(c, put(*L.img, "self_attn.v_proj.weight", &tmp));
+            CTX_TRY(c, put(*L.img, "self_attn.o_proj.weight", &r.dec.wo));
+            CTX_TRY(c, put(*L.img, "mlp.gate_proj.weight", &r.dec.wgu));
+            CTX_TRY(c, put(*L.img, "mlp.up_proj.weight", &tmp));
+            CTX_TRY(c, put(*L.img, "mlp.down_proj.weight", &r.dec.wd));
+            CTX_TRY(c, put(*L.img, ".input_layernorm.weight", &r.dec.ln1));
+            CTX_TRY(c, put(*L.img, "post_attention_layernorm.weight", &r.dec.ln2));
+        } else {
+            const char* suffix = L.kind == FLS_LAYER_EMBED ? "embed_tokens.weight"
+                                 : L.kind == FLS_LAYER_NORM ? "norm.weight" : "lm_head.weight";
+            CTX_TRY(c, put(*L.img, suffix, &r.single));
+        }
+        s.layers.push_back(r);
+        s.pins.push_back(L.img);
+    }
+    CTX_CUDA(c, cudaEventRecord(s.copy_end, c->copy_stream));
+    CTX_CUDA(c, cudaEventRecord(s.ready, c->copy_stream));
+    s.in_use = true;
+    s.freed_valid = false;
+    s.timing_pending = true;
+    s.pending_bytes = off;
+    return kOk;
+}
+
+int fls_acquire_shard(fls_ctx* c, int slot, void* stream) {
+    ENTER(c);
+    if (slot < 0 || slot >= static_cast<int>(c->slots.size()) || !c->slots[slot].in_use)
+        return ctx_fail(c, fail(kErrState, "fls_acquire_shard: slot %d has no prefetched shard", slot));
+    CTX_CUDA(c, cudaStreamWaitEvent(as_stream(stream), c->slots[slot].ready, 0));
+    return kOk;
+}
+
+int fls_release_shard(fls_ctx* c, int slot, void* stream) {
+    ENTER(c);
+    if (slot < 0 || slot >= static_cast<int>(c->slots.size()) || !c->slots[slot].in_use)
+        return ctx_fail(c, fail(kErrState, "fls_release_shard: slot %d is not in use", slot));
+    Slot& s = c->slots[slot];
+    CTX_CUDA(c, cudaEventRecord(s.freed, as_stream(stream)));
+    s.freed_valid = true;
+    s.in_use = false;
+    harvest_copy_timing(c, s);
+    return kOk;
+}
+
+int fls_preload_layer_file(const char* path) {
+    if (!path) return fail(kErrInvalid, "fls_preload_layer_file: null path");
+    std::shared_ptr<HostLayerImage> img;
+    return acquire_host_image(path, &img);
+}
+
+int fls_trim_host_cache(size_t keep_bytes) {
+    trim_host_cache(keep_bytes);
+    return kOk;
+}
+
+// --------------------------------------------------------------------------------- layer compute
+int fls_embed(fls_ctx* c, int slot, int layer_idx, const int32_t* ids, int n_rows, uint16_t* out, void* stream) {
+    ENTER(c);
+    const ResidentLayer* r = find_resident(c, slot, layer_idx, FLS_LAYER_EMBED);
+    if (!r) return ctx_fail(c, kErrState);
+    CTX_TRY(c, embed_launch(r->single, ids, n_rows, c->m.hidden_size, H(out), as_stream(stream)));
+    c->stats.kernel_launches += 1;
+    return kOk;
+}
+
+int fls_decoder_layer(fls_ctx* c, int slot, int layer_idx, uint16_t* x_dev, int n_rows, const int32_t* row_pos,
+                      const fls_attn_tile* tiles, int n_tiles, void* stream) {
+    ENTER(c);
+    const ResidentLayer* r = find_resident(c, slot, layer_idx, FLS_LAYER_DECODER);
+    if (!r) return ctx_fail(c, kErrState);
+    if (n_rows > c->max_rows)
+        return ctx_fail(c, fail(kErrCapacity, "decoder_layer: %d rows exceed the configured max_rows %d", n_rows,
+                                c->max_rows));
+    if (!c->rope_cos) return ctx_fail(c, fail(kErrState, "decoder_layer: call fls_set_rope_table first"));
+    if (n_rows <= 0) return kOk;
+    const auto& m = c->m;
+    const int Hd = m.hidden_size, I = m.intermediate_size;
+    cudaStream_t st = as_stream(stream);
+    __half* x = H(x_dev);
+    static_assert(sizeof(fls_attn_tile) == sizeof(AttnTile), "tile layouts must match");
+
+    // hidden = x + o_proj(attn(rope(qkv(norm(x)))))
+    CTX_TRY(c, rmsnorm_launch(x, nullptr, nullptr, r->dec.ln1, m.rms_norm_eps, n_rows, Hd, nullptr, c->xn, st));
+    GemmArgs a{};
+    a.A = c->xn, a.lda = Hd, a.B = r->dec.wqkv, a.ldb = Hd, a.b_rows = c->qkv_dim;
+    a.M = n_rows, a.N = c->qkv_dim, a.K = Hd, a.C = c->qkv, a.ldc = c->qkv_dim;
+    CTX_TRY(c, gemm_launch(kEpiStore, a, c->num_sms, st));
+    CTX_TRY(c, rope_launch(c->qkv, c->qkv_dim, n_rows, m.num_attention_heads, m.num_key_value_heads, m.head_dim,
+                           row_pos, c->rope_cos, c->rope_sin, c->rope_n_pos, st));
+    CTX_TRY(c, attention_launch(c->qkv, c->qkv_dim, m.num_attention_heads, m.num_key_value_heads, m.head_dim,
+                                reinterpret_cast<const AttnTile*>(tiles), n_tiles, c->attn, c->q_dim, st));
+    a = GemmArgs{};
+    a.A = c->attn, a.lda = c->q_dim, a.B = r->dec.wo, a.ldb = c->q_dim, a.b_rows = Hd;
+    a.M = n_rows, a.N = Hd, a.K = c->q_dim, a.C = x, a.ldc = Hd, a.R = x, a.ldr = Hd;
+    CTX_TRY(c, gemm_launch(kEpiResidual, a, c->num_sms, st));
+
+    // hidden = hidden + down_proj(silu(gate_proj(norm(hidden))) * up_proj(norm(hidden)))
+    CTX_TRY(c, rmsnorm_launch(x, nullptr, nullptr, r->dec.ln2, m.rms_norm_eps, n_rows, Hd, nullptr, c->xn, st));
+    a = GemmArgs{};
+    a.A = c->xn, a.lda = Hd, a.B = r->dec.wgu, a.ldb = Hd, a.b_rows = 2 * I;
+    a.M = n_rows, a.N = I, a.K = Hd, a.C = c->hmid, a.ldc = I, a.up_off = I;
+    CTX_TRY(c, gemm_launch(kEpiSwiGLU, a, c->num_sms, st));
+    a = GemmArgs{};
+    a.A = c->hmid, a.lda = I, a.B = r->dec.wd, a.ldb = I, a.b_rows = Hd;
+    a.M = n_rows, a.N = Hd, a.K = I, a.C = x, a.ldc = Hd, a.R = x, a.ldr = Hd;
+    CTX_TRY(c, gemm_launch(kEpiResidual, a, c->num_sms, st));
+    c->stats.kernel_launches += 8;
+    return kOk;
+}
+
+int fls_final_norm(fls_ctx* c, int slot, int layer_idx, const uint16_t* x, const int32_t* gather, int n_out,
+                   uint16_t* out, void* stream) {
+    ENTER(c);
+    const ResidentLayer* r = find_resident(c, slot, layer_idx, FLS_LAYER_NORM);
+    if (!r) return ctx_fail(c, kErrState);
+    CTX_TRY(c, rmsnorm_launch(H(x), nullptr, gather, r->single, c->m.rms_norm_eps, n_out, c->m.hidden_size, nullptr,
+                              H(out), as_stream(stream)));
+    c->stats.kernel_launches += 1;
+    return kOk;
+}
+
+int fls_lm_head(fls_ctx* c, int slot, int layer_idx, const uint16_t* x, int n_rows, uint16_t* probs,
+                const int32_t* answer_ids, int n_ids, float* logprob, float* lse_out, void* stream) {
+    ENTER(c);
+    const ResidentLayer* r = find_resident(c, slot, layer_idx, FLS_LAYER_HEAD);
+    if (!r) return ctx_fail(c, kErrState);
+    if (n_rows <= 0) return kOk;
+    CTX_TRY(c, head_impl(c, H(x), r->single, n_rows, c->m.vocab_size, c->m.hidden_size, H(probs), answer_ids, n_ids,
+                         logprob, lse_out, as_stream(stream)));
+    return kOk;
+}
+
+// --------------------------------------------------------------------------------- single kernels
+int fls_op_gemm(fls_ctx* c, int epilogue, const uint16_t* a_dev, int lda, const uint16_t* b_dev, int ldb, int b_rows,
+                int m, int n, int k, uint16_t* c_dev, int ldc, const uint16_t* r_dev, int ldr, int up_off,
+                void* stream) {
+    ENTER(c);
+    if (epilogue < FLS_EPI_STORE || epilogue > FLS_EPI_SWIGLU)
+        return ctx_fail(c, fail(kErrInvalid, "fls_op_gemm: epilogue %d", epilogue));
+    GemmArgs a{};
+    a.A = H(a_dev), a.lda = lda, a.B = H(b_dev), a.ldb = ldb, a.b_rows = b_rows, a.M = m, a.N = n, a.K = k;
+    a.C = H(c_dev), a.ldc = ldc, a.R = H(r_dev), a.ldr = ldr, a.up_off = up_off;
+    CTX_TRY(c, gemm_launch(static_cast<GemmEpilogue>(epilogue), a, c->num_sms, as_stream(stream)));
+    c->stats.kernel_launches += 1;
+    return kOk;
+}
+
+int fls_op_rmsnorm(fls_ctx* c, const uint16_t* x, const uint16_t* delta, const int32_t* gather, const uint16_t* w,
+                   float eps, int n_rows, int hidden, uint16_t* x_sum, uint16_t* out, void* stream) {
+    ENTER(c);
+    CTX_TRY(c, rmsnorm_launch(H(x), H(delta), gather, H(w), eps, n_rows, hidden, H(x_sum), H(out), as_stream(stream)));
+    c->stats.kernel_launches += 1;
+    return kOk;
+}
+
+int fls_op_rope(fls_ctx* c, uint16_t* qkv, int ld, int n_rows, int n_q_heads, int n_kv_heads, int head_dim,
+                const int32_t* row_pos, void* stream) {
+    ENTER(c);
+    if (!c->rope_cos || head_dim != c->m.head_dim)
+        return ctx_fail(c, fail(kErrState, "fls_op_rope: rope table missing or head_dim mismatch"));
+    CTX_TRY(c, rope_launch(H(qkv), ld, n_rows, n_q_heads, n_kv_heads, head_dim, row_pos, c->rope_cos, c->rope_sin,
+                           c->rope_n_pos, as_stream(stream)));
+    c->stats.kernel_launches += 1;
+    return kOk;
+}
+
+int fls_op_attention(fls_ctx* c, const uint16_t* qkv, int ld, int n_q_heads, int n_kv_heads, int head_dim,
+                     const fls_attn_tile* tiles, int n_tiles, uint16_t* out, int ld_out, void* stream) {
+    ENTER(c);
+    CTX_TRY(c, attention_launch(H(qkv), ld, n_q_heads, n_kv_heads, head_dim, reinterpret_cast<const AttnTile*>(tiles),
+                                n_tiles, H(out), ld_out, as_stream(stream)));
+    c->stats.kernel_launches += 1;
+    return kOk;
+}
+
+int fls_op_swiglu(fls_ctx* c, const uint16_t* gate, const uint16_t* up, int ld_in, int n_rows, int inter,
+                  uint16_t* out, int ld_out, void* stream) {
+    ENTER(c);
+    CTX_TRY(c, swiglu_launch(H(gate), H(up), ld_in, n_rows, inter, H(out), ld_out, as_stream(stream)));
+    c->stats.kernel_launches += 1;
+    return kOk;
+}
+
+int fls_op_embed(fls_ctx* c, const uint16_t* table, const int32_t* ids, int n_rows, int hidden, uint16_t* out,
+                 void* stream) {
+    ENTER(c);
+    CTX_TRY(c, embed_launch(H(table), ids, n_rows, hidden, H(out), as_stream(stream)));
+    c->stats.kernel_launches += 1;
+    return kOk;
+}
+
+int fls_op_head(fls_ctx* c, const uint16_t* x, const uint16_t* w, int n_rows, int n, int k, uint16_t* probs,
+                const int32_t* answer_ids, int n_ids, float* logprob, float* lse_out, void* stream) {
+    ENTER(c);
+    if (!c->lse_partial) return ctx_fail(c, fail(kErrState, "fls_op_head: call fls_configure first"));
+    CTX_TRY(c, head_impl(c, H(x), H(w), n_rows, n, k, H(probs), answer_ids, n_ids, logprob, lse_out,
+                         as_stream(stream)));
+    return kOk;
+}
+
+int fls_get_stats(fls_ctx* c, fls_stats* out) {
+    if (!c || !out) return fail(kErrInvalid, "fls_get_stats: null argument");
+    cudaSetDevice(c->device);
+    for (auto& s : c->slots) harvest_copy_timing(c, s);
+    c->stats.file_bytes_read = host_cache_file_bytes();
+    c->stats.pinned_bytes = host_cache_pinned_bytes();
+    c->stats.workspace_bytes = c->workspace_bytes;
+    *out = c->stats;
+    return kOk;
+}
+
+int fls_reset_stats(fls_ctx* c) {
+    if (!c) return fail(kErrInvalid, "fls_reset_stats: null context");
+    c->stats = fls_stats{};
+    return kOk;
+}
+
+}  // extern "C"

@@ -1,0 +1,97 @@
+// Shared declarations for the fls_b200 library (internal; the public surface is include/fls_b200.h).
+#pragma once
+#include <cstdint>
+#include <cstdio>
+#include <cuda_fp16.h>
+#include <cuda_runtime.h>
+
+namespace fls {
+
+// ---- error plumbing: every internal launcher returns 0 or a negative fls status and leaves a
+// message in a thread-local buffer that the C-ABI layer copies into the context.
+constexpr int kOk = 0;
+constexpr int kErrInvalid = -1;   // bad argument
+constexpr int kErrCuda = -2;      // CUDA runtime/driver error
+constexpr int kErrIo = -3;        // file / parse error
+constexpr int kErrState = -4;     // call sequence error
+constexpr int kErrCapacity = -5;  // exceeds configured workspace / slot capacity
+
+char* tls_error_buffer();  // 512 bytes
+int fail(int code, const char* fmt, ...);
+
+#define FLS_CUDA(expr)                                                                           \
+    do {                                                                                         \
+        cudaError_t _e = (expr);                                                                 \
+        if (_e != cudaSuccess)                                                                   \
+            return ::fls::fail(::fls::kErrCuda, "%s failed: %s (%s:%d)", #expr, cudaGetErrorString(_e), \
+                               __FILE__, __LINE__);                                              \
+    } while (0)
+
+#define FLS_TRY(expr)          \
+    do {                       \
+        int _s = (expr);       \
+        if (_s != 0) return _s; \
+    } while (0)
+
+// ---- GEMM (gemm_sm100.cu) ---------------------------------------------------------------
+// C[M,N] = A[M,K] * B[N,K]^T ; A, B fp16 row-major (K contiguous), fp32 accumulation in TMEM.
+enum GemmEpilogue : int {
+    kEpiStore = 0,       // C = fp16(acc)
+    kEpiResidual = 1,    // C = R + fp16(acc)            (R may alias C)
+    kEpiSwiGLU = 2,      // C[M,N] = fp16(silu(fp16(acc_gate))) * fp16(acc_up); B rows [0,N) = gate, [up_off, up_off+N) = up
+    kEpiLsePartial = 3,  // partial[row, n_blk] = (max, sum exp) of fp16(acc) over the tile's columns
+    kEpiProbs = 4,       // C = fp16(exp(fp16(acc) - lse[row]))
+};
+
+struct GemmArgs {
+    const __half* A;
+    int lda;
+    const __half* B;
+    int ldb;
+    int b_rows;  // rows of B addressable through the tensor map (>= N, or >= up_off + N for SwiGLU)
+    int M, N, K;
+    __half* C;
+    int ldc;
+    const __half* R;
+    int ldr;
+    float2* partial;  // [M, ceil(N/256)]
+    const float* lse;  // [M]
+    int up_off;
+};
+int gemm_launch(GemmEpilogue epi, const GemmArgs& a, int num_sms, cudaStream_t stream);
+int gemm_init();  // resolves cuTensorMapEncodeTiled and opts kernels into large dynamic smem
+int gemm_lse_blocks(int N);
+
+// ---- element-wise / reductions (elementwise.cu) ---------------------------------------------
+int embed_launch(const __half* table, const int32_t* ids, int n_rows, int H, __half* out, cudaStream_t s);
+// out_norm[r] = w * fp16(x32 * rsqrt(mean(x32^2) + eps)), x = x_in[gather ? gather[r] : r] (+ delta[r]);
+// when delta != nullptr the sum is also written back to x_sum (may alias x_in).
+int rmsnorm_launch(const __half* x_in, const __half* delta, const int32_t* gather, const __half* w, float eps,
+                   int n_rows, int H, __half* x_sum, __half* out_norm, cudaStream_t s);
+// In-place rotary embedding on the q and k column blocks of a packed qkv buffer.
+int rope_launch(__half* qkv, int ld, int n_rows, int n_q_heads, int n_kv_heads, int head_dim,
+                const int32_t* row_pos, const __half* cos_tab, const __half* sin_tab, int n_pos, cudaStream_t s);
+int swiglu_launch(const __half* gate, const __half* up, int ld_in, int n_rows, int I, __half* out, int ld_out,
+                  cudaStream_t s);
+int lse_reduce_launch(const float2* partial, int n_rows, int n_blocks, float* lse, cudaStream_t s);
+// out[r, j] = float(fp16(dot(x[r], W[ids[r*n_ids + j]]))) - lse[r]
+int gather_logprob_launch(const __half* x, int ldx, const __half* W, int ldw, int H, const int32_t* ids, int n_ids,
+                          const float* lse, int n_rows, float* out, cudaStream_t s);
+
+// ---- attention (attention.cu) ------------------------------------------------------------------
+// One descriptor per (query tile); see include/fls_b200.h fls_attn_tile.
+struct AttnTile {
+    int32_t q_row;     // first query row (packed row index)
+    int32_t n_q;       // queries in this tile (<= 64)
+    int32_t q_seq0;    // sequence index of the first query (key t visible iff t <= q_seq0 + i) ...
+    int32_t causal;    // ... when causal != 0; otherwise every key of both segments is visible
+    int32_t seg0_row;  // first key/value row of segment 0 (the prompt's prefix rows)
+    int32_t seg0_len;
+    int32_t seg1_row;  // first key/value row of segment 1 (the option's own rows); len may be 0
+    int32_t seg1_len;
+};
+int attention_launch(const __half* qkv, int ld, int n_q_heads, int n_kv_heads, int head_dim, const AttnTile* tiles,
+                     int n_tiles, __half* out, int ld_out, cudaStream_t s);
+int attention_init();
+
+}  // namespace fls

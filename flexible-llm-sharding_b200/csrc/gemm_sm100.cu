@@ -1,0 +1,405 @@
+// tcgen05 / TMEM / TMA GEMM for sm_100a with fused epilogues.
+//
+//   C[M,N] = A[M,K] * B[N,K]^T      A = packed token rows (fp16, K contiguous)
+//                                   B = nn.Linear weight [out,in] exactly as stored in the layer
+//                                       file (fp16, K contiguous) -> K-major operand, no transpose
+//
+// Replaces every `nn.Linear` call the reference issues through transformers (q/k/v/o_proj,
+// gate/up/down_proj, lm_head; reference utils.py:272,278,288), which there are cuBLAS HGEMMs
+// with M <= a few hundred rows, one prompt at a time.  Here M = all packed rows of a micro-batch.
+//
+// Structure: persistent CTAs (one per SM), 256 threads, warp-specialised:
+//   warp 0      TMA producer: A tile 128x64 and B tile 256x64 per stage (128B swizzle), 4 stages
+//   warp 1      MMA issuer: one elected thread, tcgen05.mma cta_group::1 kind::f16, M=128 N=256 K=16,
+//               fp32 accumulators in TMEM, two accumulator stages (2 x 256 columns = all 512)
+//   warp 2      TMEM allocator
+//   warps 4-7   epilogue: tcgen05.ld (32 lanes x 32 columns per warp) -> registers -> fused op ->
+//               global.  Overlaps the next tile's main loop through the second accumulator stage.
+// Rounding in the epilogues follows the reference's eager fp16 order (see each epilogue).
+#include <cuda.h>
+
+#include "common.cuh"
+#include "ptx.cuh"
+
+namespace fls {
+
+namespace {
+
+constexpr int BLOCK_M = 128;
+constexpr int BLOCK_N = 256;  // MMA N (TMEM columns per accumulator stage)
+constexpr int BLOCK_K = 64;   // 64 fp16 = 128 B = one swizzle row
+constexpr int UMMA_K = 16;
+constexpr int STAGES = 4;
+constexpr int ACC_STAGES = 2;
+constexpr int A_BYTES = BLOCK_M * BLOCK_K * 2;  // 16 KiB
+constexpr int B_BYTES = BLOCK_N * BLOCK_K * 2;  // 32 KiB
+constexpr int STAGE_BYTES = A_BYTES + B_BYTES;
+constexpr int SMEM_BARRIER_BYTES = 256;
+constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + SMEM_BARRIER_BYTES + 1024;  // + alignment slack
+constexpr int NUM_THREADS = 256;
+constexpr int EPI_WARP0 = 4;
+constexpr int GROUP_M = 16;  // m-blocks per raster group: A bands of a group stay in L2 while n sweeps
+
+struct KParams {
+    int M, N, K;
+    __half* C;
+    int ldc;
+    const __half* R;
+    int ldr;
+    float2* partial;
+    const float* lse;
+    int up_off;
+    int num_m_blocks, num_n_blocks;
+};
+
+template <int EPI>
+__device__ __forceinline__ constexpr int out_cols_per_tile() {
+    return EPI == kEpiSwiGLU ? BLOCK_N / 2 : BLOCK_N;
+}
+
+__device__ __forceinline__ void tile_coords(int tile, int num_m_blocks, int num_n_blocks, int& m_blk, int& n_blk) {
+    const int per_group = GROUP_M * num_n_blocks;
+    const int group = tile / per_group;
+    const int first_m = group * GROUP_M;
+    const int gsize = min(num_m_blocks - first_m, GROUP_M);
+    const int local = tile - group * per_group;
+    m_blk = first_m + local % gsize;
+    n_blk = local / gsize;
+}
+
+__device__ __forceinline__ uint32_t pack_h2(__half a, __half b) {
+    __half2 h = __halves2half2(a, b);
+    return *reinterpret_cast<uint32_t*>(&h);
+}
+
+template <int EPI>
+__global__ void __launch_bounds__(NUM_THREADS, 1)
+gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CUtensorMap tmap_b,
+                    const KParams p) {
+    extern __shared__ uint8_t smem_raw[];
+    uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+    uint64_t* full_bar = reinterpret_cast<uint64_t*>(smem + STAGES * STAGE_BYTES);
+    uint64_t* empty_bar = full_bar + STAGES;
+    uint64_t* tmem_full_bar = empty_bar + STAGES;
+    uint64_t* tmem_empty_bar = tmem_full_bar + ACC_STAGES;
+    uint32_t* tmem_base_slot = reinterpret_cast<uint32_t*>(tmem_empty_bar + ACC_STAGES);
+
+    const int warp_idx = threadIdx.x >> 5;  // warp-uniform
+    const int lane = threadIdx.x & 31;
+
+    if (warp_idx == 0 && ptx::elect_one()) {
+        ptx::prefetch_tensormap(&tmap_a);
+        ptx::prefetch_tensormap(&tmap_b);
+    }
+    if (warp_idx == 1 && ptx::elect_one()) {
+        for (int i = 0; i < STAGES; ++i) {
+            ptx::mbar_init(&full_bar[i], 1);
+            ptx::mbar_init(&empty_bar[i], 1);
+        }
+        for (int i = 0; i < ACC_STAGES; ++i) {
+            ptx::mbar_init(&tmem_full_bar[i], 1);
+            ptx::mbar_init(&tmem_empty_bar[i], 4);  // one arrive per epilogue warp
+        }
+        ptx::fence_mbar_init();
+    }
+    if (warp_idx == 2) {
+        ptx::tmem_alloc<1>(tmem_base_slot, 512);
+        ptx::tmem_relinquish<1>();
+    }
+    ptx::tc_fence_before_sync();
+    __syncthreads();
+    ptx::tc_fence_after_sync();
+    const uint32_t tmem_base = *tmem_base_slot;
+
+    const int num_tiles = p.num_m_blocks * p.num_n_blocks;
+    const int k_blocks = (p.K + BLOCK_K - 1) / BLOCK_K;
+    constexpr int OUT_COLS = out_cols_per_tile<EPI>();
+
+    if (warp_idx == 0) {
+        // ------------------------------------------------------------------ TMA producer
+        if (ptx::elect_one()) {
+            int stage = 0;
+            uint32_t phase = 0;
+            for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
+                int m_blk, n_blk;
+                tile_coords(tile, p.num_m_blocks, p.num_n_blocks, m_blk, n_blk);
+                for (int kb = 0; kb < k_blocks; ++kb) {
+                    ptx::mbar_wait(&empty_bar[stage], phase ^ 1);
+                    uint8_t* sa = smem + stage * STAGE_BYTES;
+                    uint8_t* sb = sa + A_BYTES;
+                    ptx::mbar_arrive_expect_tx(&full_bar[stage], STAGE_BYTES);
+                    ptx::tma_load_2d(sa, &tmap_a, &full_bar[stage], kb * BLOCK_K, m_blk * BLOCK_M);
+                    if constexpr (EPI == kEpiSwiGLU) {
+                        // gate rows -> MMA columns [0,128), up rows -> MMA columns [128,256)
+                        ptx::tma_load_2d(sb, &tmap_b, &full_bar[stage], kb * BLOCK_K, n_blk * OUT_COLS);
+                        ptx::tma_load_2d(sb + B_BYTES / 2, &tmap_b, &full_bar[stage], kb * BLOCK_K,
+                                         p.up_off + n_blk * OUT_COLS);
+                    } else {
+                        ptx::tma_load_2d(sb, &tmap_b, &full_bar[stage], kb * BLOCK_K, n_blk * BLOCK_N);
+                    }
+                    if (++stage == STAGES) {
+                        stage = 0;
+                        phase ^= 1;
+                    }
+                }
+            }
+        }
+    } else if (warp_idx == 1) {
+        // ------------------------------------------------------------------ MMA issuer
+        if (ptx::elect_one()) {
+            constexpr uint32_t idesc = ptx::umma_idesc_f16_f32(BLOCK_M, BLOCK_N);
+            int stage = 0;
+            uint32_t phase = 0;
+            int acc = 0;
+            uint32_t acc_phase = 0;
+            for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
+                ptx::mbar_wait(&tmem_empty_bar[acc], acc_phase ^ 1);
+                ptx::tc_fence_after_sync();
+                const uint32_t tmem_d = tmem_base + acc * BLOCK_N;
+                for (int kb = 0; kb < k_blocks; ++kb) {
+                    ptx::mbar_wait(&full_bar[stage], phase);
+                    ptx::tc_fence_after_sync();
+                    const uint32_t sa = ptx::smem_u32(smem + stage * STAGE_BYTES);
+                    const uint64_t da = ptx::umma_smem_desc_sw128(sa);
+                    const uint64_t db = ptx::umma_smem_desc_sw128(sa + A_BYTES);
+#pragma unroll
+                    for (int k = 0; k < BLOCK_K / UMMA_K; ++k) {
+                        // advance 16 fp16 = 32 B inside the 128 B swizzle row: +2 in the (addr >> 4) field
+                        ptx::umma_f16<1>(tmem_d, da + 2 * k, db + 2 * k, idesc, (kb | k) != 0);
+                    }
+                    ptx::umma_commit(&empty_bar[stage]);  // frees the smem stage once these MMAs retire
+                    if (++stage == STAGES) {
+                        stage = 0;
+                        phase ^= 1;
+                    }
+                }
+                ptx::umma_commit(&tmem_full_bar[acc]);  // accumulator complete -> epilogue
+                if (++acc == ACC_STAGES) {
+                    acc = 0;
+                    acc_phase ^= 1;
+                }
+            }
+        }
+    } else if (warp_idx >= EPI_WARP0) {
+        // ------------------------------------------------------------------ epilogue
+        const int ew = warp_idx - EPI_WARP0;  // == warp_idx % 4 -> TMEM lanes [32*ew, 32*ew+32)
+        int acc = 0;
+        uint32_t acc_phase = 0;
+        for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
+            int m_blk, n_blk;
+            tile_coords(tile, p.num_m_blocks, p.num_n_blocks, m_blk, n_blk);
+            ptx::mbar_wait(&tmem_full_bar[acc], acc_phase);
+            ptx::tc_fence_after_sync();
+            const int row = m_blk * BLOCK_M + ew * 32 + lane;
+            const bool row_ok = row < p.M;
+            const uint32_t taddr = tmem_base + (static_cast<uint32_t>(ew * 32) << 16) + acc * BLOCK_N;
+            const int col0 = n_blk * OUT_COLS;
+
+            if constexpr (EPI == kEpiSwiGLU) {
+                // HF LlamaMLP: act_fn(gate_proj(x)) * up_proj(x), each op rounded to fp16.
+#pragma unroll 1
+                for (int c = 0; c < OUT_COLS / 32; ++c) {
+                    uint32_t g[32], u[32];
+                    ptx::tmem_ld_32x32(taddr + c * 32, g);
+                    ptx::tmem_ld_32x32(taddr + OUT_COLS + c * 32, u);
+                    ptx::tmem_ld_wait();
+                    if (row_ok) {
+                        __half* dst = p.C + static_cast<size_t>(row) * p.ldc + col0 + c * 32;
+#pragma unroll
+                        for (int v = 0; v < 4; ++v) {
+                            if (col0 + c * 32 + v * 8 < p.N) {
+                                uint32_t o[4];
+#pragma unroll
+                                for (int j = 0; j < 4; ++j) {
+                                    __half r2[2];
+#pragma unroll
+                                    for (int e = 0; e < 2; ++e) {
+                                        const int i = v * 8 + j * 2 + e;
+                                        const float gf = __half2float(__float2half_rn(__uint_as_float(g[i])));
+                                        const __half s = __float2half_rn(gf / (1.0f + expf(-gf)));
+                                        const __half uh = __float2half_rn(__uint_as_float(u[i]));
+                                        r2[e] = __hmul(s, uh);
+                                    }
+                                    o[j] = pack_h2(r2[0], r2[1]);
+                                }
+                                *reinterpret_cast<uint4*>(dst + v * 8) = make_uint4(o[0], o[1], o[2], o[3]);
+                            }
+                        }
+                    }
+                }
+            } else if constexpr (EPI == kEpiLsePartial) {
+                // running (max, sum exp) over this tile's columns of the fp16-rounded logits
+                float m_run = -INFINITY, s_run = 0.f;
+#pragma unroll 1
+                for (int c = 0; c < BLOCK_N / 32; ++c) {
+                    uint32_t r[32];
+                    ptx::tmem_ld_32x32(taddr + c * 32, r);
+                    ptx::tmem_ld_wait();
+                    float v[32];
+                    float cmax = -INFINITY;
+#pragma unroll
+                    for (int i = 0; i < 32; ++i) {
+                        v[i] = (col0 + c * 32 + i < p.N) ? __half2float(__float2half_rn(__uint_as_float(r[i])))
+                                                         : -INFINITY;
+                        cmax = fmaxf(cmax, v[i]);
+                    }
+                    if (cmax > -INFINITY) {
+                        const float m_new = fmaxf(m_run, cmax);
+                        float s = 0.f;
+#pragma unroll
+                        for (int i = 0; i < 32; ++i) s += __expf(v[i] - m_new);
+                        s_run = s_run * __expf(m_run - m_new) + s;
+                        m_run = m_new;
+                    }
+                }
+                if (row_ok) p.partial[static_cast<size_t>(row) * p.num_n_blocks + n_blk] = make_float2(m_run, s_run);
+            } else {
+                float lse = 0.f;
+                if constexpr (EPI == kEpiProbs) lse = row_ok ? p.lse[row] : 0.f;
+#pragma unroll 1
+                for (int c = 0; c < BLOCK_N / 32; ++c) {
+                    uint32_t r[32];
+                    ptx::tmem_ld_32x32(taddr + c * 32, r);
+                    ptx::tmem_ld_wait();
+                    if (row_ok) {
+                        const size_t off = static_cast<size_t>(row) * p.ldc + col0 + c * 32;
+#pragma unroll
+                        for (int v = 0; v < 4; ++v) {
+                            if (col0 + c * 32 + v * 8 < p.N) {
+                                uint32_t o[4];
+                                uint4 res = make_uint4(0, 0, 0, 0);
+                                if constexpr (EPI == kEpiResidual)
+                                    res = *reinterpret_cast<const uint4*>(p.R + static_cast<size_t>(row) * p.ldr + col0 +
+                                                                          c * 32 + v * 8);
+                                const uint32_t rr[4] = {res.x, res.y, res.z, res.w};
+#pragma unroll
+                                for (int j = 0; j < 4; ++j) {
+                                    __half h0 = __float2half_rn(__uint_as_float(r[v * 8 + j * 2]));
+                                    __half h1 = __float2half_rn(__uint_as_float(r[v * 8 + j * 2 + 1]));
+                                    if constexpr (EPI == kEpiResidual) {
+                                        // hidden = residual + linear(x): fp16 add of two fp16 values
+                                        const __half2 rh = *reinterpret_cast<const __half2*>(&rr[j]);
+                                        h0 = __hadd(__low2half(rh), h0);
+                                        h1 = __hadd(__high2half(rh), h1);
+                                    } else if constexpr (EPI == kEpiProbs) {
+                                        // softmax evaluated on the fp16 logits (reference utils.py:289)
+                                        h0 = __float2half_rn(__expf(__half2float(h0) - lse));
+                                        h1 = __float2half_rn(__expf(__half2float(h1) - lse));
+                                    }
+                                    o[j] = pack_h2(h0, h1);
+                                }
+                                *reinterpret_cast<uint4*>(p.C + off + v * 8) = make_uint4(o[0], o[1], o[2], o[3]);
+                            }
+                        }
+                    }
+                }
+            }
+            ptx::tc_fence_before_sync();
+            __syncwarp();
+            if (lane == 0) ptx::mbar_arrive(&tmem_empty_bar[acc]);
+            if (++acc == ACC_STAGES) {
+                acc = 0;
+                acc_phase ^= 1;
+            }
+        }
+    }
+
+    ptx::tc_fence_before_sync();
+    __syncthreads();
+    if (warp_idx == 2) {
+        ptx::tc_fence_after_sync();
+        ptx::tmem_dealloc<1>(tmem_base, 512);
+    }
+}
+
+// ------------------------------------------------------------------------------------ host side
+using EncodeTiledFn = CUresult (*)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
+                                   const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
+                                   CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+EncodeTiledFn g_encode = nullptr;
+
+int make_tmap(CUtensorMap* tm, const __half* base, int rows, int cols, int ld, int box_rows) {
+    if ((reinterpret_cast<uintptr_t>(base) & 15) || (ld % 8))
+        return fail(kErrInvalid, "gemm operand must be 16-byte aligned with a row stride multiple of 8 (ld=%d)", ld);
+    const cuuint64_t dims[2] = {static_cast<cuuint64_t>(cols), static_cast<cuuint64_t>(rows)};
+    const cuuint64_t strides[1] = {static_cast<cuuint64_t>(ld) * sizeof(__half)};
+    const cuuint32_t box[2] = {BLOCK_K, static_cast<cuuint32_t>(box_rows)};
+    const cuuint32_t estr[2] = {1, 1};
+    CUresult r = g_encode(tm, CU_TENSOR_MAP_DATA_TYPE_FLOAT16, 2, const_cast<__half*>(base), dims, strides, box, estr,
+                          CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                          CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    if (r != CUDA_SUCCESS) return fail(kErrCuda, "cuTensorMapEncodeTiled failed (CUresult %d)", static_cast<int>(r));
+    return kOk;
+}
+
+template <int EPI>
+int launch_t(const GemmArgs& a, int num_sms, cudaStream_t stream) {
+    constexpr int OUT_COLS = EPI == kEpiSwiGLU ? BLOCK_N / 2 : BLOCK_N;
+    CUtensorMap tma, tmb;
+    FLS_TRY(make_tmap(&tma, a.A, a.M, a.K, a.lda, BLOCK_M));
+    FLS_TRY(make_tmap(&tmb, a.B, a.b_rows, a.K, a.ldb, EPI == kEpiSwiGLU ? BLOCK_N / 2 : BLOCK_N));
+    KParams p;
+    p.M = a.M, p.N = a.N, p.K = a.K;
+    p.C = a.C, p.ldc = a.ldc, p.R = a.R, p.ldr = a.ldr;
+    p.partial = a.partial, p.lse = a.lse, p.up_off = a.up_off;
+    p.num_m_blocks = (a.M + BLOCK_M - 1) / BLOCK_M;
+    p.num_n_blocks = (a.N + OUT_COLS - 1) / OUT_COLS;
+    const int tiles = p.num_m_blocks * p.num_n_blocks;
+    const int grid = tiles < num_sms ? tiles : num_sms;
+    gemm_tcgen05_kernel<EPI><<<grid, NUM_THREADS, SMEM_BYTES, stream>>>(tma, tmb, p);
+    FLS_CUDA(cudaGetLastError());
+    return kOk;
+}
+
+template <int EPI>
+int set_smem_attr() {
+    FLS_CUDA(cudaFuncSetAttribute(gemm_tcgen05_kernel<EPI>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_BYTES));
+    return kOk;
+}
+
+}  // namespace
+
+int gemm_lse_blocks(int N) { return (N + BLOCK_N - 1) / BLOCK_N; }
+
+int gemm_init() {
+    if (!g_encode) {
+        void* fn = nullptr;
+        cudaDriverEntryPointQueryResult qres;
+        FLS_CUDA(cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &fn, cudaEnableDefault, &qres));
+        if (!fn || qres != cudaDriverEntryPointSuccess)
+            return fail(kErrCuda, "driver does not export cuTensorMapEncodeTiled");
+        g_encode = reinterpret_cast<EncodeTiledFn>(fn);
+    }
+    FLS_TRY(set_smem_attr<kEpiStore>());
+    FLS_TRY(set_smem_attr<kEpiResidual>());
+    FLS_TRY(set_smem_attr<kEpiSwiGLU>());
+    FLS_TRY(set_smem_attr<kEpiLsePartial>());
+    FLS_TRY(set_smem_attr<kEpiProbs>());
+    return kOk;
+}
+
+int gemm_launch(GemmEpilogue epi, const GemmArgs& a, int num_sms, cudaStream_t stream) {
+    if (!g_encode) return fail(kErrState, "gemm_init() has not run");
+    if (a.M <= 0 || a.N <= 0 || a.K <= 0) return fail(kErrInvalid, "gemm: empty problem %dx%dx%d", a.M, a.N, a.K);
+    if (a.K % 8 || a.N % 8) return fail(kErrInvalid, "gemm: N and K must be multiples of 8 (N=%d K=%d)", a.N, a.K);
+    if (epi != kEpiLsePartial && (a.ldc % 8 || (reinterpret_cast<uintptr_t>(a.C) & 15)))
+        return fail(kErrInvalid, "gemm: C must be 16-byte aligned with ldc %% 8 == 0");
+    switch (epi) {
+        case kEpiStore: return launch_t<kEpiStore>(a, num_sms, stream);
+        case kEpiResidual:
+            if (!a.R || a.ldr % 8) return fail(kErrInvalid, "gemm: residual epilogue needs R with ldr %% 8 == 0");
+            return launch_t<kEpiResidual>(a, num_sms, stream);
+        case kEpiSwiGLU:
+            if (a.b_rows < a.up_off + a.N) return fail(kErrInvalid, "gemm: SwiGLU needs gate and up rows in B");
+            return launch_t<kEpiSwiGLU>(a, num_sms, stream);
+        case kEpiLsePartial:
+            if (!a.partial) return fail(kErrInvalid, "gemm: lse epilogue needs a partial buffer");
+            return launch_t<kEpiLsePartial>(a, num_sms, stream);
+        case kEpiProbs:
+            if (!a.lse) return fail(kErrInvalid, "gemm: probs epilogue needs lse");
+            return launch_t<kEpiProbs>(a, num_sms, stream);
+    }
+    return fail(kErrInvalid, "gemm: unknown epilogue %d", static_cast<int>(epi));
+}
+
+}  // namespace fls

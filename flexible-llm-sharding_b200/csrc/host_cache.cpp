@@ -1,0 +1,331 @@
+// Process-wide pinned-host cache of layer files + safetensors header parsing.
+//
+// Stands in for the reference's file handling: `safetensors_load(f.read())` per layer per call
+// (reference utils.py:126-127) and, in data-parallel mode, DeviceManager's "read each layer to RAM
+// once and hand the same state dict to every GPU thread" (utils.py:35-41,67-75).  Here each layer
+// file is read once per process into page-locked memory (parallel pread) and every context copies
+// from that image, so H2D copies are asynchronous and run at link rate.
+#include "host_cache.h"
+
+#include <fcntl.h>
+#include <sys/stat.h>
+#include <unistd.h>
+#include <cerrno>
+
+#include <algorithm>
+#include <atomic>
+#include <cstring>
+#include <mutex>
+#include <thread>
+#include <unordered_map>
+
+#include <cuda_fp16.h>
+#include <cuda_runtime.h>
+
+#include "common.cuh"
+
+namespace fls {
+
+namespace {
+
+// ---- a JSON reader just big enough for a safetensors header --------------------------------
+struct Json {
+    const char* p;
+    const char* end;
+    bool ok = true;
+
+    void ws() {
+        while (p < end && (*p == ' ' || *p == '\n' || *p == '\t' || *p == '\r')) ++p;
+    }
+    bool eat(char c) {
+        ws();
+        if (p < end && *p == c) {
+            ++p;
+            return true;
+        }
+        return false;
+    }
+    std::string str() {
+        ws();
+        std::string s;
+        if (p >= end || *p != '"') {
+            ok = false;
+            return s;
+        }
+        ++p;
+        while (p < end && *p != '"') {
+            if (*p == '\\' && p + 1 < end) {
+                ++p;
+                switch (*p) {
+                    case 'n': s += '\n'; break;
+                    case 't': s += '\t'; break;
+                    case 'u': s += '?'; p += std::min<ptrdiff_t>(4, end - p - 1); break;
+                    default: s += *p;
+                }
+                ++p;
+            } else {
+                s += *p++;
+            }
+        }
+        if (p >= end) ok = false;
+        else ++p;
+        return s;
+    }
+    long long num() {
+        ws();
+        char* e = nullptr;
+        long long v = strtoll(p, &e, 10);
+        if (e == p) ok = false;
+        p = e;
+        return v;
+    }
+    void skip() {  // skip any value
+        ws();
+        if (p >= end) {
+            ok = false;
+            return;
+        }
+        if (*p == '"') {
+            str();
+        } else if (*p == '{' || *p == '[') {
+            const char close = *p == '{' ? '}' : ']';
+            const bool obj = *p == '{';
+            ++p;
+            if (eat(close)) return;
+            do {
+                if (obj) {
+                    str();
+                    if (!eat(':')) ok = false;
+                }
+                skip();
+            } while (ok && eat(','));
+            if (!eat(close)) ok = false;
+        } else {
+            while (p < end && *p != ',' && *p != '}' && *p != ']') ++p;
+        }
+    }
+};
+
+struct CacheEntry {
+    std::shared_ptr<HostLayerImage> img;
+    uint64_t last_use = 0;
+};
+
+std::mutex g_mu;
+std::unordered_map<std::string, CacheEntry> g_cache;
+std::atomic<uint64_t> g_clock{0};
+std::atomic<uint64_t> g_file_bytes{0};
+std::atomic<uint64_t> g_pinned_bytes{0};
+
+int parallel_pread(int fd, char* dst, size_t off, size_t n) {
+    const size_t chunk = size_t(32) << 20;
+    const size_t n_chunks = (n + chunk - 1) / chunk;
+    const unsigned hw = std::max(1u, std::thread::hardware_concurrency());
+    const size_t n_threads = std::min<size_t>(std::min<size_t>(8, hw), std::max<size_t>(1, n_chunks));
+    std::atomic<size_t> next{0};
+    std::atomic<int> err{0};
+    auto work = [&]() {
+        for (;;) {
+            const size_t c = next.fetch_add(1);
+            if (c >= n_chunks || err.load()) return;
+            size_t o = c * chunk, left = std::min(chunk, n - o);
+            while (left) {
+                const ssize_t r = pread(fd, dst + o, left, static_cast<off_t>(off + o));
+                if (r <= 0) {
+                    err.store(1);
+                    return;
+                }
+                o += static_cast<size_t>(r);
+                left -= static_cast<size_t>(r);
+            }
+        }
+    };
+    std::vector<std::thread> th;
+    for (size_t i = 1; i < n_threads; ++i) th.emplace_back(work);
+    work();
+    for (auto& t : th) t.join();
+    return err.load() ? -1 : 0;
+}
+
+void convert_to_f16(const char* src, const std::string& dtype, size_t n, __half* dst) {
+    if (dtype == "F32") {
+        const float* s = reinterpret_cast<const float*>(src);
+        for (size_t i = 0; i < n; ++i) dst[i] = __float2half_rn(s[i]);
+    } else {  // BF16
+        const uint16_t* s = reinterpret_cast<const uint16_t*>(src);
+        for (size_t i = 0; i < n; ++i) {
+            const uint32_t bits = static_cast<uint32_t>(s[i]) << 16;
+            float f;
+            memcpy(&f, &bits, 4);
+            dst[i] = __float2half_rn(f);
+        }
+    }
+}
+
+}  // namespace
+
+HostLayerImage::~HostLayerImage() {
+    if (pinned) {
+        cudaFreeHost(pinned);
+        g_pinned_bytes.fetch_sub(pinned_bytes);
+    }
+}
+
+int parse_safetensors_header(const std::string& path, std::vector<TensorEntry>* out, size_t* data_start,
+                             size_t* file_size) {
+    const int fd = open(path.c_str(), O_RDONLY);
+    if (fd < 0) return fail(kErrIo, "cannot open %s: %s", path.c_str(), strerror(errno));
+    struct stat st;
+    fstat(fd, &st);
+    uint64_t hlen = 0;
+    if (pread(fd, &hlen, 8, 0) != 8 || hlen == 0 || hlen > (100u << 20) ||
+        8 + hlen > static_cast<uint64_t>(st.st_size)) {
+        close(fd);
+        return fail(kErrIo, "%s: not a safetensors file (bad header length)", path.c_str());
+    }
+    std::string hdr(hlen, '\0');
+    if (pread(fd, hdr.data(), hlen, 8) != static_cast<ssize_t>(hlen)) {
+        close(fd);
+        return fail(kErrIo, "%s: short read of the header", path.c_str());
+    }
+    close(fd);
+    *data_start = 8 + hlen;
+    *file_size = static_cast<size_t>(st.st_size);
+
+    Json j{hdr.data(), hdr.data() + hdr.size()};
+    if (!j.eat('{')) return fail(kErrIo, "%s: header is not a JSON object", path.c_str());
+    if (!j.eat('}')) {
+        do {
+            const std::string name = j.str();
+            if (!j.eat(':')) j.ok = false;
+            if (name == "__metadata__") {
+                j.skip();
+                continue;
+            }
+            TensorEntry t;
+            t.name = name;
+            if (!j.eat('{')) j.ok = false;
+            do {
+                const std::string key = j.str();
+                if (!j.eat(':')) j.ok = false;
+                if (key == "dtype") {
+                    t.dtype = j.str();
+                } else if (key == "shape") {
+                    if (!j.eat('[')) j.ok = false;
+                    if (!j.eat(']')) {
+                        do t.shape.push_back(j.num());
+                        while (j.ok && j.eat(','));
+                        if (!j.eat(']')) j.ok = false;
+                    }
+                } else if (key == "data_offsets") {
+                    if (!j.eat('[')) j.ok = false;
+                    t.begin = static_cast<size_t>(j.num());
+                    if (!j.eat(',')) j.ok = false;
+                    t.end = static_cast<size_t>(j.num());
+                    if (!j.eat(']')) j.ok = false;
+                } else {
+                    j.skip();
+                }
+            } while (j.ok && j.eat(','));
+            if (!j.eat('}')) j.ok = false;
+            if (!j.ok) break;
+            size_t n = 1;
+            for (long long d : t.shape) n *= static_cast<size_t>(d);
+            t.numel = n;
+            if (t.end < t.begin || *data_start + t.end > *file_size)
+                return fail(kErrIo, "%s: tensor %s data_offsets outside the file", path.c_str(), name.c_str());
+            out->push_back(std::move(t));
+        } while (j.ok && j.eat(','));
+        if (j.ok && !j.eat('}')) j.ok = false;
+    }
+    if (!j.ok) return fail(kErrIo, "%s: malformed safetensors header", path.c_str());
+    return kOk;
+}
+
+int acquire_host_image(const std::string& path, std::shared_ptr<HostLayerImage>* out) {
+    {
+        std::lock_guard<std::mutex> lk(g_mu);
+        auto it = g_cache.find(path);
+        if (it != g_cache.end()) {
+            it->second.last_use = ++g_clock;
+            *out = it->second.img;
+            return kOk;
+        }
+    }
+    // Load outside the lock on a private image, publish afterwards (a racing duplicate is dropped).
+    auto img = std::make_shared<HostLayerImage>();
+    img->path = path;
+    size_t data_start = 0, file_size = 0;
+    FLS_TRY(parse_safetensors_header(path, &img->tensors, &data_start, &file_size));
+    size_t total = 0;
+    for (auto& t : img->tensors) {
+        if (t.dtype != "F16" && t.dtype != "BF16" && t.dtype != "F32")
+            return fail(kErrInvalid, "%s: tensor %s has dtype %s; only F16/BF16/F32 weights are supported "
+                        "(int8 needs fp16 statistics, as in the reference)", path.c_str(), t.name.c_str(),
+                        t.dtype.c_str());
+        t.host_off = total;
+        total += (t.numel * 2 + 255) & ~size_t(255);
+    }
+    cudaError_t e = cudaHostAlloc(reinterpret_cast<void**>(&img->pinned), std::max<size_t>(total, 256),
+                                  cudaHostAllocPortable);
+    if (e != cudaSuccess)
+        return fail(kErrCuda, "cudaHostAlloc(%zu bytes) for %s failed: %s", total, path.c_str(), cudaGetErrorString(e));
+    img->pinned_bytes = total;
+    g_pinned_bytes.fetch_add(total);
+
+    const int fd = open(path.c_str(), O_RDONLY);
+    if (fd < 0) return fail(kErrIo, "cannot open %s: %s", path.c_str(), strerror(errno));
+    int rc = kOk;
+    std::vector<char> staging;
+    for (auto& t : img->tensors) {
+        const size_t nbytes = t.end - t.begin;
+        if (t.dtype == "F16") {
+            if (nbytes != t.numel * 2) {
+                rc = fail(kErrIo, "%s: tensor %s size mismatch", path.c_str(), t.name.c_str());
+                break;
+            }
+            if (parallel_pread(fd, img->pinned + t.host_off, data_start + t.begin, nbytes)) {
+                rc = fail(kErrIo, "%s: short read of tensor %s", path.c_str(), t.name.c_str());
+                break;
+            }
+        } else {
+            staging.resize(nbytes);
+            if (parallel_pread(fd, staging.data(), data_start + t.begin, nbytes)) {
+                rc = fail(kErrIo, "%s: short read of tensor %s", path.c_str(), t.name.c_str());
+                break;
+            }
+            convert_to_f16(staging.data(), t.dtype, t.numel, reinterpret_cast<__half*>(img->pinned + t.host_off));
+        }
+        g_file_bytes.fetch_add(nbytes);
+    }
+    close(fd);
+    if (rc != kOk) return rc;
+
+    std::lock_guard<std::mutex> lk(g_mu);
+    auto& slot = g_cache[path];
+    if (!slot.img) slot.img = img;
+    slot.last_use = ++g_clock;
+    *out = slot.img;
+    return kOk;
+}
+
+size_t trim_host_cache(size_t keep_bytes) {
+    std::lock_guard<std::mutex> lk(g_mu);
+    size_t held = 0;
+    for (auto& kv : g_cache) held += kv.second.img->pinned_bytes;
+    while (held > keep_bytes) {
+        auto victim = g_cache.end();
+        for (auto it = g_cache.begin(); it != g_cache.end(); ++it)
+            if (it->second.img.use_count() == 1 && (victim == g_cache.end() || it->second.last_use < victim->second.last_use))
+                victim = it;
+        if (victim == g_cache.end()) break;
+        held -= victim->second.img->pinned_bytes;
+        g_cache.erase(victim);
+    }
+    return held;
+}
+
+uint64_t host_cache_file_bytes() { return g_file_bytes.load(); }
+uint64_t host_cache_pinned_bytes() { return g_pinned_bytes.load(); }
+
+}  // namespace fls

@@ -1,0 +1,153 @@
+"""CLI - same flags, pickle formats and side effects as the reference's `main.py`
+(reference main.py:28-98), driving the B200 path.
+
+    python main.py --model_path ./llama2_layers --prompt_pickle prompts.pkl --output_file scores.pkl \
+                   [--layer_num_per_shard 1] [--storage_location cpu|gpu|disk] [--num_batch 1] \
+                   [--data_parallel True] [--max_activation_in_cpu 100] [--disk_folder ./temp] [--num_gen_token 1]
+
+Input pickle: list of `(prefix: str, suffixes: tuple[str, ...])`.  Outputs: `output_file` = list of
+`np.ndarray [n_suffixes, num_gen_token, vocab]` float16, and `<prompt_pickle>_updated.pkl` with the
+generated tokens appended to every suffix (main.py:86-98).
+
+Multi-GPU: inside one process the reference's threading model is kept (one host thread per visible
+GPU, main.py:67-73).  Under `torchrun` (WORLD_SIZE set) each rank drives its own GPU instead:
+`--data_parallel` partitions the prompts (np.array_split order) and rank 0 gathers the scores.
+"""
+from __future__ import annotations
+
+import argparse
+import copy
+import os
+import pickle
+from concurrent.futures import ThreadPoolExecutor
+from functools import partial
+
+import numpy as np
+
+from . import planner
+
+
+def run_sharded_llama(device, prompt_list, device_manager, args):
+    """reference main.py:14-25."""
+    from .utils import ShardedLlama
+    model = ShardedLlama(args, device_manager, device=device)
+    if not args.data_parallel and device != device_manager.devices[0]:  # don't need actual prompts
+        prompt_list = [None] * len(prompt_list)
+    outputs = []
+    for lo, hi in planner.batch_ranges(len(prompt_list), args.num_batch):
+        outputs += model(prompt_list[lo:hi])
+    return outputs
+
+
+def build_parser() -> argparse.ArgumentParser:
+    parser = argparse.ArgumentParser()
+    parser.add_argument("--model_path", type=str, default="./")
+    parser.add_argument("--prompt_pickle", type=str, required=True, help="Path to the input prompt pickle file")
+    parser.add_argument("--output_file", type=str, required=True, help="Path to the LLM output scores file")
+    parser.add_argument("--num_batch", type=int, default=1)
+    parser.add_argument("--layer_num_per_shard", type=int, default=1)
+    parser.add_argument("--storage_location", type=str, default="cpu",
+                        help="'gpu': use vRAM to store intermediate activations, 'cpu': use RAM, 'disk': use disk")
+    parser.add_argument("--max_activation_in_cpu", type=int, default=100)
+    # type=bool as in the reference (main.py:40): any non-empty string, including "False", is True
+    parser.add_argument("--data_parallel", type=bool, default=False, required=False,
+                        help="if True, multiple GPUs run with data parallelism; if False, with model parallelism.")
+    parser.add_argument("--disk_folder", type=str, default="./temp",
+                        help="folder path for writing files of intermediate activations in 'disk' mode")
+    parser.add_argument("--num_gen_token", type=int, default=1, help="how many new tokens to be generated")
+    return parser
+
+
+def score_all(args, input_prompts, devices):
+    """One pass over all prompts on all devices of this process (main.py:66-76)."""
+    from .utils import DeviceManager
+    device_manager = DeviceManager(args, devices)
+    run = partial(run_sharded_llama, device_manager=device_manager, args=args)
+    if len(devices) > 1:
+        if args.data_parallel:
+            parts = [input_prompts[lo:hi] for lo, hi in planner.partition_prompts(len(input_prompts), len(devices))]
+            with ThreadPoolExecutor(max_workers=len(devices)) as ex:
+                outputs = list(ex.map(run, devices, parts))
+        else:
+            with ThreadPoolExecutor(max_workers=len(devices)) as ex:
+                outputs = list(ex.map(run, devices, [list(input_prompts) for _ in devices]))
+        return sum(outputs, [])
+    return run(devices[0], input_prompts)
+
+
+def score_all_distributed(args, input_prompts):
+    """torchrun mode: rank r scores its np.array_split part on its own GPU; rank 0 gathers."""
+    import torch
+    import torch.distributed as dist
+    rank, world = dist.get_rank(), dist.get_world_size()
+    local = int(os.environ.get("LOCAL_RANK", rank))
+    lo, hi = planner.partition_prompts(len(input_prompts), world)[rank]
+    from .utils import DeviceManager
+    device = f"cuda:{local}"
+    dm = DeviceManager(args, [device])
+    mine = run_sharded_llama(device, input_prompts[lo:hi], dm, args)
+    gathered = [None] * world if rank == 0 else None
+    dist.gather_object(mine, gathered, dst=0)
+    if rank == 0:
+        return sum(gathered, [])
+    return None
+
+
+def main(argv=None):
+    import torch
+    args = build_parser().parse_args(argv)
+    print(args)
+    if args.storage_location == "disk":
+        os.makedirs(args.disk_folder, exist_ok=True)
+    with open(args.prompt_pickle, "rb") as f:
+        original_input_prompts = pickle.load(f)
+    input_prompts = copy.deepcopy(original_input_prompts)
+
+    distributed = int(os.environ.get("WORLD_SIZE", "1")) > 1
+    if distributed:
+        import torch.distributed as dist
+        if not dist.is_initialized():
+            dist.init_process_group("gloo")       # host-side gather only; no data-path collective
+        if not args.data_parallel:
+            raise SystemExit("under torchrun only --data_parallel True is supported; model parallel runs "
+                             "in-process (python main.py with several visible GPUs)")
+        is_root = dist.get_rank() == 0
+    else:
+        is_root = True
+        num_device = torch.cuda.device_count()
+        devices = [f"cuda:{i}" for i in range(num_device)]
+        if not devices:
+            raise SystemExit("no CUDA device visible: this implementation has no CPU path")
+
+    from transformers import AutoTokenizer
+    output_scores, tokenizer = [], None
+    for i_new in range(args.num_gen_token):
+        prompts_now = list(input_prompts)
+        outputs = score_all_distributed(args, prompts_now) if distributed else score_all(args, prompts_now, devices)
+        if is_root:
+            if i_new == 0:
+                output_scores = outputs
+                tokenizer = AutoTokenizer.from_pretrained(args.model_path)
+                tokenizer.pad_token = tokenizer.eos_token
+            else:
+                output_scores = [np.concatenate((old, new), axis=1) for old, new in zip(output_scores, outputs)]
+            # append the greedy token to every suffix (main.py:84-90)
+            for idx in range(len(input_prompts)):
+                prefix, suffix = original_input_prompts[idx]
+                new_tokens = np.argmax(output_scores[idx], axis=-1)
+                input_prompts[idx] = (prefix, tuple(s + tokenizer.decode(t) for s, t in zip(suffix, new_tokens)))
+        if distributed and args.num_gen_token > 1:
+            import torch.distributed as dist
+            box = [input_prompts if is_root else None]
+            dist.broadcast_object_list(box, src=0)
+            input_prompts = box[0]
+    if is_root:
+        with open(args.prompt_pickle.replace(".pkl", "_updated.pkl"), "wb") as f:
+            pickle.dump(input_prompts, f)
+        with open(args.output_file, "wb") as f:
+            pickle.dump(output_scores, f)
+    return output_scores if is_root else None
+
+
+if __name__ == "__main__":
+    main()

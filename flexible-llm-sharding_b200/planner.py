@@ -1,0 +1,190 @@
+"""Host-side scheduling: shard plan, batching, prompt partitioning, row packing, attention tiles.
+
+Pure numpy/Python (no CUDA) so it is testable on a CPU box.  Mirrors the reference's plans:
+  shard_plan          utils.py:143-157   (np.array_split; MP rounds the shard count up to a multiple
+                                          of the GPU count and rank r takes shards r::G)
+  batch_ranges        main.py:19-20
+  partition_prompts   main.py:69-70      (np.array_split of the prompt list across GPUs)
+and adds what the packed B200 path needs: every prompt's `len_p + S*len_s` token rows are laid out
+contiguously so that one GEMM covers a whole micro-batch, with per-row rotary positions and
+per-tile attention descriptors replacing the reference's per-prompt mask/KV-expand logic
+(utils.py:219-221,275-277).
+"""
+from __future__ import annotations
+
+from dataclasses import dataclass, field
+
+import numpy as np
+
+MAX_TOKEN_LEN = 4096     # reference utils.py:14
+ATTN_TILE_Q = 64         # queries per attention tile (csrc/attention.cu BQ)
+
+
+def shard_plan(n_layers_total: int, layer_num_per_shard: int, data_parallel: bool,
+               num_gpu: int = 1, gpu_rank: int = 0) -> list[tuple[int, ...]]:
+    """Layer indices per shard for this rank; `n_layers_total` = decoder layers + 3."""
+    n_min = -(-n_layers_total // layer_num_per_shard)
+    if data_parallel:
+        n_shards = n_min
+        mine = slice(None)
+    else:
+        n_shards = -(-n_min // num_gpu) * num_gpu
+        mine = slice(gpu_rank, None, num_gpu)
+    # np.array_split semantics: the first (n % k) parts get one extra element; parts may be empty
+    base, extra = divmod(n_layers_total, n_shards)
+    shards, start = [], 0
+    for i in range(n_shards):
+        size = base + (1 if i < extra else 0)
+        shards.append(tuple(range(start, start + size)))
+        start += size
+    return shards[mine]
+
+
+def batch_ranges(n_prompts: int, num_batch: int) -> list[tuple[int, int]]:
+    ends = [n_prompts // num_batch * i for i in range(1, num_batch)] + [n_prompts]
+    return list(zip([0] + ends[:-1], ends))
+
+
+def partition_prompts(n_prompts: int, world: int) -> list[tuple[int, int]]:
+    """[start, end) of each rank's prompts, np.array_split order (main.py:69-70)."""
+    base, extra = divmod(n_prompts, world)
+    out, start = [], 0
+    for r in range(world):
+        size = base + (1 if r < extra else 0)
+        out.append((start, start + size))
+        start += size
+    return out
+
+
+@dataclass
+class TokenizedPrompt:
+    prefix_ids: np.ndarray   # [len_p] int32, BOS first
+    suffix_ids: np.ndarray   # [S, len_s] int32, BOS stripped, right-padded with pad(=eos)
+    suffix_eos: np.ndarray   # [S] index of the last non-pad token (may be -1: wraps like torch indexing)
+
+    @property
+    def len_p(self): return int(self.prefix_ids.shape[0])
+    @property
+    def n_options(self): return int(self.suffix_ids.shape[0])
+    @property
+    def len_s(self): return int(self.suffix_ids.shape[1])
+    @property
+    def rows(self): return self.len_p + self.n_options * self.len_s
+
+
+def tokenize_prompts(tokenizer, prompts) -> list[TokenizedPrompt]:
+    """utils.py:246-258 for every prompt up front (the reference tokenises inside the GPU loop)."""
+    out = []
+    pad = tokenizer.pad_token_id
+    for prefix, suffixes in prompts:
+        p = tokenizer(prefix, return_tensors="np", return_attention_mask=False, truncation=True,
+                      max_length=MAX_TOKEN_LEN)["input_ids"][0]
+        s = tokenizer(list(suffixes), return_tensors="np", return_attention_mask=False, truncation=True,
+                      max_length=MAX_TOKEN_LEN, padding=True)["input_ids"][:, 1:]
+        eos = (s != pad).sum(1) - 1
+        out.append(TokenizedPrompt(np.ascontiguousarray(p, dtype=np.int32),
+                                   np.ascontiguousarray(s, dtype=np.int32), eos.astype(np.int64)))
+    return out
+
+
+@dataclass
+class MicroBatch:
+    prompt_lo: int
+    prompt_hi: int
+    row_lo: int              # first packed row (global)
+    n_rows: int
+    head_lo: int             # first scored row (global) = sum of S over earlier prompts
+    n_head: int
+    tiles: np.ndarray        # [n_tiles, 8] int32, rows relative to row_lo
+    gather: np.ndarray       # [n_head] int32 rows (relative to row_lo) of each option's last real token
+
+
+@dataclass
+class PackedPrompts:
+    ids: np.ndarray          # [total_rows] int32 token ids
+    row_pos: np.ndarray      # [total_rows] int32 rotary positions
+    prompt_row: np.ndarray   # [n_prompts + 1] first row of each prompt
+    head_row: np.ndarray     # [n_prompts + 1] first scored row of each prompt
+    shapes: list[tuple[int, int, int]]   # (len_p, S, len_s)
+    micro_batches: list[MicroBatch] = field(default_factory=list)
+
+    @property
+    def total_rows(self): return int(self.prompt_row[-1])
+    @property
+    def total_head_rows(self): return int(self.head_row[-1])
+
+
+def prompt_tiles(base: int, len_p: int, S: int, len_s: int, prefix_causal: bool) -> list[list[int]]:
+    t = []
+    for q0 in range(0, len_p, ATTN_TILE_Q):
+        t.append([base + q0, min(ATTN_TILE_Q, len_p - q0), q0, int(prefix_causal), base, len_p, 0, 0])
+    for s in range(S):
+        srow = base + len_p + s * len_s
+        for j0 in range(0, len_s, ATTN_TILE_Q):
+            t.append([srow + j0, min(ATTN_TILE_Q, len_s - j0), len_p + j0, 1, base, len_p, srow, len_s])
+    return t
+
+
+def pack_prompts(tok: list[TokenizedPrompt], max_rows: int, max_head_rows: int,
+                 prefix_causal: bool = False) -> PackedPrompts:
+    n = len(tok)
+    prompt_row = np.zeros(n + 1, dtype=np.int64)
+    head_row = np.zeros(n + 1, dtype=np.int64)
+    for i, t in enumerate(tok):
+        if t.len_p + t.len_s > MAX_TOKEN_LEN:
+            # the reference would fail slicing its 4096^2 mask (utils.py:276)
+            raise ValueError(f"prompt {i}: prefix + option length {t.len_p + t.len_s} exceeds {MAX_TOKEN_LEN}")
+        if t.rows > max_rows:
+            raise ValueError(f"prompt {i} has {t.rows} token rows; raise max_rows (currently {max_rows})")
+        if t.len_s == 0:
+            raise ValueError(f"prompt {i}: every option is empty")
+        prompt_row[i + 1] = prompt_row[i] + t.rows
+        head_row[i + 1] = head_row[i] + t.n_options
+    total = int(prompt_row[-1])
+    ids = np.empty(total, dtype=np.int32)
+    row_pos = np.empty(total, dtype=np.int32)
+    shapes = []
+    for i, t in enumerate(tok):
+        b = int(prompt_row[i])
+        ids[b:b + t.len_p] = t.prefix_ids
+        row_pos[b:b + t.len_p] = np.arange(t.len_p)
+        so = b + t.len_p
+        ids[so:so + t.n_options * t.len_s] = t.suffix_ids.reshape(-1)
+        row_pos[so:so + t.n_options * t.len_s] = np.tile(np.arange(t.len_p, t.len_p + t.len_s), t.n_options)
+        shapes.append((t.len_p, t.n_options, t.len_s))
+    packed = PackedPrompts(ids, row_pos, prompt_row, head_row, shapes)
+
+    lo = 0
+    while lo < n:
+        hi = lo
+        while hi < n and (prompt_row[hi + 1] - prompt_row[lo] <= max_rows
+                          and head_row[hi + 1] - head_row[lo] <= max_head_rows):
+            hi += 1
+        if hi == lo:
+            raise ValueError(f"prompt {lo} does not fit a micro-batch (max_rows {max_rows}, max_head_rows {max_head_rows})")
+        row_lo = int(prompt_row[lo])
+        tiles, gather = [], []
+        for i in range(lo, hi):
+            len_p, S, len_s = shapes[i]
+            base = int(prompt_row[i]) - row_lo
+            tiles += prompt_tiles(base, len_p, S, len_s, prefix_causal)
+            for s in range(S):
+                e = int(tok[i].suffix_eos[s])
+                if e < 0:
+                    e += len_s          # torch negative indexing at utils.py:286
+                gather.append(base + len_p + s * len_s + e)
+        packed.micro_batches.append(MicroBatch(
+            lo, hi, row_lo, int(prompt_row[hi]) - row_lo, int(head_row[lo]), int(head_row[hi] - head_row[lo]),
+            np.asarray(tiles, dtype=np.int32).reshape(-1, 8), np.asarray(gather, dtype=np.int32)))
+        lo = hi
+    return packed
+
+
+def rope_tables(n_pos: int, head_dim: int, theta: float = 10000.0):
+    """fp16(cos), fp16(sin) [n_pos, head_dim], built the way the reference's rotary buffers are
+    (transformers 4.3x `_set_cos_sin_cache` in fp32, cast to fp16 by utils.py:117-119)."""
+    import torch
+    inv_freq = 1.0 / (theta ** (torch.arange(0, head_dim, 2, dtype=torch.int64).to(torch.float32) / head_dim))
+    freqs = torch.arange(n_pos, dtype=torch.int64).to(torch.float32)[:, None] * inv_freq[None, :]
+    emb = torch.cat((freqs, freqs), dim=-1)
+    return emb.cos().to(torch.float16).contiguous(), emb.sin().to(torch.float16).contiguous()

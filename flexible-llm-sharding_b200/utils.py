@@ -1,0 +1,284 @@
+"""DeviceManager and ShardedLlama - same names, constructor arguments and call convention as the
+reference's `utils.py` (reference utils.py:24-75 and :78-305), re-built for B200.
+
+What stays: `ShardedLlama(args, device_manager, device="cuda:0", dtype=torch.float16)`;
+`model(inputs)` takes a list of `(prefix, (suffix, ...))`, sets every consumed entry of `inputs`
+to None (utils.py:259) and returns one `np.ndarray [n_suffixes, 1, vocab]` of float16 next-token
+probabilities per prompt (utils.py:289-290), scored layer-shard by layer-shard.
+
+What changes: all prompts are tokenised up front and packed into one row matrix;
+each shard is streamed from pinned host memory into one of two HBM slots on a copy stream while the
+previous shard computes; every layer runs as hand-written sm_100a kernels behind the C ABI
+(`include/fls_b200.h`); activations stay in HBM when they fit.  There is no CPU path.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import json
+import os
+import threading
+from collections import defaultdict
+from time import perf_counter
+
+import numpy as np
+import torch
+
+from . import _lib, planner
+from .activation_store import ActivationStore
+
+max_token_len = planner.MAX_TOKEN_LEN  # reference utils.py:14
+
+
+def clean_memory():
+    """Kept for API compatibility (reference utils.py:18-21).  Nothing to do: weight slots and
+    workspace are allocated once per context instead of per shard."""
+    return None
+
+
+class DeviceManager:
+    """Shared state of the per-GPU workers of one process (reference utils.py:24-75).
+
+    data_parallel: the reference keeps at most `max_layer_num` layer state-dicts in host RAM and
+    hands the same dict to every GPU thread.  Here that cache lives inside the C library (one
+    pinned image per layer file per process, `csrc/host_cache.cpp`); `send_device_request`
+    pre-loads a layer file into it and `get_state_dict` exposes the tensors for inspection.
+    model parallel: `shared_activation_dict`, `prompt2layer` and `suffix_eos` are the hand-off
+    state between pipeline stages, as in the reference (utils.py:42-44,157).
+    """
+
+    def __init__(self, args, devices, max_layer_num=1):
+        assert max_layer_num >= 1, "Must set max_layer_num >= 1 to allow loading a layer"
+        self.args = args
+        self.devices = list(devices)
+        self.max_layer_num = max_layer_num
+        self.lock = threading.Lock()
+        self.condition = threading.Condition()
+        self.waiting_queue = []
+        # model-parallel hand-off state
+        self.shared_activation_dict = dict()
+        self.prompt2layer = defaultdict(lambda: -1)
+        self.suffix_eos = []
+        self.handoff = {}          # (batch_serial, micro_batch, layer_idx) -> (tensor, event)
+        self.batch_serial = defaultdict(int)
+
+    def send_device_request(self, device, layer):
+        """Ask for `layer` to be resident in host memory (pinned)."""
+        path = f"{self.args.model_path}/{layer}.safetensors"
+        with self.lock:
+            if layer not in self.waiting_queue:
+                self.waiting_queue.append(layer)
+        rc = _lib.load().fls_preload_layer_file(path.encode())
+        with self.lock:
+            if layer in self.waiting_queue:
+                self.waiting_queue.remove(layer)
+        if rc != 0:
+            raise _lib.FlsError(rc, _lib.load().fls_last_error(None).decode())
+
+    def get_state_dict(self, device, layer):
+        from safetensors.torch import load_file
+        return load_file(f"{self.args.model_path}/{layer}.safetensors")
+
+    def clean_waiting_queue(self):
+        _lib.load().fls_trim_host_cache(C.c_size_t(0))
+
+
+class ShardedLlama:
+    def __init__(self, args, device_manager, device="cuda:0", dtype=torch.float16):
+        if dtype != torch.float16:
+            raise ValueError("the B200 path computes in fp16 like the reference's default (utils.py:80)")
+        if not torch.cuda.is_available():
+            raise RuntimeError("ShardedLlama needs a CUDA device: there is no CPU fallback")
+        self.args = args
+        self.device = device
+        self.torch_device = torch.device(device)
+        self.dtype = dtype
+        self.device_manager = device_manager
+
+        with open(os.path.join(args.model_path, "config.json")) as f:
+            self.config = json.load(f)
+        from transformers import AutoTokenizer
+        self.tokenizer = AutoTokenizer.from_pretrained(args.model_path)
+        self.tokenizer.pad_token = self.tokenizer.eos_token      # utils.py:103
+        self.tokenizer.padding_side = "right"                    # utils.py:104
+        cfg = self.config
+        L = cfg["num_hidden_layers"]
+        self.layer_names = ["model.embed_tokens"] + [f"model.layers.{i}" for i in range(L)] + ["model.norm", "lm_head"]
+        self.layer_kinds = [_lib.LAYER_EMBED] + [_lib.LAYER_DECODER] * L + [_lib.LAYER_NORM, _lib.LAYER_HEAD]
+
+        # extras with reference-compatible defaults (not CLI flags in the reference)
+        self.prefix_causal = bool(getattr(args, "prefix_causal", False))     # False = reference (utils.py:272)
+        self.max_rows = int(getattr(args, "max_rows", 16384))
+        self.max_head_rows = int(getattr(args, "max_head_rows", 4096))
+        self.force_tier = bool(getattr(args, "force_storage_tier", False) or os.environ.get("FLS_FORCE_STORAGE"))
+        self.hbm_activation_budget = getattr(args, "hbm_activation_budget", None)
+
+        H = cfg["hidden_size"]
+        nh = cfg["num_attention_heads"]
+        self.hidden = H
+        self.vocab = cfg["vocab_size"]
+        self.head_dim = cfg.get("head_dim") or H // nh
+        desc = _lib.ModelDesc(H, cfg["intermediate_size"], nh, cfg.get("num_key_value_heads", nh), self.head_dim,
+                              self.vocab, L, float(cfg.get("rms_norm_eps", 1e-6)))
+        idx = self.torch_device.index if self.torch_device.index is not None else 0
+        self.ctx = _lib.Context(desc, idx)
+        for i, (name, kind) in enumerate(zip(self.layer_names, self.layer_kinds)):
+            path = os.path.join(args.model_path, f"{name}.safetensors")
+            self.ctx.call("fls_register_layer_file", i, kind, path.encode(), 0)
+        self._layer_bytes = []
+        for i in range(len(self.layer_names)):
+            b = C.c_size_t()
+            self.ctx.call("fls_layer_slot_bytes", i, C.byref(b))
+            self._layer_bytes.append(b.value)
+        cos, sin = planner.rope_tables(cfg.get("max_position_embeddings", max_token_len) if
+                                       cfg.get("max_position_embeddings", max_token_len) >= max_token_len
+                                       else max_token_len, self.head_dim, float(cfg.get("rope_theta", 10000.0)))
+        self.ctx.call("fls_set_rope_table", cos.data_ptr(), sin.data_ptr(), cos.shape[0])
+        self._configured = None
+        self.last_timing = {}
+
+    # ------------------------------------------------------------------ plan
+    def _plan(self):
+        num_gpu = len(self.device_manager.devices)
+        rank = self.device_manager.devices.index(self.device)
+        dp = bool(self.args.data_parallel) or num_gpu == 1
+        shards = planner.shard_plan(len(self.layer_names), self.args.layer_num_per_shard, dp, num_gpu, rank)
+        return shards, num_gpu, rank, dp
+
+    def _configure(self, shards):
+        slot_bytes = max([sum(self._layer_bytes[i] for i in s) for s in shards if len(s)] + [256])
+        key = (slot_bytes, self.max_rows, self.max_head_rows)
+        if self._configured != key:
+            self.ctx.call("fls_configure", 2, C.c_size_t(slot_bytes), self.max_rows, self.max_head_rows)
+            self._configured = key
+
+    # ------------------------------------------------------------------ public call
+    def __call__(self, inputs):
+        """Reference-compatible scoring: list of fp16 probability arrays [S, 1, vocab]."""
+        probs, packed = self.run(inputs, want_probs=True)
+        if probs is None:
+            return []
+        out = []
+        for i in range(len(packed.shapes)):
+            lo, hi = int(packed.head_row[i]), int(packed.head_row[i + 1])
+            out.append(np.expand_dims(probs[lo:hi], axis=1))
+        return out
+
+    def score_tokens(self, inputs, answer_token_ids):
+        """B200-native extra: log-probabilities [n_prompts][S, n_ids] (fp32) of the given next-token
+        ids without materialising full-vocabulary probabilities (fused lm_head + log-softmax + gather)."""
+        ids = np.asarray(answer_token_ids, dtype=np.int32).reshape(-1)
+        lp, packed = self.run(inputs, want_probs=False, answer_ids=ids)
+        if lp is None:
+            return []
+        return [lp[int(packed.head_row[i]):int(packed.head_row[i + 1])] for i in range(len(packed.shapes))]
+
+    # ------------------------------------------------------------------ engine
+    def run(self, inputs, want_probs=True, answer_ids=None, packed=None, return_device=False):
+        shards, num_gpu, rank, dp = self._plan()
+        if not dp:
+            from .pipeline import run_model_parallel
+            return run_model_parallel(self, inputs, shards, num_gpu, rank, want_probs, answer_ids)
+        t0 = perf_counter()
+        if packed is None:
+            tok = planner.tokenize_prompts(self.tokenizer, inputs)
+            for i in range(len(inputs)):
+                inputs[i] = None                                  # utils.py:259
+            if not tok:
+                return None, None
+            packed = planner.pack_prompts(tok, self.max_rows, self.max_head_rows, self.prefix_causal)
+        t_tok = perf_counter() - t0
+        self._configure(shards)
+        dev = self.torch_device
+        H, V = self.hidden, self.vocab
+        n_layers_total = len(self.layer_names)
+        call = self.ctx.call
+        with torch.cuda.device(dev):
+            stream = torch.cuda.current_stream(dev)
+            sp = C.c_void_p(stream.cuda_stream)
+            ids_dev = torch.from_numpy(packed.ids).pin_memory().to(dev, non_blocking=True)
+            pos_dev = torch.from_numpy(packed.row_pos).pin_memory().to(dev, non_blocking=True)
+            mbs = packed.micro_batches
+            tiles_dev = [torch.from_numpy(mb.tiles).pin_memory().to(dev, non_blocking=True) for mb in mbs]
+            gather_dev = [torch.from_numpy(mb.gather).pin_memory().to(dev, non_blocking=True) for mb in mbs]
+            in_bytes = packed.ids.nbytes + packed.row_pos.nbytes + sum(mb.tiles.nbytes + mb.gather.nbytes for mb in mbs)
+            rank_tag = str(rank) if self.args.data_parallel else ""
+            store = ActivationStore(self.args.storage_location, packed, H, dev, stream,
+                                    disk_folder=getattr(self.args, "disk_folder", "./temp"), rank_tag=rank_tag,
+                                    hbm_budget_bytes=self.hbm_activation_budget, force_tier=self.force_tier)
+            n_head = packed.total_head_rows
+            probs_dev = torch.empty((n_head, V), dtype=torch.float16, device=dev) if want_probs else None
+            n_ids = 0 if answer_ids is None else int(len(answer_ids))
+            if n_ids:
+                aid = np.tile(np.asarray(answer_ids, dtype=np.int32), (n_head, 1))
+                aid_dev = torch.from_numpy(aid).pin_memory().to(dev, non_blocking=True)
+                lp_dev = torch.empty((n_head, n_ids), dtype=torch.float32, device=dev)
+            else:
+                aid_dev = lp_dev = None
+
+            live = [s for s in shards if len(s)]
+
+            def prefetch(si):
+                arr = (C.c_int32 * len(live[si]))(*live[si])
+                call("fls_prefetch_shard", si % 2, arr, len(live[si]))
+
+            if live:
+                prefetch(0)
+            for si, shard in enumerate(live):
+                slot = si % 2
+                if si + 1 < len(live):
+                    prefetch(si + 1)            # H2D of shard si+1 overlaps this shard's compute
+                call("fls_acquire_shard", slot, sp)
+                has_input = shard[0] != 0
+                tokens_in = shard[0] <= n_layers_total - 2      # input is token-stage rows (incl. norm layer)
+                for bi, mb in enumerate(mbs):
+                    if tokens_in:
+                        store.prefetch(bi + 1, has_input)
+                        x = store.fetch(bi, has_input)
+                    else:
+                        x = store.heads_view(bi)
+                    stage_tokens = tokens_in
+                    for li in shard:
+                        kind = self.layer_kinds[li]
+                        if kind == _lib.LAYER_EMBED:
+                            call("fls_embed", slot, li, ids_dev[mb.row_lo:].data_ptr(), mb.n_rows, x.data_ptr(), sp)
+                        elif kind == _lib.LAYER_DECODER:
+                            call("fls_decoder_layer", slot, li, x.data_ptr(), mb.n_rows, pos_dev[mb.row_lo:].data_ptr(),
+                                 tiles_dev[bi].data_ptr(), int(mb.tiles.shape[0]), sp)
+                        elif kind == _lib.LAYER_NORM:
+                            h = store.heads_view(bi)
+                            call("fls_final_norm", slot, li, x.data_ptr(), gather_dev[bi].data_ptr(), mb.n_head,
+                                 h.data_ptr(), sp)
+                            if stage_tokens:
+                                store.store(bi, x, keep_tokens=False)
+                            x, stage_tokens = h, False
+                        else:
+                            pd = probs_dev[mb.head_lo:].data_ptr() if want_probs else None
+                            ad = aid_dev[mb.head_lo:].data_ptr() if n_ids else None
+                            ld = lp_dev[mb.head_lo:].data_ptr() if n_ids else None
+                            call("fls_lm_head", slot, li, x.data_ptr(), mb.n_head, pd, ad, n_ids, ld, None, sp)
+                    if stage_tokens:
+                        store.store(bi, x, keep_tokens=True)
+                store.end_shard()
+                call("fls_release_shard", slot, sp)
+
+            result = None
+            out_bytes = 0
+            owns_head = any(n_layers_total - 1 in s for s in live)
+            if owns_head:
+                if return_device:
+                    result = probs_dev if want_probs else lp_dev
+                else:
+                    src = probs_dev if want_probs else lp_dev
+                    host = torch.empty(src.shape, dtype=src.dtype).pin_memory()
+                    host.copy_(src, non_blocking=True)
+                    stream.synchronize()
+                    result = host.numpy()
+                    out_bytes = host.numel() * host.element_size()
+            else:
+                stream.synchronize()
+            store.cleanup()
+            self.last_timing = dict(tokenize_s=t_tok, total_s=perf_counter() - t0, h2d_input_bytes=in_bytes,
+                                    d2h_output_bytes=out_bytes, activation_tier=store.tier,
+                                    act_h2d_bytes=store.h2d_bytes, act_d2h_bytes=store.d2h_bytes)
+            self._keepalive = (ids_dev, pos_dev, tiles_dev, gather_dev, aid_dev, store)
+        return result, packed

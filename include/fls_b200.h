@@ -1,0 +1,186 @@
+/* fls_b200 - C ABI of the B200-native layer-sharded prompt-scoring path.
+ *
+ * The reference (eyedealism/flexible-LLM-sharding) is pure Python and has no FFI of its own; this
+ * header is the boundary a maintainer binds (ctypes stub in INTEGRATION.md) to replace the hot
+ * path of `ShardedLlama.__call__` (reference utils.py:133-305).  Each entry point names the
+ * reference code it stands in for.
+ *
+ * Conventions
+ *  - plain C types only: pointers, sizes, ints.  `stream` arguments are `cudaStream_t` passed as
+ *    `void*` (NULL = the legacy default stream).  Pointers ending in `_dev` are device pointers,
+ *    `_host` host pointers.  All activations are fp16, row-major, packed token rows `[rows, width]`.
+ *  - one context per GPU; a context is used by one host thread at a time (the reference runs one
+ *    Python thread per GPU, main.py:68-73).  Different contexts may be driven concurrently; the
+ *    pinned host copies of layer files are shared between all contexts of the process
+ *    (the analogue of DeviceManager's read-once state dict, utils.py:35-41,67-75).
+ *  - every function returns 0 on success or a negative FLS_ERR_* code and never throws or exits;
+ *    `fls_last_error` returns the message of the last failure on that context (or, with a NULL
+ *    context, of the calling thread).
+ *  - the caller owns every activation / id / output buffer.  The library owns the pinned layer
+ *    images, the HBM weight slots and its workspace, all allocated in `fls_create` /
+ *    `fls_configure` / `fls_register_layer_file`; nothing is allocated by the compute calls.
+ */
+#ifndef FLS_B200_H
+#define FLS_B200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define FLS_OK 0
+#define FLS_ERR_INVALID (-1)  /* bad argument */
+#define FLS_ERR_CUDA (-2)     /* CUDA runtime / driver error (sticky for the context) */
+#define FLS_ERR_IO (-3)       /* file missing, short read, malformed safetensors header */
+#define FLS_ERR_STATE (-4)    /* call sequence error (e.g. compute on a slot that holds no such layer) */
+#define FLS_ERR_CAPACITY (-5) /* request exceeds what fls_configure reserved */
+
+typedef struct fls_ctx fls_ctx;
+
+/* Llama-2 architecture numbers = the fields of config.json the reference reads through
+ * AutoConfig (utils.py:101). */
+typedef struct fls_model_desc {
+    int32_t hidden_size;
+    int32_t intermediate_size;
+    int32_t num_attention_heads;
+    int32_t num_key_value_heads;
+    int32_t head_dim; /* 64 or 128 */
+    int32_t vocab_size;
+    int32_t num_hidden_layers;
+    float rms_norm_eps;
+} fls_model_desc;
+
+/* Kind of a layer file, in the reference's layer order (utils.py:106-107,114-115). */
+#define FLS_LAYER_EMBED 0   /* model.embed_tokens.safetensors */
+#define FLS_LAYER_DECODER 1 /* model.layers.N.safetensors */
+#define FLS_LAYER_NORM 2    /* model.norm.safetensors */
+#define FLS_LAYER_HEAD 3    /* lm_head.safetensors */
+
+/* One attention query tile (<= 64 consecutive query rows of one prompt part); built by the host
+ * scheduler.  Replaces the reference's per-prompt kv_cache expand + mask slice (utils.py:275-277).
+ * Key t of the concatenated segments (seg0 then seg1) is visible to query i of the tile iff
+ * `!causal || t <= q_seq0 + i`. */
+typedef struct fls_attn_tile {
+    int32_t q_row;    /* first query row */
+    int32_t n_q;      /* 1..64 */
+    int32_t q_seq0;   /* sequence index of the first query */
+    int32_t causal;   /* 0: all keys visible (reference prefix pass, utils.py:272); 1: causal */
+    int32_t seg0_row; /* key/value rows of the shared prefix */
+    int32_t seg0_len;
+    int32_t seg1_row; /* key/value rows of the option itself (len 0 for prefix tiles) */
+    int32_t seg1_len;
+} fls_attn_tile;
+
+typedef struct fls_stats {
+    uint64_t kernel_launches; /* kernels this context has launched */
+    uint64_t h2d_bytes;       /* weight bytes copied pinned host -> HBM slots */
+    double h2d_ms;            /* device time of those copies (copy-stream events) */
+    uint64_t file_bytes_read; /* bytes read from layer files into pinned memory (process-wide) */
+    uint64_t pinned_bytes;    /* pinned host bytes currently held (process-wide) */
+    uint64_t workspace_bytes; /* HBM held by this context (slots + workspace) */
+} fls_stats;
+
+/* ---------------------------------------------------------------------------------------------
+ * lifecycle - replaces ShardedLlama.__init__/init_model (utils.py:80-119): instead of a meta-device
+ * model rebuilt on every call (utils.py:135-137) a context is created once per GPU. */
+int fls_version(void);
+const char* fls_last_error(const fls_ctx* ctx);
+int fls_create(const fls_model_desc* desc, int device, fls_ctx** out);
+int fls_destroy(fls_ctx* ctx);
+
+/* Reserve HBM: `n_slots` weight slots of `slot_bytes` each (2 = double buffering: shard k+1 is
+ * copied while shard k computes) and workspace for micro-batches of up to `max_rows` token rows
+ * and `max_head_rows` scored rows.  May be called again to resize (frees the old reservation). */
+int fls_configure(fls_ctx* ctx, int n_slots, size_t slot_bytes, int max_rows, int max_head_rows);
+
+/* Rotary tables [n_pos, head_dim] fp16 (host pointers), built by the host exactly as the
+ * reference's rotary buffers are built and cast (utils.py:117-119): fp16(cos(fp32 pos * inv_freq)). */
+int fls_set_rope_table(fls_ctx* ctx, const uint16_t* cos_host, const uint16_t* sin_host, int n_pos);
+
+/* ---------------------------------------------------------------------------------------------
+ * weight stream - replaces load_layer_to_gpu (utils.py:121-131) and DeviceManager's DP state
+ * (utils.py:46-75): file -> pinned host image (read once per process, shared by all contexts)
+ * -> asynchronous H2D into an HBM slot on the context's copy stream. */
+
+/* Parse `<layer>.safetensors` written by prepare_weights.py (8-byte LE header length, JSON
+ * header, raw tensors) and bind it to `layer_idx`.  The file is read into pinned memory at the
+ * first prefetch that needs it (or now, if `load_now`).  F16 tensors are used as stored; BF16/F32
+ * are converted to fp16 once on load (the reference casts to fp16 too, utils.py:130); integer
+ * dtypes are rejected like utils.py:129. */
+int fls_register_layer_file(fls_ctx* ctx, int layer_idx, int kind, const char* path, int load_now);
+/* HBM bytes layer `layer_idx` needs in a slot. */
+int fls_layer_slot_bytes(fls_ctx* ctx, int layer_idx, size_t* out_bytes);
+/* Enqueue the H2D copies of `n` layers into `slot` on the copy stream.  Waits (on the device) for
+ * the slot's previous user to have released it. */
+int fls_prefetch_shard(fls_ctx* ctx, int slot, const int32_t* layer_ids, int n);
+/* Make `stream` wait until the slot's copies have landed (no host blocking). */
+int fls_acquire_shard(fls_ctx* ctx, int slot, void* stream);
+/* Mark the slot reusable once everything enqueued on `stream` so far has finished.  Replaces
+ * `layer.to("meta")` + clean_memory (utils.py:299-302). */
+int fls_release_shard(fls_ctx* ctx, int slot, void* stream);
+/* Read a layer file into the process-wide pinned cache without binding it to a context: the
+ * analogue of DeviceManager.send_device_request/clean_waiting_queue (utils.py:61-75).  Safe to call
+ * from a reader thread running ahead of the GPU loop. */
+int fls_preload_layer_file(const char* path);
+/* Drop pinned images no context needs any more (process-wide cache). */
+int fls_trim_host_cache(size_t keep_bytes);
+
+/* ---------------------------------------------------------------------------------------------
+ * layer compute on a resident shard.  `x_dev` etc. are fp16 [rows, hidden]. */
+
+/* utils.py:266-268  prefix/suffix = embed_tokens(ids), for all packed rows at once. */
+int fls_embed(fls_ctx* ctx, int slot, int layer_idx, const int32_t* ids_dev, int n_rows, uint16_t* out_dev,
+              void* stream);
+/* utils.py:269-279  one LlamaDecoderLayer over every packed row of the micro-batch, in place:
+ * RMSNorm -> QKV GEMM -> RoPE -> shared-prefix attention -> O GEMM(+residual) -> RMSNorm ->
+ * gate/up GEMM(+SwiGLU) -> down GEMM(+residual).  `row_pos_dev[r]` = rotary position of row r
+ * (0..len_p-1 for prefix rows, len_p.. for option rows, utils.py:221,275). */
+int fls_decoder_layer(fls_ctx* ctx, int slot, int layer_idx, uint16_t* x_dev, int n_rows, const int32_t* row_pos_dev,
+                      const fls_attn_tile* tiles_dev, int n_tiles, void* stream);
+/* utils.py:281-286  out[j] = norm(x[gather_dev[j]]) - the last real token of every option. */
+int fls_final_norm(fls_ctx* ctx, int slot, int layer_idx, const uint16_t* x_dev, const int32_t* gather_dev, int n_out,
+                   uint16_t* out_dev, void* stream);
+/* utils.py:287-291  softmax(lm_head(x)) without storing logits: pass 1 = GEMM with a per-tile
+ * (max, sum-exp) epilogue + reduction -> log-sum-exp per row; then, as requested,
+ *   probs_dev   [n_rows, vocab] fp16 probabilities (the reference's output format), GEMM pass 2 with
+ *               an exp(logit - lse) epilogue; may be NULL;
+ *   logprob_dev [n_rows, n_ids] fp32 log-probabilities of `answer_ids_dev[n_rows, n_ids]`; may be NULL;
+ *   lse_dev     [n_rows] fp32; may be NULL. */
+int fls_lm_head(fls_ctx* ctx, int slot, int layer_idx, const uint16_t* x_dev, int n_rows, uint16_t* probs_dev,
+                const int32_t* answer_ids_dev, int n_ids, float* logprob_dev, float* lse_dev, void* stream);
+
+/* ---------------------------------------------------------------------------------------------
+ * single kernels on caller-supplied device buffers (unit parity tests, profiling). */
+#define FLS_EPI_STORE 0
+#define FLS_EPI_RESIDUAL 1
+#define FLS_EPI_SWIGLU 2
+/* C[M,N] = A[M,K] * B[N,K]^T (+ epilogue).  SWIGLU: B holds gate rows [0,N) and up rows
+ * [up_off, up_off+N); RESIDUAL: C = R + A*B^T (R may alias C). */
+int fls_op_gemm(fls_ctx* ctx, int epilogue, const uint16_t* a_dev, int lda, const uint16_t* b_dev, int ldb, int b_rows,
+                int m, int n, int k, uint16_t* c_dev, int ldc, const uint16_t* r_dev, int ldr, int up_off,
+                void* stream);
+int fls_op_rmsnorm(fls_ctx* ctx, const uint16_t* x_dev, const uint16_t* delta_dev, const int32_t* gather_dev,
+                   const uint16_t* w_dev, float eps, int n_rows, int hidden, uint16_t* x_sum_dev, uint16_t* out_dev,
+                   void* stream);
+int fls_op_rope(fls_ctx* ctx, uint16_t* qkv_dev, int ld, int n_rows, int n_q_heads, int n_kv_heads, int head_dim,
+                const int32_t* row_pos_dev, void* stream);
+int fls_op_attention(fls_ctx* ctx, const uint16_t* qkv_dev, int ld, int n_q_heads, int n_kv_heads, int head_dim,
+                     const fls_attn_tile* tiles_dev, int n_tiles, uint16_t* out_dev, int ld_out, void* stream);
+int fls_op_swiglu(fls_ctx* ctx, const uint16_t* gate_dev, const uint16_t* up_dev, int ld_in, int n_rows, int inter,
+                  uint16_t* out_dev, int ld_out, void* stream);
+int fls_op_embed(fls_ctx* ctx, const uint16_t* table_dev, const int32_t* ids_dev, int n_rows, int hidden,
+                 uint16_t* out_dev, void* stream);
+/* softmax over [n_rows, n] given W[n, k] (lm_head without a registered layer). */
+int fls_op_head(fls_ctx* ctx, const uint16_t* x_dev, const uint16_t* w_dev, int n_rows, int n, int k,
+                uint16_t* probs_dev, const int32_t* answer_ids_dev, int n_ids, float* logprob_dev, float* lse_dev,
+                void* stream);
+
+int fls_get_stats(fls_ctx* ctx, fls_stats* out);
+int fls_reset_stats(fls_ctx* ctx);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* FLS_B200_H */

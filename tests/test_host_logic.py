@@ -1,0 +1,131 @@
+"""CPU-only checks of the host side: plans against the oracle's restatement of the reference
+(which uses numpy's own array_split), row packing invariants, and the C-ABI library's exports."""
+import ctypes
+import os
+import re
+
+import numpy as np
+import pytest
+
+from flexible_llm_sharding_b200 import planner
+from oracle import llama_oracle as O
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+@pytest.mark.parametrize("n_total", [7, 35, 43, 83])
+@pytest.mark.parametrize("k", [1, 2, 3, 4, 10])
+def test_shard_plan_matches_reference_semantics(n_total, k):
+    assert planner.shard_plan(n_total, k, True) == O.shard_plan(n_total, k, True)
+    for G in (1, 2, 4, 8):
+        seen = []
+        for r in range(G):
+            mine = planner.shard_plan(n_total, k, False, G, r)
+            assert mine == O.shard_plan(n_total, k, False, G, r)
+            seen += [i for s in mine for i in s]
+        assert sorted(seen) == list(range(n_total))        # every layer owned exactly once
+
+
+def test_batch_and_partition_match_numpy():
+    for n in (0, 1, 5, 32, 1024):
+        for b in (1, 2, 3, 7):
+            assert planner.batch_ranges(n, b) == O.batch_ranges(n, b)
+        for w in (1, 2, 3, 8):
+            parts = planner.partition_prompts(n, w)
+            want = np.array_split(np.arange(n), w)
+            assert [hi - lo for lo, hi in parts] == [len(x) for x in want]
+            assert all(lo == (x[0] if len(x) else lo) for (lo, hi), x in zip(parts, want))
+
+
+def _tok(shapes, seed=0):
+    rng = np.random.default_rng(seed)
+    out = []
+    for lp, S, ls in shapes:
+        eos = rng.integers(-1, ls, S)
+        out.append(planner.TokenizedPrompt(rng.integers(3, 100, lp).astype(np.int32),
+                                           rng.integers(3, 100, (S, ls)).astype(np.int32), eos.astype(np.int64)))
+    return out
+
+
+def test_pack_prompts_layout_and_tiles():
+    shapes = [(70, 3, 9), (1, 2, 5), (129, 4, 33), (64, 1, 64), (200, 2, 70)]
+    tok = _tok(shapes)
+    packed = planner.pack_prompts(tok, max_rows=400, max_head_rows=6, prefix_causal=False)
+    assert packed.total_rows == sum(lp + S * ls for lp, S, ls in shapes)
+    assert packed.total_head_rows == sum(S for _, S, _ in shapes)
+    # micro-batches tile the prompt list in order and respect both limits
+    assert [mb.prompt_lo for mb in packed.micro_batches][0] == 0
+    assert packed.micro_batches[-1].prompt_hi == len(shapes)
+    for a, b in zip(packed.micro_batches, packed.micro_batches[1:]):
+        assert a.prompt_hi == b.prompt_lo and a.row_lo + a.n_rows == b.row_lo
+    covered = np.zeros(packed.total_rows, dtype=int)
+    for mb in packed.micro_batches:
+        assert mb.n_rows <= 400 and mb.n_head <= 6
+        for q_row, n_q, q_seq0, causal, s0r, s0l, s1r, s1l in mb.tiles:
+            assert 1 <= n_q <= planner.ATTN_TILE_Q
+            covered[mb.row_lo + q_row: mb.row_lo + q_row + n_q] += 1
+            # rotary position of a query == its sequence index used for the causal rule
+            assert packed.row_pos[mb.row_lo + q_row] == q_seq0
+            if s1l:      # option tile: causal, own rows follow the prefix in sequence order
+                assert causal == 1 and q_seq0 >= s0l and s1r <= q_row < s1r + s1l
+            else:
+                assert causal == 0 and s0r <= q_row < s0r + s0l
+        for j, g in enumerate(mb.gather):
+            assert 0 <= g < mb.n_rows
+    assert (covered == 1).all()                              # every row is a query exactly once
+    # gather picks suffix[arange(S), eos] with python negative-index wrap (utils.py:286)
+    mb0 = packed.micro_batches[0]
+    lp, S, ls = shapes[0]
+    for s in range(S):
+        e = int(tok[0].suffix_eos[s]) % ls
+        assert mb0.gather[s] == lp + s * ls + e
+    with pytest.raises(ValueError):
+        planner.pack_prompts(tok, max_rows=100, max_head_rows=6)
+    with pytest.raises(ValueError):
+        planner.pack_prompts(_tok([(4000, 1, 200)]), max_rows=10000, max_head_rows=6)     # > 4096 (utils.py:276)
+
+
+def test_rope_table_matches_oracle():
+    import torch
+    cos, sin = planner.rope_tables(300, 128)
+    c2, s2 = O.rope_cos_sin(torch.arange(300), 128, 10000.0, torch.float16)
+    assert torch.equal(cos, c2) and torch.equal(sin, s2)
+
+
+def test_tokenize_matches_oracle(tiny):
+    from transformers import AutoTokenizer
+    tok = AutoTokenizer.from_pretrained(tiny["layer_dir"])
+    tok.pad_token = tok.eos_token
+    tok.padding_side = "right"
+    got = planner.tokenize_prompts(tok, tiny["prompts"])
+    for g, (pre, suf) in zip(got, tiny["prompts"]):
+        p, s, e = O.tokenize_prompt(tok, pre, suf)
+        assert g.prefix_ids.tolist() == p[0].tolist() and g.suffix_ids.tolist() == s.tolist()
+        assert g.suffix_eos.tolist() == e.tolist()
+
+
+def test_cabi_library_exports_every_declared_symbol():
+    """No compute: the library must load on a CPU box and export exactly what the header declares."""
+    import __graft_entry__ as ge
+    from flexible_llm_sharding_b200 import _lib
+    ge.build()
+    header = open(os.path.join(ROOT, "include", "fls_b200.h")).read()
+    header = re.sub(r"/\*.*?\*/", "", header, flags=re.S)
+    declared = sorted(set(re.findall(r"\b(fls_[a-z0-9_]+)\s*\(", header)))
+    assert len(declared) >= 20
+    lib = ctypes.CDLL(_lib.LIB_PATH)
+    for name in declared:
+        assert hasattr(lib, name), f"{name} is declared in include/fls_b200.h but not exported"
+    assert sorted(_lib.exported_symbols()) == declared       # the ctypes binding covers the whole header
+    assert lib.fls_version() == 1
+    typed = _lib.load()
+    assert typed.fls_preload_layer_file(b"/nonexistent.safetensors") == -3
+    assert b"cannot open" in typed.fls_last_error(None)
+
+
+def test_safetensors_header_parse_rejects_garbage(tmp_path):
+    from flexible_llm_sharding_b200 import _lib
+    bad = tmp_path / "bad.safetensors"
+    bad.write_bytes(b"\x10\x00\x00\x00\x00\x00\x00\x00{not json.......")
+    lib = _lib.load()
+    assert lib.fls_preload_layer_file(str(bad).encode()) == -3
