@@ -56,6 +56,12 @@ class Stats(C.Structure):
                 ("file_bytes_read", C.c_uint64), ("pinned_bytes", C.c_uint64), ("workspace_bytes", C.c_uint64)]
 
 
+class KernelProfile(C.Structure):
+    _fields_ = [("ms", C.c_double), ("work", C.c_double), ("launches", C.c_uint64)]
+
+
+PROF_CLASSES = ["gemm_qkv", "gemm_o", "gemm_gate_up", "gemm_down", "gemm_head", "attention", "rmsnorm", "rope",
+                "embed", "other"]
 LAYER_EMBED, LAYER_DECODER, LAYER_NORM, LAYER_HEAD = 0, 1, 2, 3
 EPI_STORE, EPI_RESIDUAL, EPI_SWIGLU = 0, 1, 2
 ATTN_TILE_INTS = 8  # sizeof(fls_attn_tile) / 4
@@ -88,6 +94,8 @@ _SIGNATURES = {
     "fls_op_swiglu": (_I, [_P, _P, _P, _I, _I, _I, _P, _I, _P]),
     "fls_op_embed": (_I, [_P, _P, _P, _I, _I, _P, _P]),
     "fls_op_head": (_I, [_P, _P, _P, _I, _I, _I, _P, _P, _I, _P, _P, _P]),
+    "fls_set_profiling": (_I, [_P, _I]),
+    "fls_get_profile": (_I, [_P, _P]),
     "fls_get_stats": (_I, [_P, C.POINTER(Stats)]),
     "fls_reset_stats": (_I, [_P]),
 }
@@ -137,6 +145,12 @@ class Context:
         s = Stats()
         self.call("fls_get_stats", C.byref(s))
         return s
+
+    def profile(self) -> dict:
+        arr = (KernelProfile * len(PROF_CLASSES))()
+        self.call("fls_get_profile", C.cast(arr, _P))
+        return {n: dict(ms=arr[i].ms, work=arr[i].work, launches=int(arr[i].launches))
+                for i, n in enumerate(PROF_CLASSES)}
 
     def close(self):
         if self._h:

@@ -75,6 +75,16 @@ struct fls_ctx {
     int rope_n_pos = 0;
     size_t workspace_bytes = 0;
     fls_stats stats{};
+    // per-kernel event profiling
+    bool profiling = false;
+    struct ProfSlot {
+        cudaEvent_t a = nullptr, b = nullptr;
+        int cls = 0;
+        bool pending = false;
+    };
+    std::vector<ProfSlot> prof_ring;
+    size_t prof_next = 0;
+    fls_kernel_profile prof[FLS_PROF_CLASSES] = {};
     char err[512] = {0};
     bool cuda_poisoned = false;
 };
@@ -179,6 +189,47 @@ const ResidentLayer* find_resident(fls_ctx* c, int slot, int layer_idx, int kind
     return nullptr;
 }
 
+void prof_harvest(fls_ctx* c, fls_ctx::ProfSlot& p, bool wait) {
+    if (!p.pending) return;
+    if (wait) cudaEventSynchronize(p.b);
+    float ms = 0.f;
+    if (cudaEventElapsedTime(&ms, p.a, p.b) == cudaSuccess) {
+        c->prof[p.cls].ms += ms;
+        p.pending = false;
+    } else {
+        cudaGetLastError();
+    }
+}
+
+// Brackets one launch with events on its stream when profiling is on.
+struct ProfScope {
+    fls_ctx* c;
+    fls_ctx::ProfSlot* slot = nullptr;
+    cudaStream_t st;
+    ProfScope(fls_ctx* ctx, int cls, double work, cudaStream_t stream) : c(ctx), st(stream) {
+        if (!c->profiling) return;
+        if (c->prof_ring.empty()) {
+            c->prof_ring.resize(4096);
+            for (auto& p : c->prof_ring) {
+                cudaEventCreate(&p.a);
+                cudaEventCreate(&p.b);
+            }
+        }
+        slot = &c->prof_ring[c->prof_next++ % c->prof_ring.size()];
+        prof_harvest(c, *slot, true);
+        slot->cls = cls;
+        c->prof[cls].work += work;
+        c->prof[cls].launches += 1;
+        cudaEventRecord(slot->a, st);
+    }
+    ~ProfScope() {
+        if (slot) {
+            cudaEventRecord(slot->b, st);
+            slot->pending = true;
+        }
+    }
+};
+
 inline cudaStream_t as_stream(void* s) { return reinterpret_cast<cudaStream_t>(s); }
 inline const __half* H(const uint16_t* p) { return reinterpret_cast<const __half*>(p); }
 inline __half* H(uint16_t* p) { return reinterpret_cast<__half*>(p); }
@@ -192,15 +243,24 @@ int head_impl(fls_ctx* c, const __half* x, const __half* W, int n_rows, int V, i
     GemmArgs a{};
     a.A = x, a.lda = K, a.B = W, a.ldb = K, a.b_rows = V, a.M = n_rows, a.N = V, a.K = K;
     a.partial = c->lse_partial;
-    FLS_TRY(gemm_launch(kEpiLsePartial, a, c->num_sms, st));
-    FLS_TRY(lse_reduce_launch(c->lse_partial, n_rows, gemm_lse_blocks(V), c->lse, st));
+    const double flops = 2.0 * n_rows * V * K;
+    {
+        ProfScope ps(c, FLS_PROF_GEMM_HEAD, flops, st);
+        FLS_TRY(gemm_launch(kEpiLsePartial, a, c->num_sms, st));
+    }
+    {
+        ProfScope ps(c, FLS_PROF_OTHER, 0, st);
+        FLS_TRY(lse_reduce_launch(c->lse_partial, n_rows, gemm_lse_blocks(V), c->lse, st));
+    }
     c->stats.kernel_launches += 2;
     if (probs) {
         a.C = probs, a.ldc = V, a.lse = c->lse;
+        ProfScope ps(c, FLS_PROF_GEMM_HEAD, flops, st);
         FLS_TRY(gemm_launch(kEpiProbs, a, c->num_sms, st));
         c->stats.kernel_launches += 1;
     }
     if (logprob && n_ids > 0) {
+        ProfScope ps(c, FLS_PROF_OTHER, 0, st);
         FLS_TRY(gather_logprob_launch(x, K, W, K, K, answer_ids, n_ids, c->lse, n_rows, logprob, st));
         c->stats.kernel_launches += 1;
     }
@@ -258,6 +318,10 @@ int fls_destroy(fls_ctx* c) {
     if (c->rope_cos) cudaFree(c->rope_cos);
     if (c->rope_sin) cudaFree(c->rope_sin);
     if (c->copy_stream) cudaStreamDestroy(c->copy_stream);
+    for (auto& p : c->prof_ring) {
+        cudaEventDestroy(p.a);
+        cudaEventDestroy(p.b);
+    }
     delete c;
     return kOk;
 }
@@ -463,7 +527,10 @@ int fls_embed(fls_ctx* c, int slot, int layer_idx, const int32_t* ids, int n_row
     ENTER(c);
     const ResidentLayer* r = find_resident(c, slot, layer_idx, FLS_LAYER_EMBED);
     if (!r) return ctx_fail(c, kErrState);
-    CTX_TRY(c, embed_launch(r->single, ids, n_rows, c->m.hidden_size, H(out), as_stream(stream)));
+    {
+        ProfScope ps(c, FLS_PROF_EMBED, static_cast<double>(n_rows) * c->m.hidden_size * 4.0, as_stream(stream));
+        CTX_TRY(c, embed_launch(r->single, ids, n_rows, c->m.hidden_size, H(out), as_stream(stream)));
+    }
     c->stats.kernel_launches += 1;
     return kOk;
 }
@@ -484,31 +551,57 @@ int fls_decoder_layer(fls_ctx* c, int slot, int layer_idx, uint16_t* x_dev, int 
     __half* x = H(x_dev);
     static_assert(sizeof(fls_attn_tile) == sizeof(AttnTile), "tile layouts must match");
 
+    const double R = n_rows;
+    const double norm_bytes = R * Hd * 4 + Hd * 2.0;
     // hidden = x + o_proj(attn(rope(qkv(norm(x)))))
-    CTX_TRY(c, rmsnorm_launch(x, nullptr, nullptr, r->dec.ln1, m.rms_norm_eps, n_rows, Hd, nullptr, c->xn, st));
+    {
+        ProfScope ps(c, FLS_PROF_RMSNORM, norm_bytes, st);
+        CTX_TRY(c, rmsnorm_launch(x, nullptr, nullptr, r->dec.ln1, m.rms_norm_eps, n_rows, Hd, nullptr, c->xn, st));
+    }
     GemmArgs a{};
     a.A = c->xn, a.lda = Hd, a.B = r->dec.wqkv, a.ldb = Hd, a.b_rows = c->qkv_dim;
     a.M = n_rows, a.N = c->qkv_dim, a.K = Hd, a.C = c->qkv, a.ldc = c->qkv_dim;
-    CTX_TRY(c, gemm_launch(kEpiStore, a, c->num_sms, st));
-    CTX_TRY(c, rope_launch(c->qkv, c->qkv_dim, n_rows, m.num_attention_heads, m.num_key_value_heads, m.head_dim,
-                           row_pos, c->rope_cos, c->rope_sin, c->rope_n_pos, st));
-    CTX_TRY(c, attention_launch(c->qkv, c->qkv_dim, m.num_attention_heads, m.num_key_value_heads, m.head_dim,
-                                reinterpret_cast<const AttnTile*>(tiles), n_tiles, c->attn, c->q_dim, st));
+    {
+        ProfScope ps(c, FLS_PROF_GEMM_QKV, 2.0 * R * c->qkv_dim * Hd, st);
+        CTX_TRY(c, gemm_launch(kEpiStore, a, c->num_sms, st));
+    }
+    {
+        ProfScope ps(c, FLS_PROF_ROPE, R * (c->q_dim + c->kv_dim) * 4.0, st);
+        CTX_TRY(c, rope_launch(c->qkv, c->qkv_dim, n_rows, m.num_attention_heads, m.num_key_value_heads, m.head_dim,
+                               row_pos, c->rope_cos, c->rope_sin, c->rope_n_pos, st));
+    }
+    {
+        ProfScope ps(c, FLS_PROF_ATTENTION, 0, st);
+        CTX_TRY(c, attention_launch(c->qkv, c->qkv_dim, m.num_attention_heads, m.num_key_value_heads, m.head_dim,
+                                    reinterpret_cast<const AttnTile*>(tiles), n_tiles, c->attn, c->q_dim, st));
+    }
     a = GemmArgs{};
     a.A = c->attn, a.lda = c->q_dim, a.B = r->dec.wo, a.ldb = c->q_dim, a.b_rows = Hd;
     a.M = n_rows, a.N = Hd, a.K = c->q_dim, a.C = x, a.ldc = Hd, a.R = x, a.ldr = Hd;
-    CTX_TRY(c, gemm_launch(kEpiResidual, a, c->num_sms, st));
+    {
+        ProfScope ps(c, FLS_PROF_GEMM_O, 2.0 * R * Hd * c->q_dim, st);
+        CTX_TRY(c, gemm_launch(kEpiResidual, a, c->num_sms, st));
+    }
 
     // hidden = hidden + down_proj(silu(gate_proj(norm(hidden))) * up_proj(norm(hidden)))
-    CTX_TRY(c, rmsnorm_launch(x, nullptr, nullptr, r->dec.ln2, m.rms_norm_eps, n_rows, Hd, nullptr, c->xn, st));
+    {
+        ProfScope ps(c, FLS_PROF_RMSNORM, norm_bytes, st);
+        CTX_TRY(c, rmsnorm_launch(x, nullptr, nullptr, r->dec.ln2, m.rms_norm_eps, n_rows, Hd, nullptr, c->xn, st));
+    }
     a = GemmArgs{};
     a.A = c->xn, a.lda = Hd, a.B = r->dec.wgu, a.ldb = Hd, a.b_rows = 2 * I;
     a.M = n_rows, a.N = I, a.K = Hd, a.C = c->hmid, a.ldc = I, a.up_off = I;
-    CTX_TRY(c, gemm_launch(kEpiSwiGLU, a, c->num_sms, st));
+    {
+        ProfScope ps(c, FLS_PROF_GEMM_GATE_UP, 2.0 * R * (2.0 * I) * Hd, st);
+        CTX_TRY(c, gemm_launch(kEpiSwiGLU, a, c->num_sms, st));
+    }
     a = GemmArgs{};
     a.A = c->hmid, a.lda = I, a.B = r->dec.wd, a.ldb = I, a.b_rows = Hd;
     a.M = n_rows, a.N = Hd, a.K = I, a.C = x, a.ldc = Hd, a.R = x, a.ldr = Hd;
-    CTX_TRY(c, gemm_launch(kEpiResidual, a, c->num_sms, st));
+    {
+        ProfScope ps(c, FLS_PROF_GEMM_DOWN, 2.0 * R * Hd * I, st);
+        CTX_TRY(c, gemm_launch(kEpiResidual, a, c->num_sms, st));
+    }
     c->stats.kernel_launches += 8;
     return kOk;
 }
@@ -518,8 +611,11 @@ int fls_final_norm(fls_ctx* c, int slot, int layer_idx, const uint16_t* x, const
     ENTER(c);
     const ResidentLayer* r = find_resident(c, slot, layer_idx, FLS_LAYER_NORM);
     if (!r) return ctx_fail(c, kErrState);
-    CTX_TRY(c, rmsnorm_launch(H(x), nullptr, gather, r->single, c->m.rms_norm_eps, n_out, c->m.hidden_size, nullptr,
-                              H(out), as_stream(stream)));
+    {
+        ProfScope ps(c, FLS_PROF_RMSNORM, static_cast<double>(n_out) * c->m.hidden_size * 4.0, as_stream(stream));
+        CTX_TRY(c, rmsnorm_launch(H(x), nullptr, gather, r->single, c->m.rms_norm_eps, n_out, c->m.hidden_size,
+                                  nullptr, H(out), as_stream(stream)));
+    }
     c->stats.kernel_launches += 1;
     return kOk;
 }
@@ -603,6 +699,20 @@ int fls_op_head(fls_ctx* c, const uint16_t* x, const uint16_t* w, int n_rows, in
     return kOk;
 }
 
+int fls_set_profiling(fls_ctx* c, int enabled) {
+    if (!c) return fail(kErrInvalid, "fls_set_profiling: null context");
+    c->profiling = enabled != 0;
+    return kOk;
+}
+
+int fls_get_profile(fls_ctx* c, fls_kernel_profile* out) {
+    ENTER(c);
+    if (!out) return ctx_fail(c, fail(kErrInvalid, "fls_get_profile: null output"));
+    for (auto& p : c->prof_ring) prof_harvest(c, p, true);
+    for (int i = 0; i < FLS_PROF_CLASSES; ++i) out[i] = c->prof[i];
+    return kOk;
+}
+
 int fls_get_stats(fls_ctx* c, fls_stats* out) {
     if (!c || !out) return fail(kErrInvalid, "fls_get_stats: null argument");
     cudaSetDevice(c->device);
@@ -617,6 +727,8 @@ int fls_get_stats(fls_ctx* c, fls_stats* out) {
 int fls_reset_stats(fls_ctx* c) {
     if (!c) return fail(kErrInvalid, "fls_reset_stats: null context");
     c->stats = fls_stats{};
+    for (auto& p : c->prof_ring) p.pending = false;
+    for (auto& p : c->prof) p = fls_kernel_profile{};
     return kOk;
 }
 

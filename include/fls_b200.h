@@ -177,6 +177,29 @@ int fls_op_head(fls_ctx* ctx, const uint16_t* x_dev, const uint16_t* w_dev, int 
                 uint16_t* probs_dev, const int32_t* answer_ids_dev, int n_ids, float* logprob_dev, float* lse_dev,
                 void* stream);
 
+/* Per-kernel device timing (CUDA events recorded around every launch on the caller's stream while
+ * profiling is on; a few microseconds per launch).  The reference's only instrumentation is a
+ * wall-clock sum of weight-loading time (utils.py:223,230-233,304). */
+#define FLS_PROF_GEMM_QKV 0
+#define FLS_PROF_GEMM_O 1
+#define FLS_PROF_GEMM_GATE_UP 2
+#define FLS_PROF_GEMM_DOWN 3
+#define FLS_PROF_GEMM_HEAD 4
+#define FLS_PROF_ATTENTION 5
+#define FLS_PROF_RMSNORM 6
+#define FLS_PROF_ROPE 7
+#define FLS_PROF_EMBED 8
+#define FLS_PROF_OTHER 9
+#define FLS_PROF_CLASSES 10
+typedef struct fls_kernel_profile {
+    double ms;         /* summed device time of the class */
+    double work;       /* algorithmic FLOPs (GEMM classes: 2*M*N*K) or bytes (HBM-bound classes) */
+    uint64_t launches;
+} fls_kernel_profile;
+int fls_set_profiling(fls_ctx* ctx, int enabled);
+/* Waits for the profiled launches to finish, then fills out[0..FLS_PROF_CLASSES). */
+int fls_get_profile(fls_ctx* ctx, fls_kernel_profile* out);
+
 int fls_get_stats(fls_ctx* ctx, fls_stats* out);
 int fls_reset_stats(fls_ctx* ctx);
 

@@ -210,8 +210,10 @@ def test_head_softmax_and_logprob(env, rows, V, K):
     logits = (x.float() @ w.float().t()).half()                 # lm_head output as the reference holds it
     want = torch.softmax(logits.float(), dim=-1)
     # probabilities: relative error of one fp16 rounding (2^-11) + a logit that rounded to its fp16 neighbour
-    rel = ((probs.float() - want).abs() / want.clamp_min(1e-7))[want > 1e-6].max().item()
+    # (checked on fp16-normal outputs; below 6.1e-5 fp16 is subnormal with absolute steps of 6e-8)
+    rel = ((probs.float() - want).abs() / want.clamp_min(1e-7))[want > 1e-4].max().item()
     assert rel <= 2e-2, rel
+    assert (probs.float() - want).abs()[want <= 1e-4].max().item() <= 2e-6
     assert abs(probs.float().sum(-1) - 1).max().item() <= 2e-3
     want_lse = torch.logsumexp(logits.float(), dim=-1)
     assert (lse - want_lse).abs().max().item() <= 2e-3
