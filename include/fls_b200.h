@@ -177,6 +177,25 @@ int fls_op_head(fls_ctx* ctx, const uint16_t* x_dev, const uint16_t* w_dev, int 
                 uint16_t* probs_dev, const int32_t* answer_ids_dev, int n_ids, float* logprob_dev, float* lse_dev,
                 void* stream);
 
+/* No counterpart in the reference.  The same computation as fls_op_head for callers that cannot
+ * allocate device memory: a plugin inside a serving process whose own pool already owns all of HBM,
+ * or a latency-critical thread that cannot afford cudaMalloc's device-wide synchronisation.  It
+ * takes no context and calls no cudaMalloc/cudaFree: its scratch (the per-tile softmax partials and
+ * the per-row log-sum-exp) is a fixed ~1 MiB array inside the library image, held by every GPU
+ * that loads the library until the process exits.
+ *  - limit: n_rows <= FLS_NOALLOC_MAX_ROWS and n <= FLS_NOALLOC_MAX_VOCAB per call, otherwise
+ *    FLS_ERR_CAPACITY (split the rows over several calls, or use fls_op_head);
+ *  - runs on the current device; the first call on a device resolves the array's address - make it
+ *    before any stream capture begins;
+ *  - all calls on a device share that array: calls whose kernels overlap on the GPU race, so keep
+ *    them on one stream or order them.  Nothing in the array needs clearing between calls (each
+ *    call writes every entry it reads).
+ * Inputs/outputs are the caller's buffers, as in fls_op_head; errors via fls_last_error(NULL). */
+#define FLS_NOALLOC_MAX_ROWS 1024
+#define FLS_NOALLOC_MAX_VOCAB 32768
+int fls_op_head_noalloc(const uint16_t* x_dev, const uint16_t* w_dev, int n_rows, int n, int k, uint16_t* probs_dev,
+                        const int32_t* answer_ids_dev, int n_ids, float* logprob_dev, float* lse_dev, void* stream);
+
 /* Per-kernel device timing (CUDA events recorded around every launch on the caller's stream while
  * profiling is on; a few microseconds per launch).  The reference's only instrumentation is a
  * wall-clock sum of weight-loading time (utils.py:223,230-233,304). */
