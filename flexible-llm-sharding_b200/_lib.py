@@ -53,7 +53,8 @@ class ModelDesc(C.Structure):
 
 class Stats(C.Structure):
     _fields_ = [("kernel_launches", C.c_uint64), ("h2d_bytes", C.c_uint64), ("h2d_ms", C.c_double),
-                ("file_bytes_read", C.c_uint64), ("pinned_bytes", C.c_uint64), ("workspace_bytes", C.c_uint64)]
+                ("file_bytes_read", C.c_uint64), ("pinned_bytes", C.c_uint64), ("workspace_bytes", C.c_uint64),
+                ("p2p_bytes", C.c_uint64)]
 
 
 class KernelProfile(C.Structure):
@@ -83,6 +84,7 @@ _SIGNATURES = {
     "fls_release_shard": (_I, [_P, _I, _P]),
     "fls_preload_layer_file": (_I, [C.c_char_p]),
     "fls_trim_host_cache": (_I, [C.c_size_t]),
+    "fls_peer_copy": (_I, [_P, _P, _I, _P, C.c_size_t, _P]),
     "fls_embed": (_I, [_P, _I, _I, _P, _I, _P, _P]),
     "fls_decoder_layer": (_I, [_P, _I, _I, _P, _I, _P, _P, _I, _P]),
     "fls_final_norm": (_I, [_P, _I, _I, _P, _P, _I, _P, _P]),

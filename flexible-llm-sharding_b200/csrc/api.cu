@@ -44,11 +44,9 @@ struct ResidentLayer {
 struct Slot {
     char* dev = nullptr;
     size_t cap = 0;
-    cudaEvent_t ready = nullptr, freed = nullptr, copy_begin = nullptr, copy_end = nullptr;
+    cudaEvent_t ready = nullptr, freed = nullptr;
     bool in_use = false;       // copies enqueued, not yet released
     bool freed_valid = false;  // `freed` has been recorded at least once since the last prefetch
-    bool timing_pending = false;
-    size_t pending_bytes = 0;
     std::vector<ResidentLayer> layers;
     std::vector<std::shared_ptr<HostLayerImage>> pins;  // keep host images alive while copies fly
 };
@@ -75,6 +73,14 @@ struct fls_ctx {
     int rope_n_pos = 0;
     size_t workspace_bytes = 0;
     fls_stats stats{};
+    // weight-stream timing: ring of (begin, end) event pairs on the copy stream
+    struct CopyTiming {
+        cudaEvent_t a = nullptr, b = nullptr;
+        size_t bytes = 0;
+        bool pending = false;
+    };
+    std::vector<CopyTiming> copy_ring;
+    size_t copy_next = 0;
     // per-kernel event profiling
     bool profiling = false;
     struct ProfSlot {
@@ -87,6 +93,7 @@ struct fls_ctx {
     fls_kernel_profile prof[FLS_PROF_CLASSES] = {};
     char err[512] = {0};
     bool cuda_poisoned = false;
+    unsigned long long peer_enabled_mask = 0;
 };
 
 namespace {
@@ -145,8 +152,6 @@ void free_workspace(fls_ctx* c) {
         if (s.dev) cudaFree(s.dev);
         if (s.ready) cudaEventDestroy(s.ready);
         if (s.freed) cudaEventDestroy(s.freed);
-        if (s.copy_begin) cudaEventDestroy(s.copy_begin);
-        if (s.copy_end) cudaEventDestroy(s.copy_end);
     }
     c->slots.clear();
     for (void* p : {static_cast<void*>(c->xn), static_cast<void*>(c->qkv), static_cast<void*>(c->attn),
@@ -158,15 +163,16 @@ void free_workspace(fls_ctx* c) {
     c->workspace_bytes = 0;
 }
 
-void harvest_copy_timing(fls_ctx* c, Slot& s) {
-    if (!s.timing_pending) return;
-    if (cudaEventQuery(s.copy_end) == cudaSuccess) {
+void harvest_copy_timing(fls_ctx* c, fls_ctx::CopyTiming& t, bool wait) {
+    if (!t.pending) return;
+    if (wait) cudaEventSynchronize(t.b);
+    if (cudaEventQuery(t.b) == cudaSuccess) {
         float ms = 0.f;
-        if (cudaEventElapsedTime(&ms, s.copy_begin, s.copy_end) == cudaSuccess) {
+        if (cudaEventElapsedTime(&ms, t.a, t.b) == cudaSuccess) {
             c->stats.h2d_ms += ms;
-            c->stats.h2d_bytes += s.pending_bytes;
+            c->stats.h2d_bytes += t.bytes;
         }
-        s.timing_pending = false;
+        t.pending = false;
     } else {
         cudaGetLastError();
     }
@@ -322,6 +328,10 @@ int fls_destroy(fls_ctx* c) {
         cudaEventDestroy(p.a);
         cudaEventDestroy(p.b);
     }
+    for (auto& t : c->copy_ring) {
+        cudaEventDestroy(t.a);
+        cudaEventDestroy(t.b);
+    }
     delete c;
     return kOk;
 }
@@ -340,8 +350,6 @@ int fls_configure(fls_ctx* c, int n_slots, size_t slot_bytes, int max_rows, int 
         CTX_CUDA(c, cudaMalloc(reinterpret_cast<void**>(&s.dev), std::max<size_t>(s.cap, 256)));
         CTX_CUDA(c, cudaEventCreateWithFlags(&s.ready, cudaEventDisableTiming));
         CTX_CUDA(c, cudaEventCreateWithFlags(&s.freed, cudaEventDisableTiming));
-        CTX_CUDA(c, cudaEventCreate(&s.copy_begin));
-        CTX_CUDA(c, cudaEventCreate(&s.copy_end));
         total += s.cap;
     }
     const size_t R = static_cast<size_t>(max_rows);
@@ -428,7 +436,6 @@ int fls_prefetch_shard(fls_ctx* c, int slot, const int32_t* layer_ids, int n) {
         return ctx_fail(c, fail(kErrInvalid, "fls_prefetch_shard: slot %d, n %d", slot, n));
     Slot& s = c->slots[slot];
     if (s.in_use) return ctx_fail(c, fail(kErrState, "slot %d is still in use: release it before prefetching", slot));
-    harvest_copy_timing(c, s);
     size_t need = 0;
     for (int i = 0; i < n; ++i) {
         const int li = layer_ids[i];
@@ -446,7 +453,17 @@ int fls_prefetch_shard(fls_ctx* c, int slot, const int32_t* layer_ids, int n) {
     if (s.freed_valid) CTX_CUDA(c, cudaStreamWaitEvent(c->copy_stream, s.freed, 0));
     s.layers.clear();
     s.pins.clear();
-    CTX_CUDA(c, cudaEventRecord(s.copy_begin, c->copy_stream));
+    if (c->copy_ring.empty()) {
+        c->copy_ring.resize(64);
+        for (auto& t : c->copy_ring) {
+            CTX_CUDA(c, cudaEventCreate(&t.a));
+            CTX_CUDA(c, cudaEventCreate(&t.b));
+        }
+    }
+    for (auto& t : c->copy_ring) harvest_copy_timing(c, t, false);
+    fls_ctx::CopyTiming& timing = c->copy_ring[c->copy_next++ % c->copy_ring.size()];
+    harvest_copy_timing(c, timing, true);  // only blocks if 64 shard copies are still in flight
+    CTX_CUDA(c, cudaEventRecord(timing.a, c->copy_stream));
     size_t off = 0;
     auto put = [&](const HostLayerImage& img, const char* suffix, const __half** dst) -> int {
         const TensorEntry* t = img.find(suffix);
@@ -482,12 +499,12 @@ int fls_prefetch_shard(fls_ctx* c, int slot, const int32_t* layer_ids, int n) {
         s.layers.push_back(r);
         s.pins.push_back(L.img);
     }
-    CTX_CUDA(c, cudaEventRecord(s.copy_end, c->copy_stream));
+    CTX_CUDA(c, cudaEventRecord(timing.b, c->copy_stream));
+    timing.bytes = off;
+    timing.pending = true;
     CTX_CUDA(c, cudaEventRecord(s.ready, c->copy_stream));
     s.in_use = true;
     s.freed_valid = false;
-    s.timing_pending = true;
-    s.pending_bytes = off;
     return kOk;
 }
 
@@ -507,7 +524,6 @@ int fls_release_shard(fls_ctx* c, int slot, void* stream) {
     CTX_CUDA(c, cudaEventRecord(s.freed, as_stream(stream)));
     s.freed_valid = true;
     s.in_use = false;
-    harvest_copy_timing(c, s);
     return kOk;
 }
 
@@ -631,6 +647,26 @@ int fls_lm_head(fls_ctx* c, int slot, int layer_idx, const uint16_t* x, int n_ro
     return kOk;
 }
 
+int fls_peer_copy(fls_ctx* c, void* dst_dev, int dst_device, const void* src_dev, size_t bytes, void* stream) {
+    ENTER(c);
+    if (!dst_dev || !src_dev) return ctx_fail(c, fail(kErrInvalid, "fls_peer_copy: null pointer"));
+    if (bytes == 0) return kOk;
+    if (dst_device != c->device && !(c->peer_enabled_mask & (1ull << (dst_device & 63)))) {
+        int can = 0;
+        CTX_CUDA(c, cudaDeviceCanAccessPeer(&can, c->device, dst_device));
+        if (can) {
+            cudaError_t e = cudaDeviceEnablePeerAccess(dst_device, 0);
+            if (e != cudaSuccess && e != cudaErrorPeerAccessAlreadyEnabled)
+                return ctx_fail(c, fail(kErrCuda, "cudaDeviceEnablePeerAccess(%d): %s", dst_device, cudaGetErrorString(e)));
+            cudaGetLastError();
+        }  // without peer access cudaMemcpyPeerAsync still works (staged by the driver)
+        c->peer_enabled_mask |= 1ull << (dst_device & 63);
+    }
+    CTX_CUDA(c, cudaMemcpyPeerAsync(dst_dev, dst_device, src_dev, c->device, bytes, as_stream(stream)));
+    c->stats.p2p_bytes += bytes;
+    return kOk;
+}
+
 // --------------------------------------------------------------------------------- single kernels
 int fls_op_gemm(fls_ctx* c, int epilogue, const uint16_t* a_dev, int lda, const uint16_t* b_dev, int ldb, int b_rows,
                 int m, int n, int k, uint16_t* c_dev, int ldc, const uint16_t* r_dev, int ldr, int up_off,
@@ -716,7 +752,7 @@ int fls_get_profile(fls_ctx* c, fls_kernel_profile* out) {
 int fls_get_stats(fls_ctx* c, fls_stats* out) {
     if (!c || !out) return fail(kErrInvalid, "fls_get_stats: null argument");
     cudaSetDevice(c->device);
-    for (auto& s : c->slots) harvest_copy_timing(c, s);
+    for (auto& t : c->copy_ring) harvest_copy_timing(c, t, true);
     c->stats.file_bytes_read = host_cache_file_bytes();
     c->stats.pinned_bytes = host_cache_pinned_bytes();
     c->stats.workspace_bytes = c->workspace_bytes;
@@ -727,6 +763,7 @@ int fls_get_stats(fls_ctx* c, fls_stats* out) {
 int fls_reset_stats(fls_ctx* c) {
     if (!c) return fail(kErrInvalid, "fls_reset_stats: null context");
     c->stats = fls_stats{};
+    for (auto& t : c->copy_ring) t.pending = false;
     for (auto& p : c->prof_ring) p.pending = false;
     for (auto& p : c->prof) p = fls_kernel_profile{};
     return kOk;

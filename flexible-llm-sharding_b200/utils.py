@@ -173,11 +173,64 @@ class ShardedLlama:
         return [lp[int(packed.head_row[i]):int(packed.head_row[i + 1])] for i in range(len(packed.shapes))]
 
     # ------------------------------------------------------------------ engine
+    def _device_inputs(self, packed, dev):
+        """Token ids, rotary positions, attention tiles and gather lists on the device (pinned -> async H2D)."""
+        up = lambda a: torch.from_numpy(a).pin_memory().to(dev, non_blocking=True)
+        mbs = packed.micro_batches
+        d = dict(ids=up(packed.ids), pos=up(packed.row_pos), tiles=[up(mb.tiles) for mb in mbs],
+                 gather=[up(mb.gather) for mb in mbs])
+        d["bytes"] = packed.ids.nbytes + packed.row_pos.nbytes + sum(mb.tiles.nbytes + mb.gather.nbytes for mb in mbs)
+        return d
+
+    def _run_layers(self, slot, shard, bi, mb, x, heads, dv, out, sp):
+        """Runs the layers of `shard` on micro-batch `bi`.  `x` = token-stage rows (or scored rows when
+        the shard starts after model.norm).  Returns (tensor holding the shard's output, is_token_stage)."""
+        call = self.ctx.call
+        n_total = len(self.layer_names)
+        stage_tokens = shard[0] <= n_total - 2
+        for li in shard:
+            kind = self.layer_kinds[li]
+            if kind == _lib.LAYER_EMBED:
+                call("fls_embed", slot, li, dv["ids"][mb.row_lo:].data_ptr(), mb.n_rows, x.data_ptr(), sp)
+            elif kind == _lib.LAYER_DECODER:
+                call("fls_decoder_layer", slot, li, x.data_ptr(), mb.n_rows, dv["pos"][mb.row_lo:].data_ptr(),
+                     dv["tiles"][bi].data_ptr(), int(mb.tiles.shape[0]), sp)
+            elif kind == _lib.LAYER_NORM:
+                call("fls_final_norm", slot, li, x.data_ptr(), dv["gather"][bi].data_ptr(), mb.n_head,
+                     heads.data_ptr(), sp)
+                x, stage_tokens = heads, False
+            else:
+                pd = out["probs"][mb.head_lo:].data_ptr() if out["probs"] is not None else None
+                ad = out["aid"][mb.head_lo:].data_ptr() if out["n_ids"] else None
+                ld = out["lp"][mb.head_lo:].data_ptr() if out["n_ids"] else None
+                call("fls_lm_head", slot, li, x.data_ptr(), mb.n_head, pd, ad, out["n_ids"], ld, None, sp)
+        return x, stage_tokens
+
+    def _alloc_outputs(self, packed, dev, want_probs, answer_ids):
+        n_head = packed.total_head_rows
+        out = dict(probs=None, aid=None, lp=None, n_ids=0 if answer_ids is None else int(len(answer_ids)))
+        if want_probs:
+            out["probs"] = torch.empty((n_head, self.vocab), dtype=torch.float16, device=dev)
+        if out["n_ids"]:
+            aid = np.tile(np.asarray(answer_ids, dtype=np.int32), (n_head, 1))
+            out["aid"] = torch.from_numpy(aid).pin_memory().to(dev, non_blocking=True)
+            out["lp"] = torch.empty((n_head, out["n_ids"]), dtype=torch.float32, device=dev)
+        return out
+
+    def _fetch_result(self, out, want_probs, stream, return_device):
+        src = out["probs"] if want_probs else out["lp"]
+        if return_device:
+            return src, 0
+        host = torch.empty(src.shape, dtype=src.dtype).pin_memory()
+        host.copy_(src, non_blocking=True)
+        stream.synchronize()
+        return host.numpy(), host.numel() * host.element_size()
+
     def run(self, inputs, want_probs=True, answer_ids=None, packed=None, return_device=False):
         shards, num_gpu, rank, dp = self._plan()
         if not dp:
             from .pipeline import run_model_parallel
-            return run_model_parallel(self, inputs, shards, num_gpu, rank, want_probs, answer_ids)
+            return run_model_parallel(self, inputs, shards, num_gpu, rank, want_probs, answer_ids, return_device)
         t0 = perf_counter()
         if packed is None:
             tok = planner.tokenize_prompts(self.tokenizer, inputs)
@@ -189,32 +242,18 @@ class ShardedLlama:
         t_tok = perf_counter() - t0
         self._configure(shards)
         dev = self.torch_device
-        H, V = self.hidden, self.vocab
         n_layers_total = len(self.layer_names)
         call = self.ctx.call
         with torch.cuda.device(dev):
             stream = torch.cuda.current_stream(dev)
             sp = C.c_void_p(stream.cuda_stream)
-            ids_dev = torch.from_numpy(packed.ids).pin_memory().to(dev, non_blocking=True)
-            pos_dev = torch.from_numpy(packed.row_pos).pin_memory().to(dev, non_blocking=True)
+            dv = self._device_inputs(packed, dev)
             mbs = packed.micro_batches
-            tiles_dev = [torch.from_numpy(mb.tiles).pin_memory().to(dev, non_blocking=True) for mb in mbs]
-            gather_dev = [torch.from_numpy(mb.gather).pin_memory().to(dev, non_blocking=True) for mb in mbs]
-            in_bytes = packed.ids.nbytes + packed.row_pos.nbytes + sum(mb.tiles.nbytes + mb.gather.nbytes for mb in mbs)
             rank_tag = str(rank) if self.args.data_parallel else ""
-            store = ActivationStore(self.args.storage_location, packed, H, dev, stream,
+            store = ActivationStore(self.args.storage_location, packed, self.hidden, dev, stream,
                                     disk_folder=getattr(self.args, "disk_folder", "./temp"), rank_tag=rank_tag,
                                     hbm_budget_bytes=self.hbm_activation_budget, force_tier=self.force_tier)
-            n_head = packed.total_head_rows
-            probs_dev = torch.empty((n_head, V), dtype=torch.float16, device=dev) if want_probs else None
-            n_ids = 0 if answer_ids is None else int(len(answer_ids))
-            if n_ids:
-                aid = np.tile(np.asarray(answer_ids, dtype=np.int32), (n_head, 1))
-                aid_dev = torch.from_numpy(aid).pin_memory().to(dev, non_blocking=True)
-                lp_dev = torch.empty((n_head, n_ids), dtype=torch.float32, device=dev)
-            else:
-                aid_dev = lp_dev = None
-
+            out = self._alloc_outputs(packed, dev, want_probs, answer_ids)
             live = [s for s in shards if len(s)]
 
             def prefetch(si):
@@ -236,49 +275,20 @@ class ShardedLlama:
                         x = store.fetch(bi, has_input)
                     else:
                         x = store.heads_view(bi)
-                    stage_tokens = tokens_in
-                    for li in shard:
-                        kind = self.layer_kinds[li]
-                        if kind == _lib.LAYER_EMBED:
-                            call("fls_embed", slot, li, ids_dev[mb.row_lo:].data_ptr(), mb.n_rows, x.data_ptr(), sp)
-                        elif kind == _lib.LAYER_DECODER:
-                            call("fls_decoder_layer", slot, li, x.data_ptr(), mb.n_rows, pos_dev[mb.row_lo:].data_ptr(),
-                                 tiles_dev[bi].data_ptr(), int(mb.tiles.shape[0]), sp)
-                        elif kind == _lib.LAYER_NORM:
-                            h = store.heads_view(bi)
-                            call("fls_final_norm", slot, li, x.data_ptr(), gather_dev[bi].data_ptr(), mb.n_head,
-                                 h.data_ptr(), sp)
-                            if stage_tokens:
-                                store.store(bi, x, keep_tokens=False)
-                            x, stage_tokens = h, False
-                        else:
-                            pd = probs_dev[mb.head_lo:].data_ptr() if want_probs else None
-                            ad = aid_dev[mb.head_lo:].data_ptr() if n_ids else None
-                            ld = lp_dev[mb.head_lo:].data_ptr() if n_ids else None
-                            call("fls_lm_head", slot, li, x.data_ptr(), mb.n_head, pd, ad, n_ids, ld, None, sp)
-                    if stage_tokens:
-                        store.store(bi, x, keep_tokens=True)
+                    y, still_tokens = self._run_layers(slot, shard, bi, mb, x, store.heads_view(bi), dv, out, sp)
+                    if tokens_in:
+                        store.store(bi, x, keep_tokens=still_tokens)
                 store.end_shard()
                 call("fls_release_shard", slot, sp)
 
-            result = None
-            out_bytes = 0
-            owns_head = any(n_layers_total - 1 in s for s in live)
-            if owns_head:
-                if return_device:
-                    result = probs_dev if want_probs else lp_dev
-                else:
-                    src = probs_dev if want_probs else lp_dev
-                    host = torch.empty(src.shape, dtype=src.dtype).pin_memory()
-                    host.copy_(src, non_blocking=True)
-                    stream.synchronize()
-                    result = host.numpy()
-                    out_bytes = host.numel() * host.element_size()
+            result, out_bytes = None, 0
+            if any(n_layers_total - 1 in s for s in live):
+                result, out_bytes = self._fetch_result(out, want_probs, stream, return_device)
             else:
                 stream.synchronize()
             store.cleanup()
-            self.last_timing = dict(tokenize_s=t_tok, total_s=perf_counter() - t0, h2d_input_bytes=in_bytes,
+            self.last_timing = dict(tokenize_s=t_tok, total_s=perf_counter() - t0, h2d_input_bytes=dv["bytes"],
                                     d2h_output_bytes=out_bytes, activation_tier=store.tier,
                                     act_h2d_bytes=store.h2d_bytes, act_d2h_bytes=store.d2h_bytes)
-            self._keepalive = (ids_dev, pos_dev, tiles_dev, gather_dev, aid_dev, store)
+            self._keepalive = (dv, out, store)
         return result, packed

@@ -80,6 +80,7 @@ typedef struct fls_stats {
     uint64_t file_bytes_read; /* bytes read from layer files into pinned memory (process-wide) */
     uint64_t pinned_bytes;    /* pinned host bytes currently held (process-wide) */
     uint64_t workspace_bytes; /* HBM held by this context (slots + workspace) */
+    uint64_t p2p_bytes;       /* activation bytes handed to other GPUs (fls_peer_copy) */
 } fls_stats;
 
 /* ---------------------------------------------------------------------------------------------
@@ -150,6 +151,12 @@ int fls_final_norm(fls_ctx* ctx, int slot, int layer_idx, const uint16_t* x_dev,
  *   lse_dev     [n_rows] fp32; may be NULL. */
 int fls_lm_head(fls_ctx* ctx, int slot, int layer_idx, const uint16_t* x_dev, int n_rows, uint16_t* probs_dev,
                 const int32_t* answer_ids_dev, int n_ids, float* logprob_dev, float* lse_dev, void* stream);
+
+/* Model-parallel hand-off (utils.py:163,185,193-195: the reference passes activations between GPU
+ * threads through a shared dict and `.to(self.device)`): copy `bytes` from this context's GPU
+ * straight into a buffer on GPU `dst_device` over NVLink (cudaMemcpyPeerAsync on `stream`, peer
+ * access enabled on first use).  Ordering with the consumer is the caller's (events). */
+int fls_peer_copy(fls_ctx* ctx, void* dst_dev, int dst_device, const void* src_dev, size_t bytes, void* stream);
 
 /* ---------------------------------------------------------------------------------------------
  * single kernels on caller-supplied device buffers (unit parity tests, profiling). */
