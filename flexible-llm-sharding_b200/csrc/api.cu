@@ -94,6 +94,7 @@ struct fls_ctx {
     char err[512] = {0};
     bool cuda_poisoned = false;
     unsigned long long peer_enabled_mask = 0;
+    int gemm_cg = 2;  // tcgen05 cta_group of the GEMM kernels (2 = CTA pairs, 1 = single CTA)
 };
 
 namespace {
@@ -252,7 +253,7 @@ int head_impl(fls_ctx* c, const __half* x, const __half* W, int n_rows, int V, i
     const double flops = 2.0 * n_rows * V * K;
     {
         ProfScope ps(c, FLS_PROF_GEMM_HEAD, flops, st);
-        FLS_TRY(gemm_launch(kEpiLsePartial, a, c->num_sms, st));
+        FLS_TRY(gemm_launch(kEpiLsePartial, a, c->num_sms, st, c->gemm_cg));
     }
     {
         ProfScope ps(c, FLS_PROF_OTHER, 0, st);
@@ -262,7 +263,7 @@ int head_impl(fls_ctx* c, const __half* x, const __half* W, int n_rows, int V, i
     if (probs) {
         a.C = probs, a.ldc = V, a.lse = c->lse;
         ProfScope ps(c, FLS_PROF_GEMM_HEAD, flops, st);
-        FLS_TRY(gemm_launch(kEpiProbs, a, c->num_sms, st));
+        FLS_TRY(gemm_launch(kEpiProbs, a, c->num_sms, st, c->gemm_cg));
         c->stats.kernel_launches += 1;
     }
     if (logprob && n_ids > 0) {
@@ -579,7 +580,7 @@ int fls_decoder_layer(fls_ctx* c, int slot, int layer_idx, uint16_t* x_dev, int 
     a.M = n_rows, a.N = c->qkv_dim, a.K = Hd, a.C = c->qkv, a.ldc = c->qkv_dim;
     {
         ProfScope ps(c, FLS_PROF_GEMM_QKV, 2.0 * R * c->qkv_dim * Hd, st);
-        CTX_TRY(c, gemm_launch(kEpiStore, a, c->num_sms, st));
+        CTX_TRY(c, gemm_launch(kEpiStore, a, c->num_sms, st, c->gemm_cg));
     }
     {
         ProfScope ps(c, FLS_PROF_ROPE, R * (c->q_dim + c->kv_dim) * 4.0, st);
@@ -596,7 +597,7 @@ int fls_decoder_layer(fls_ctx* c, int slot, int layer_idx, uint16_t* x_dev, int 
     a.M = n_rows, a.N = Hd, a.K = c->q_dim, a.C = x, a.ldc = Hd, a.R = x, a.ldr = Hd;
     {
         ProfScope ps(c, FLS_PROF_GEMM_O, 2.0 * R * Hd * c->q_dim, st);
-        CTX_TRY(c, gemm_launch(kEpiResidual, a, c->num_sms, st));
+        CTX_TRY(c, gemm_launch(kEpiResidual, a, c->num_sms, st, c->gemm_cg));
     }
 
     // hidden = hidden + down_proj(silu(gate_proj(norm(hidden))) * up_proj(norm(hidden)))
@@ -609,14 +610,14 @@ int fls_decoder_layer(fls_ctx* c, int slot, int layer_idx, uint16_t* x_dev, int 
     a.M = n_rows, a.N = I, a.K = Hd, a.C = c->hmid, a.ldc = I, a.up_off = I;
     {
         ProfScope ps(c, FLS_PROF_GEMM_GATE_UP, 2.0 * R * (2.0 * I) * Hd, st);
-        CTX_TRY(c, gemm_launch(kEpiSwiGLU, a, c->num_sms, st));
+        CTX_TRY(c, gemm_launch(kEpiSwiGLU, a, c->num_sms, st, c->gemm_cg));
     }
     a = GemmArgs{};
     a.A = c->hmid, a.lda = I, a.B = r->dec.wd, a.ldb = I, a.b_rows = Hd;
     a.M = n_rows, a.N = Hd, a.K = I, a.C = x, a.ldc = Hd, a.R = x, a.ldr = Hd;
     {
         ProfScope ps(c, FLS_PROF_GEMM_DOWN, 2.0 * R * Hd * I, st);
-        CTX_TRY(c, gemm_launch(kEpiResidual, a, c->num_sms, st));
+        CTX_TRY(c, gemm_launch(kEpiResidual, a, c->num_sms, st, c->gemm_cg));
     }
     c->stats.kernel_launches += 8;
     return kOk;
@@ -677,7 +678,7 @@ int fls_op_gemm(fls_ctx* c, int epilogue, const uint16_t* a_dev, int lda, const 
     GemmArgs a{};
     a.A = H(a_dev), a.lda = lda, a.B = H(b_dev), a.ldb = ldb, a.b_rows = b_rows, a.M = m, a.N = n, a.K = k;
     a.C = H(c_dev), a.ldc = ldc, a.R = H(r_dev), a.ldr = ldr, a.up_off = up_off;
-    CTX_TRY(c, gemm_launch(static_cast<GemmEpilogue>(epilogue), a, c->num_sms, as_stream(stream)));
+    CTX_TRY(c, gemm_launch(static_cast<GemmEpilogue>(epilogue), a, c->num_sms, as_stream(stream), c->gemm_cg));
     c->stats.kernel_launches += 1;
     return kOk;
 }
@@ -733,6 +734,16 @@ int fls_op_head(fls_ctx* c, const uint16_t* x, const uint16_t* w, int n_rows, in
     CTX_TRY(c, head_impl(c, H(x), H(w), n_rows, n, k, H(probs), answer_ids, n_ids, logprob, lse_out,
                          as_stream(stream)));
     return kOk;
+}
+
+int fls_set_option(fls_ctx* c, const char* name, int value) {
+    if (!c || !name) return fail(kErrInvalid, "fls_set_option: null argument");
+    if (strcmp(name, "gemm_cta_group") == 0) {
+        if (value != 1 && value != 2) return ctx_fail(c, fail(kErrInvalid, "gemm_cta_group must be 1 or 2"));
+        c->gemm_cg = value;
+        return kOk;
+    }
+    return ctx_fail(c, fail(kErrInvalid, "fls_set_option: unknown option '%s'", name));
 }
 
 int fls_set_profiling(fls_ctx* c, int enabled) {

@@ -58,7 +58,7 @@ struct GemmArgs {
     const float* lse;  // [M]
     int up_off;
 };
-int gemm_launch(GemmEpilogue epi, const GemmArgs& a, int num_sms, cudaStream_t stream);
+int gemm_launch(GemmEpilogue epi, const GemmArgs& a, int num_sms, cudaStream_t stream, int cta_group = 2);
 int gemm_init();  // resolves cuTensorMapEncodeTiled and opts kernels into large dynamic smem
 int gemm_lse_blocks(int N);
 

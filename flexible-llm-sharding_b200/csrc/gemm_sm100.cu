@@ -18,6 +18,8 @@
 // Rounding in the epilogues follows the reference's eager fp16 order (see each epilogue).
 #include <cuda.h>
 
+#include <algorithm>
+
 #include "common.cuh"
 #include "ptx.cuh"
 
@@ -25,17 +27,27 @@ namespace fls {
 
 namespace {
 
-constexpr int BLOCK_M = 128;
+constexpr int BLOCK_M = 128;  // rows per CTA (a CTA pair covers 256)
 constexpr int BLOCK_N = 256;  // MMA N (TMEM columns per accumulator stage)
 constexpr int BLOCK_K = 64;   // 64 fp16 = 128 B = one swizzle row
 constexpr int UMMA_K = 16;
-constexpr int STAGES = 4;
 constexpr int ACC_STAGES = 2;
 constexpr int A_BYTES = BLOCK_M * BLOCK_K * 2;  // 16 KiB
-constexpr int B_BYTES = BLOCK_N * BLOCK_K * 2;  // 32 KiB
-constexpr int STAGE_BYTES = A_BYTES + B_BYTES;
 constexpr int SMEM_BARRIER_BYTES = 256;
-constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + SMEM_BARRIER_BYTES + 1024;  // + alignment slack
+constexpr int MAX_STAGES = 8;
+
+// CG = tcgen05 cta_group.  CG 1: one CTA per 128x256 tile, B tile 256 rows, 4 stages of 48 KiB.
+// CG 2: a CTA pair (cluster of 2) per 256x256 tile; each CTA stages its own 128 A rows and HALF of
+// the B rows (the pair's MMA reads both halves), 6 stages of 32 KiB: half the shared-memory operand
+// traffic per SM and a deeper TMA look-ahead.
+template <int CG>
+struct Cfg {
+    static constexpr int STAGES = CG == 1 ? 4 : 6;
+    static constexpr int B_ROWS = BLOCK_N / CG;
+    static constexpr int B_BYTES = B_ROWS * BLOCK_K * 2;
+    static constexpr int STAGE_BYTES = A_BYTES + B_BYTES;
+    static constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + SMEM_BARRIER_BYTES + 1024;  // + alignment slack
+};
 constexpr int NUM_THREADS = 256;
 constexpr int EPI_WARP0 = 4;
 constexpr int GROUP_M = 16;  // m-blocks per raster group: A bands of a group stay in L2 while n sweeps
@@ -72,20 +84,25 @@ __device__ __forceinline__ uint32_t pack_h2(__half a, __half b) {
     return *reinterpret_cast<uint32_t*>(&h);
 }
 
-template <int EPI>
+template <int EPI, int CG>
 __global__ void __launch_bounds__(NUM_THREADS, 1)
 gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CUtensorMap tmap_b,
                     const KParams p) {
+    constexpr int STAGES = Cfg<CG>::STAGES;
+    constexpr int B_BYTES = Cfg<CG>::B_BYTES;
+    constexpr int STAGE_BYTES = Cfg<CG>::STAGE_BYTES;
     extern __shared__ uint8_t smem_raw[];
     uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
     uint64_t* full_bar = reinterpret_cast<uint64_t*>(smem + STAGES * STAGE_BYTES);
-    uint64_t* empty_bar = full_bar + STAGES;
-    uint64_t* tmem_full_bar = empty_bar + STAGES;
+    uint64_t* empty_bar = full_bar + MAX_STAGES;
+    uint64_t* tmem_full_bar = empty_bar + MAX_STAGES;
     uint64_t* tmem_empty_bar = tmem_full_bar + ACC_STAGES;
     uint32_t* tmem_base_slot = reinterpret_cast<uint32_t*>(tmem_empty_bar + ACC_STAGES);
 
     const int warp_idx = threadIdx.x >> 5;  // warp-uniform
     const int lane = threadIdx.x & 31;
+    const uint32_t cta_rank = CG == 2 ? ptx::cluster_ctarank() : 0;  // 0 = leader of the pair
+    const bool is_leader = cta_rank == 0;
 
     if (warp_idx == 0 && ptx::elect_one()) {
         ptx::prefetch_tensormap(&tmap_a);
@@ -93,49 +110,64 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_con
     }
     if (warp_idx == 1 && ptx::elect_one()) {
         for (int i = 0; i < STAGES; ++i) {
-            ptx::mbar_init(&full_bar[i], 1);
-            ptx::mbar_init(&empty_bar[i], 1);
+            ptx::mbar_init(&full_bar[i], 1);   // the (leader's) producer arrive.expect_tx
+            ptx::mbar_init(&empty_bar[i], 1);  // one tcgen05.commit
         }
         for (int i = 0; i < ACC_STAGES; ++i) {
             ptx::mbar_init(&tmem_full_bar[i], 1);
-            ptx::mbar_init(&tmem_empty_bar[i], 4);  // one arrive per epilogue warp
+            ptx::mbar_init(&tmem_empty_bar[i], 4 * CG);  // one arrive per epilogue warp of every CTA of the pair
         }
         ptx::fence_mbar_init();
     }
     if (warp_idx == 2) {
-        ptx::tmem_alloc<1>(tmem_base_slot, 512);
-        ptx::tmem_relinquish<1>();
+        ptx::tmem_alloc<CG>(tmem_base_slot, 512);
+        ptx::tmem_relinquish<CG>();
     }
     ptx::tc_fence_before_sync();
-    __syncthreads();
+    if constexpr (CG == 2) ptx::cluster_sync_all(); else __syncthreads();
     ptx::tc_fence_after_sync();
     const uint32_t tmem_base = *tmem_base_slot;
 
-    const int num_tiles = p.num_m_blocks * p.num_n_blocks;
+    const int num_tiles = p.num_m_blocks * p.num_n_blocks;  // m blocks of 128*CG rows
     const int k_blocks = (p.K + BLOCK_K - 1) / BLOCK_K;
     constexpr int OUT_COLS = out_cols_per_tile<EPI>();
+    const int worker = blockIdx.x / CG, n_workers = gridDim.x / CG;
 
     if (warp_idx == 0) {
-        // ------------------------------------------------------------------ TMA producer
+        // ------------------------------------------------------------------ TMA producer (every CTA)
         if (ptx::elect_one()) {
             int stage = 0;
             uint32_t phase = 0;
-            for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
+            for (int tile = worker; tile < num_tiles; tile += n_workers) {
                 int m_blk, n_blk;
                 tile_coords(tile, p.num_m_blocks, p.num_n_blocks, m_blk, n_blk);
+                const int a_row = (m_blk * CG + static_cast<int>(cta_rank)) * BLOCK_M;
+                int b_row;
+                if constexpr (EPI == kEpiSwiGLU)  // CG 2: leader stages the gate rows, its peer the up rows
+                    b_row = n_blk * OUT_COLS + (CG == 2 ? static_cast<int>(cta_rank) * p.up_off : 0);
+                else
+                    b_row = n_blk * BLOCK_N + static_cast<int>(cta_rank) * Cfg<CG>::B_ROWS;
                 for (int kb = 0; kb < k_blocks; ++kb) {
                     ptx::mbar_wait(&empty_bar[stage], phase ^ 1);
                     uint8_t* sa = smem + stage * STAGE_BYTES;
                     uint8_t* sb = sa + A_BYTES;
-                    ptx::mbar_arrive_expect_tx(&full_bar[stage], STAGE_BYTES);
-                    ptx::tma_load_2d(sa, &tmap_a, &full_bar[stage], kb * BLOCK_K, m_blk * BLOCK_M);
-                    if constexpr (EPI == kEpiSwiGLU) {
-                        // gate rows -> MMA columns [0,128), up rows -> MMA columns [128,256)
-                        ptx::tma_load_2d(sb, &tmap_b, &full_bar[stage], kb * BLOCK_K, n_blk * OUT_COLS);
-                        ptx::tma_load_2d(sb + B_BYTES / 2, &tmap_b, &full_bar[stage], kb * BLOCK_K,
-                                         p.up_off + n_blk * OUT_COLS);
+                    if constexpr (CG == 1) {
+                        ptx::mbar_arrive_expect_tx(&full_bar[stage], STAGE_BYTES);
+                        ptx::tma_load_2d(sa, &tmap_a, &full_bar[stage], kb * BLOCK_K, a_row);
+                        if constexpr (EPI == kEpiSwiGLU) {
+                            // gate rows -> MMA columns [0,128), up rows -> MMA columns [128,256)
+                            ptx::tma_load_2d(sb, &tmap_b, &full_bar[stage], kb * BLOCK_K, b_row);
+                            ptx::tma_load_2d(sb + B_BYTES / 2, &tmap_b, &full_bar[stage], kb * BLOCK_K,
+                                             p.up_off + b_row);
+                        } else {
+                            ptx::tma_load_2d(sb, &tmap_b, &full_bar[stage], kb * BLOCK_K, b_row);
+                        }
                     } else {
-                        ptx::tma_load_2d(sb, &tmap_b, &full_bar[stage], kb * BLOCK_K, n_blk * BLOCK_N);
+                        // both CTAs' bytes are credited to the leader's barrier (peer bit cleared)
+                        if (is_leader) ptx::mbar_arrive_expect_tx(&full_bar[stage], 2 * STAGE_BYTES);
+                        const uint32_t bar = ptx::smem_u32(&full_bar[stage]) & 0xFEFFFFFFu;
+                        ptx::tma_load_2d_cta2(sa, &tmap_a, bar, kb * BLOCK_K, a_row);
+                        ptx::tma_load_2d_cta2(sb, &tmap_b, bar, kb * BLOCK_K, b_row);
                     }
                     if (++stage == STAGES) {
                         stage = 0;
@@ -145,14 +177,14 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_con
             }
         }
     } else if (warp_idx == 1) {
-        // ------------------------------------------------------------------ MMA issuer
-        if (ptx::elect_one()) {
-            constexpr uint32_t idesc = ptx::umma_idesc_f16_f32(BLOCK_M, BLOCK_N);
+        // ------------------------------------------------------------------ MMA issuer (leader CTA only)
+        if (is_leader && ptx::elect_one()) {
+            constexpr uint32_t idesc = ptx::umma_idesc_f16_f32(BLOCK_M * CG, BLOCK_N);
             int stage = 0;
             uint32_t phase = 0;
             int acc = 0;
             uint32_t acc_phase = 0;
-            for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
+            for (int tile = worker; tile < num_tiles; tile += n_workers) {
                 ptx::mbar_wait(&tmem_empty_bar[acc], acc_phase ^ 1);
                 ptx::tc_fence_after_sync();
                 const uint32_t tmem_d = tmem_base + acc * BLOCK_N;
@@ -165,15 +197,19 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_con
 #pragma unroll
                     for (int k = 0; k < BLOCK_K / UMMA_K; ++k) {
                         // advance 16 fp16 = 32 B inside the 128 B swizzle row: +2 in the (addr >> 4) field
-                        ptx::umma_f16<1>(tmem_d, da + 2 * k, db + 2 * k, idesc, (kb | k) != 0);
+                        ptx::umma_f16<CG>(tmem_d, da + 2 * k, db + 2 * k, idesc, (kb | k) != 0);
                     }
-                    ptx::umma_commit(&empty_bar[stage]);  // frees the smem stage once these MMAs retire
+                    // frees the smem stage (in both CTAs of a pair) once these MMAs retire
+                    if constexpr (CG == 1) ptx::umma_commit(&empty_bar[stage]);
+                    else ptx::umma_commit_cta2(&empty_bar[stage], 0b11);
                     if (++stage == STAGES) {
                         stage = 0;
                         phase ^= 1;
                     }
                 }
-                ptx::umma_commit(&tmem_full_bar[acc]);  // accumulator complete -> epilogue
+                // accumulator complete -> epilogue warps (of both CTAs)
+                if constexpr (CG == 1) ptx::umma_commit(&tmem_full_bar[acc]);
+                else ptx::umma_commit_cta2(&tmem_full_bar[acc], 0b11);
                 if (++acc == ACC_STAGES) {
                     acc = 0;
                     acc_phase ^= 1;
@@ -185,12 +221,12 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_con
         const int ew = warp_idx - EPI_WARP0;  // == warp_idx % 4 -> TMEM lanes [32*ew, 32*ew+32)
         int acc = 0;
         uint32_t acc_phase = 0;
-        for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
+        for (int tile = worker; tile < num_tiles; tile += n_workers) {
             int m_blk, n_blk;
             tile_coords(tile, p.num_m_blocks, p.num_n_blocks, m_blk, n_blk);
             ptx::mbar_wait(&tmem_full_bar[acc], acc_phase);
             ptx::tc_fence_after_sync();
-            const int row = m_blk * BLOCK_M + ew * 32 + lane;
+            const int row = (m_blk * CG + static_cast<int>(cta_rank)) * BLOCK_M + ew * 32 + lane;
             const bool row_ok = row < p.M;
             const uint32_t taddr = tmem_base + (static_cast<uint32_t>(ew * 32) << 16) + acc * BLOCK_N;
             const int col0 = n_blk * OUT_COLS;
@@ -296,7 +332,10 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_con
             }
             ptx::tc_fence_before_sync();
             __syncwarp();
-            if (lane == 0) ptx::mbar_arrive(&tmem_empty_bar[acc]);
+            if (lane == 0) {
+                if constexpr (CG == 1) ptx::mbar_arrive(&tmem_empty_bar[acc]);
+                else ptx::mbar_arrive_cluster(&tmem_empty_bar[acc], 0);  // the leader's MMA thread waits on it
+            }
             if (++acc == ACC_STAGES) {
                 acc = 0;
                 acc_phase ^= 1;
@@ -305,10 +344,12 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_con
     }
 
     ptx::tc_fence_before_sync();
-    __syncthreads();
+    __syncwarp();
+    // a pair must leave together: the leader's MMAs read the peer's smem and signal its barriers
+    if constexpr (CG == 2) ptx::cluster_sync_all(); else __syncthreads();
     if (warp_idx == 2) {
         ptx::tc_fence_after_sync();
-        ptx::tmem_dealloc<1>(tmem_base, 512);
+        ptx::tmem_dealloc<CG>(tmem_base, 512);
     }
 }
 
@@ -332,28 +373,48 @@ int make_tmap(CUtensorMap* tm, const __half* base, int rows, int cols, int ld, i
     return kOk;
 }
 
-template <int EPI>
+template <int EPI, int CG>
 int launch_t(const GemmArgs& a, int num_sms, cudaStream_t stream) {
     constexpr int OUT_COLS = EPI == kEpiSwiGLU ? BLOCK_N / 2 : BLOCK_N;
+    constexpr int B_BOX = (EPI == kEpiSwiGLU || CG == 2) ? BLOCK_N / 2 : BLOCK_N;
     CUtensorMap tma, tmb;
     FLS_TRY(make_tmap(&tma, a.A, a.M, a.K, a.lda, BLOCK_M));
-    FLS_TRY(make_tmap(&tmb, a.B, a.b_rows, a.K, a.ldb, EPI == kEpiSwiGLU ? BLOCK_N / 2 : BLOCK_N));
+    FLS_TRY(make_tmap(&tmb, a.B, a.b_rows, a.K, a.ldb, B_BOX));
     KParams p;
     p.M = a.M, p.N = a.N, p.K = a.K;
     p.C = a.C, p.ldc = a.ldc, p.R = a.R, p.ldr = a.ldr;
     p.partial = a.partial, p.lse = a.lse, p.up_off = a.up_off;
-    p.num_m_blocks = (a.M + BLOCK_M - 1) / BLOCK_M;
+    p.num_m_blocks = (a.M + BLOCK_M * CG - 1) / (BLOCK_M * CG);
     p.num_n_blocks = (a.N + OUT_COLS - 1) / OUT_COLS;
     const int tiles = p.num_m_blocks * p.num_n_blocks;
-    const int grid = tiles < num_sms ? tiles : num_sms;
-    gemm_tcgen05_kernel<EPI><<<grid, NUM_THREADS, SMEM_BYTES, stream>>>(tma, tmb, p);
-    FLS_CUDA(cudaGetLastError());
+    const int workers = std::min(tiles, num_sms / CG);
+    cudaLaunchConfig_t cfg{};
+    cfg.gridDim = dim3(workers * CG);
+    cfg.blockDim = dim3(NUM_THREADS);
+    cfg.dynamicSmemBytes = Cfg<CG>::SMEM_BYTES;
+    cfg.stream = stream;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeClusterDimension;
+    attr[0].val.clusterDim.x = CG;
+    attr[0].val.clusterDim.y = 1;
+    attr[0].val.clusterDim.z = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = 1;
+    FLS_CUDA(cudaLaunchKernelEx(&cfg, gemm_tcgen05_kernel<EPI, CG>, tma, tmb, p));
     return kOk;
 }
 
 template <int EPI>
+int launch_cg(const GemmArgs& a, int num_sms, int cta_group, cudaStream_t stream) {
+    return cta_group == 2 ? launch_t<EPI, 2>(a, num_sms, stream) : launch_t<EPI, 1>(a, num_sms, stream);
+}
+
+template <int EPI>
 int set_smem_attr() {
-    FLS_CUDA(cudaFuncSetAttribute(gemm_tcgen05_kernel<EPI>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_BYTES));
+    FLS_CUDA(cudaFuncSetAttribute(gemm_tcgen05_kernel<EPI, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                  Cfg<1>::SMEM_BYTES));
+    FLS_CUDA(cudaFuncSetAttribute(gemm_tcgen05_kernel<EPI, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                  Cfg<2>::SMEM_BYTES));
     return kOk;
 }
 
@@ -378,26 +439,26 @@ int gemm_init() {
     return kOk;
 }
 
-int gemm_launch(GemmEpilogue epi, const GemmArgs& a, int num_sms, cudaStream_t stream) {
+int gemm_launch(GemmEpilogue epi, const GemmArgs& a, int num_sms, cudaStream_t stream, int cta_group) {
     if (!g_encode) return fail(kErrState, "gemm_init() has not run");
     if (a.M <= 0 || a.N <= 0 || a.K <= 0) return fail(kErrInvalid, "gemm: empty problem %dx%dx%d", a.M, a.N, a.K);
     if (a.K % 8 || a.N % 8) return fail(kErrInvalid, "gemm: N and K must be multiples of 8 (N=%d K=%d)", a.N, a.K);
     if (epi != kEpiLsePartial && (a.ldc % 8 || (reinterpret_cast<uintptr_t>(a.C) & 15)))
         return fail(kErrInvalid, "gemm: C must be 16-byte aligned with ldc %% 8 == 0");
     switch (epi) {
-        case kEpiStore: return launch_t<kEpiStore>(a, num_sms, stream);
+        case kEpiStore: return launch_cg<kEpiStore>(a, num_sms, cta_group, stream);
         case kEpiResidual:
             if (!a.R || a.ldr % 8) return fail(kErrInvalid, "gemm: residual epilogue needs R with ldr %% 8 == 0");
-            return launch_t<kEpiResidual>(a, num_sms, stream);
+            return launch_cg<kEpiResidual>(a, num_sms, cta_group, stream);
         case kEpiSwiGLU:
             if (a.b_rows < a.up_off + a.N) return fail(kErrInvalid, "gemm: SwiGLU needs gate and up rows in B");
-            return launch_t<kEpiSwiGLU>(a, num_sms, stream);
+            return launch_cg<kEpiSwiGLU>(a, num_sms, cta_group, stream);
         case kEpiLsePartial:
             if (!a.partial) return fail(kErrInvalid, "gemm: lse epilogue needs a partial buffer");
-            return launch_t<kEpiLsePartial>(a, num_sms, stream);
+            return launch_cg<kEpiLsePartial>(a, num_sms, cta_group, stream);
         case kEpiProbs:
             if (!a.lse) return fail(kErrInvalid, "gemm: probs epilogue needs lse");
-            return launch_t<kEpiProbs>(a, num_sms, stream);
+            return launch_cg<kEpiProbs>(a, num_sms, cta_group, stream);
     }
     return fail(kErrInvalid, "gemm: unknown epilogue %d", static_cast<int>(epi));
 }

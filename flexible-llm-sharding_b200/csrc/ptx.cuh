@@ -82,7 +82,7 @@ __device__ __forceinline__ void tma_load_2d(void* smem_dst, const void* tmap, ui
 __device__ __forceinline__ void tma_load_2d_cta2(void* smem_dst, const void* tmap, uint32_t bar_cluster_addr,
                                                  int32_t c_inner, int32_t c_outer) {
     asm volatile(
-        "cp.async.bulk.tensor.2d.cta_group::2.shared::cluster.global.tile.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];\n" ::
+        "cp.async.bulk.tensor.2d.cta_group::2.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];\n" ::
             "r"(smem_u32(smem_dst)),
         "l"(reinterpret_cast<uint64_t>(tmap)), "r"(bar_cluster_addr), "r"(c_inner), "r"(c_outer)
         : "memory");

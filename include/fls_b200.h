@@ -226,6 +226,10 @@ int fls_set_profiling(fls_ctx* ctx, int enabled);
 /* Waits for the profiled launches to finish, then fills out[0..FLS_PROF_CLASSES). */
 int fls_get_profile(fls_ctx* ctx, fls_kernel_profile* out);
 
+/* Tuning knobs.  "gemm_cta_group": 2 (default; CTA pairs share a 256x256 tile through
+ * tcgen05 cta_group::2) or 1 (one CTA per 128x256 tile). */
+int fls_set_option(fls_ctx* ctx, const char* name, int value);
+
 int fls_get_stats(fls_ctx* ctx, fls_stats* out);
 int fls_reset_stats(fls_ctx* ctx);
 

@@ -34,11 +34,18 @@ def _rand(shape, std, seed, dev):
 
 # M, N, K: full tiles, M tail, N tail (vocab-like 1000), tiny K, K tail (not a multiple of 64), multi-wave
 GEMM_SHAPES = [(128, 256, 64), (256, 512, 512), (200, 256, 128), (130, 1000, 512), (64, 8, 8), (300, 264, 200),
-               (4096, 2304, 512), (1000, 512, 1408)]
+               (4096, 2304, 512), (1000, 512, 1408), (257, 384, 72), (5000, 4096, 256)]
+
+
+@pytest.fixture(params=[2, 1], ids=["cta_group2", "cta_group1"])
+def cta_group(request, env):
+    env["ctx"].call("fls_set_option", b"gemm_cta_group", request.param)
+    yield request.param
+    env["ctx"].call("fls_set_option", b"gemm_cta_group", 2)
 
 
 @pytest.mark.parametrize("M,N,K", GEMM_SHAPES)
-def test_gemm_store(env, M, N, K):
+def test_gemm_store(env, cta_group, M, N, K):
     dev, ctx = env["dev"], env["ctx"]
     a, b = _rand((M, K), 1.0, 1, dev), _rand((N, K), 0.05, 2, dev)
     c = torch.full((M, N), float("nan"), dtype=torch.float16, device=dev)
@@ -54,7 +61,7 @@ def test_gemm_store(env, M, N, K):
 
 
 @pytest.mark.parametrize("M,N,K", [(256, 512, 512), (130, 520, 200)])
-def test_gemm_residual_in_place(env, M, N, K):
+def test_gemm_residual_in_place(env, cta_group, M, N, K):
     dev, ctx = env["dev"], env["ctx"]
     a, b = _rand((M, K), 1.0, 3, dev), _rand((N, K), 0.05, 4, dev)
     x = _rand((M, N), 1.0, 5, dev)
@@ -67,7 +74,7 @@ def test_gemm_residual_in_place(env, M, N, K):
 
 
 @pytest.mark.parametrize("M,I,K", [(256, 1408, 512), (100, 136, 64)])
-def test_gemm_swiglu_matches_unfused(env, M, I, K):
+def test_gemm_swiglu_matches_unfused(env, cta_group, M, I, K):
     dev, ctx = env["dev"], env["ctx"]
     a = _rand((M, K), 1.0, 6, dev)
     wgu = _rand((2 * I, K), 0.05, 7, dev)            # gate rows then up rows, as laid out in a weight slot
