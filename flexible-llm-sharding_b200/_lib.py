@@ -14,7 +14,8 @@ import threading
 PKG_DIR = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(PKG_DIR, "csrc")
 LIB_PATH = os.path.join(CSRC, "libfls_b200.so")
-SOURCES = ["api.cu", "gemm_sm100.cu", "elementwise.cu", "attention.cu", "host_cache.cpp", "noalloc.cu"]
+SOURCES = ["api.cu", "gemm_sm100.cu", "elementwise.cu", "attention.cu", "attention_sm100.cu", "host_cache.cpp",
+           "noalloc.cu"]
 HEADERS = ["common.cuh", "ptx.cuh", "host_cache.h", os.path.join("..", "..", "include", "fls_b200.h")]
 NVCC_FLAGS = ["-shared", "-Xcompiler", "-fPIC", "-std=c++17", "-O3", "-lineinfo",
               "-gencode", "arch=compute_100a,code=sm_100a"]
@@ -92,7 +93,7 @@ _SIGNATURES = {
     "fls_op_gemm": (_I, [_P, _I, _P, _I, _P, _I, _I, _I, _I, _I, _P, _I, _P, _I, _I, _P]),
     "fls_op_rmsnorm": (_I, [_P, _P, _P, _P, _P, C.c_float, _I, _I, _P, _P, _P]),
     "fls_op_rope": (_I, [_P, _P, _I, _I, _I, _I, _I, _P, _P]),
-    "fls_op_attention": (_I, [_P, _P, _I, _I, _I, _I, _P, _I, _P, _I, _P]),
+    "fls_op_attention": (_I, [_P, _P, _I, _I, _I, _I, _I, _P, _I, _P, _I, _P]),
     "fls_op_swiglu": (_I, [_P, _P, _P, _I, _I, _I, _P, _I, _P]),
     "fls_op_embed": (_I, [_P, _P, _P, _I, _I, _P, _P]),
     "fls_op_head": (_I, [_P, _P, _P, _I, _I, _I, _P, _P, _I, _P, _P, _P]),

@@ -95,6 +95,7 @@ struct fls_ctx {
     bool cuda_poisoned = false;
     unsigned long long peer_enabled_mask = 0;
     int gemm_cg = 2;  // tcgen05 cta_group of the GEMM kernels (2 = CTA pairs, 1 = single CTA)
+    int attn_impl = 1;  // 1 = tcgen05 attention (head_dim 128), 0 = mma.sync attention
 };
 
 namespace {
@@ -241,6 +242,13 @@ inline cudaStream_t as_stream(void* s) { return reinterpret_cast<cudaStream_t>(s
 inline const __half* H(const uint16_t* p) { return reinterpret_cast<const __half*>(p); }
 inline __half* H(uint16_t* p) { return reinterpret_cast<__half*>(p); }
 
+int attention_dispatch(fls_ctx* c, const __half* qkv, int ld, int n_rows, int n_q_heads, int n_kv_heads, int head_dim,
+                       const AttnTile* tiles, int n_tiles, __half* out, int ld_out, cudaStream_t st) {
+    if (c->attn_impl == 1 && head_dim == 128)
+        return attention_sm100_launch(qkv, ld, n_rows, n_q_heads, n_kv_heads, tiles, n_tiles, out, ld_out, st);
+    return attention_launch(qkv, ld, n_q_heads, n_kv_heads, head_dim, tiles, n_tiles, out, ld_out, st);
+}
+
 int head_impl(fls_ctx* c, const __half* x, const __half* W, int n_rows, int V, int K, __half* probs,
               const int32_t* answer_ids, int n_ids, float* logprob, float* lse_out, cudaStream_t st) {
     if (n_rows > c->max_head_rows)
@@ -300,6 +308,7 @@ int fls_create(const fls_model_desc* d, int device, fls_ctx** out) {
                     prop.minor);
     FLS_TRY(gemm_init());
     FLS_TRY(attention_init());
+    FLS_TRY(attention_sm100_init());
     auto c = new fls_ctx();
     c->device = device;
     c->num_sms = prop.multiProcessorCount;
@@ -589,8 +598,9 @@ int fls_decoder_layer(fls_ctx* c, int slot, int layer_idx, uint16_t* x_dev, int 
     }
     {
         ProfScope ps(c, FLS_PROF_ATTENTION, 0, st);
-        CTX_TRY(c, attention_launch(c->qkv, c->qkv_dim, m.num_attention_heads, m.num_key_value_heads, m.head_dim,
-                                    reinterpret_cast<const AttnTile*>(tiles), n_tiles, c->attn, c->q_dim, st));
+        CTX_TRY(c, attention_dispatch(c, c->qkv, c->qkv_dim, n_rows, m.num_attention_heads, m.num_key_value_heads,
+                                      m.head_dim, reinterpret_cast<const AttnTile*>(tiles), n_tiles, c->attn,
+                                      c->q_dim, st));
     }
     a = GemmArgs{};
     a.A = c->attn, a.lda = c->q_dim, a.B = r->dec.wo, a.ldb = c->q_dim, a.b_rows = Hd;
@@ -702,11 +712,12 @@ int fls_op_rope(fls_ctx* c, uint16_t* qkv, int ld, int n_rows, int n_q_heads, in
     return kOk;
 }
 
-int fls_op_attention(fls_ctx* c, const uint16_t* qkv, int ld, int n_q_heads, int n_kv_heads, int head_dim,
+int fls_op_attention(fls_ctx* c, const uint16_t* qkv, int ld, int n_rows, int n_q_heads, int n_kv_heads, int head_dim,
                      const fls_attn_tile* tiles, int n_tiles, uint16_t* out, int ld_out, void* stream) {
     ENTER(c);
-    CTX_TRY(c, attention_launch(H(qkv), ld, n_q_heads, n_kv_heads, head_dim, reinterpret_cast<const AttnTile*>(tiles),
-                                n_tiles, H(out), ld_out, as_stream(stream)));
+    CTX_TRY(c, attention_dispatch(c, H(qkv), ld, n_rows, n_q_heads, n_kv_heads, head_dim,
+                                  reinterpret_cast<const AttnTile*>(tiles), n_tiles, H(out), ld_out,
+                                  as_stream(stream)));
     c->stats.kernel_launches += 1;
     return kOk;
 }
@@ -741,6 +752,11 @@ int fls_set_option(fls_ctx* c, const char* name, int value) {
     if (strcmp(name, "gemm_cta_group") == 0) {
         if (value != 1 && value != 2) return ctx_fail(c, fail(kErrInvalid, "gemm_cta_group must be 1 or 2"));
         c->gemm_cg = value;
+        return kOk;
+    }
+    if (strcmp(name, "attention_impl") == 0) {
+        if (value != 0 && value != 1) return ctx_fail(c, fail(kErrInvalid, "attention_impl must be 0 or 1"));
+        c->attn_impl = value;
         return kOk;
     }
     return ctx_fail(c, fail(kErrInvalid, "fls_set_option: unknown option '%s'", name));

@@ -8,10 +8,14 @@
 // segments (segment 0 = the prompt's prefix rows, shared by all options; segment 1 = the option's
 // own rows), GQA is a head-index mapping, and scores never leave the SM (online softmax).
 //
-//   prefix tile   seg0 = prefix rows, seg1 empty; causal = 0 reproduces the reference
-//                 (attention_mask=None => bidirectional prefix), causal = 1 gives a causal prefix.
-//   suffix tile   seg0 = prefix rows, seg1 = option rows, causal = 1 with q_seq0 = len_p + j0
-//                 == the reference's mask slice attention_mask[:, :, -len_s:, -len_p-len_s:].
+//   prefix tile   seg0 = prefix rows; mode 0 reproduces the reference (attention_mask=None =>
+//                 bidirectional prefix), mode 1 gives a causal prefix.
+//   suffix tile   mode 2: queries are the rows of one or more whole options (<= 128 rows); seg0 =
+//                 prefix rows (all visible), seg1 = those options' rows; a query sees the keys of its
+//                 own option at positions <= its own == the reference's mask slice
+//                 attention_mask[:, :, -len_s:, -len_p-len_s:] applied per option.
+// This file is the mma.sync (HMMA) implementation: head_dim 64, and the comparison kernel for the
+// tcgen05 version in attention_sm100.cu.
 //
 // Arithmetic: S = Q K^T in fp32 (tensor cores, fp16 inputs), scaled by d^-1/2, softmax in fp32,
 // P rounded to fp16 for the PV product (as HF's softmax(...).to(fp16) @ V), fp32 accumulation,
@@ -75,7 +79,12 @@ attention_kernel(const __half* __restrict__ qkv, int ld, int n_q_heads, int n_kv
     const uint32_t sK = sQ + BQ * D * 2;            // 2 stages
     const uint32_t sV = sK + 2 * TILE_BYTES;        // 2 stages
 
-    const AttnTile t = tiles[blockIdx.x];
+    AttnTile t = tiles[blockIdx.x];
+    // a tile holds up to 128 queries; this kernel takes them 64 at a time (blockIdx.z)
+    const int q_off = blockIdx.z * BQ;
+    if (q_off >= t.n_q) return;
+    t.q_row += q_off;
+    t.n_q = min(BQ, t.n_q - q_off);
     const int head = blockIdx.y;
     const int kvh = head / (n_q_heads / n_kv_heads);
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -85,8 +94,10 @@ attention_kernel(const __half* __restrict__ qkv, int ld, int n_q_heads, int n_kv
     const __half* k_base = qkv + static_cast<size_t>(n_q_heads + kvh) * D;
     const __half* v_base = qkv + static_cast<size_t>(n_q_heads + n_kv_heads + kvh) * D;
 
-    const int Lk_all = t.seg0_len + t.seg1_len;
-    const int Lk = t.causal ? min(Lk_all, t.q_seq0 + t.n_q) : Lk_all;  // keys any query of the tile can see
+    // keys any query of this block can see (concatenated index: segment 0, then segment 1)
+    const int Lk = t.mode == kAttnPrefixCausal ? min(t.seg0_len, t.q_seq0 + q_off + t.n_q)
+                   : t.mode == kAttnSuffix     ? t.seg0_len + t.seg1_len
+                                               : t.seg0_len;
     const int n_kv_tiles = (Lk + BK - 1) / BK;
 
     auto kv_row = [&](int key) { return key < t.seg0_len ? t.seg0_row + key : t.seg1_row + (key - t.seg0_len); };
@@ -131,7 +142,20 @@ attention_kernel(const __half* __restrict__ qkv, int ld, int n_q_heads, int n_kv
     for (int i = 0; i < D / 8; ++i) o[i][0] = o[i][1] = o[i][2] = o[i][3] = 0.f;
     float m_run[2] = {-INFINITY, -INFINITY};
     float l_run[2] = {0.f, 0.f};
-    const int qi0 = warp * 16 + g;  // this thread's rows inside the tile: qi0 and qi0 + 8
+    const int qi0 = warp * 16 + g;  // this thread's rows inside the block: qi0 and qi0 + 8
+    // visible key range of each of the two rows: [0, lim0) in segment 0, [lo1, hi1] in segment 1
+    int lim0[2], lo1[2], hi1[2];
+#pragma unroll
+    for (int r = 0; r < 2; ++r) {
+        const int qi = q_off + qi0 + r * 8;  // query index inside the whole tile
+        lim0[r] = t.mode == kAttnPrefixCausal ? min(t.seg0_len, t.q_seq0 + qi + 1) : t.seg0_len;
+        lo1[r] = 0, hi1[r] = -1;
+        if (t.mode == kAttnSuffix) {
+            const int qa = (t.q_row - q_off - t.seg1_row) + qi, L = t.q_seq0;
+            lo1[r] = (qa / L) * L;
+            hi1[r] = min(qa, t.seg1_len - 1);
+        }
+    }
 
     for (int kt = 0; kt < n_kv_tiles; ++kt) {
         const int stage = kt & 1;
@@ -160,8 +184,8 @@ attention_kernel(const __half* __restrict__ qkv, int ld, int n_q_heads, int n_kv
 #pragma unroll
             for (int e = 0; e < 4; ++e) {
                 const int key = kt * BK + nt * 8 + 2 * tq + (e & 1);
-                const int qi = qi0 + (e >> 1) * 8;
-                const bool vis = key < Lk_all && (!t.causal || key <= t.q_seq0 + qi);
+                const int r = e >> 1, k1 = key - t.seg0_len;
+                const bool vis = key < t.seg0_len ? key < lim0[r] : (k1 >= lo1[r] && k1 <= hi1[r]);
                 s[nt][e] = vis ? s[nt][e] * scale_log2e : -INFINITY;
                 mx[e >> 1] = fmaxf(mx[e >> 1], s[nt][e]);
             }
@@ -264,7 +288,7 @@ int attention_launch(const __half* qkv, int ld, int n_q_heads, int n_kv_heads, i
     if (ld % 8 || ld_out % 8) return fail(kErrInvalid, "attention: row strides must be multiples of 8");
     if (n_kv_heads <= 0 || n_q_heads % n_kv_heads) return fail(kErrInvalid, "attention: heads %d / kv heads %d", n_q_heads, n_kv_heads);
     const float scale_log2e = 1.4426950408889634f / sqrtf(static_cast<float>(head_dim));
-    const dim3 grid(n_tiles, n_q_heads);
+    const dim3 grid(n_tiles, n_q_heads, 2);
     if (head_dim == 128)
         attention_kernel<128><<<grid, ATT_THREADS, att_smem_bytes<128>(), s>>>(qkv, ld, n_q_heads, n_kv_heads, tiles,
                                                                               out, ld_out, scale_log2e);

@@ -1,0 +1,282 @@
+// Shared-prefix prefill attention on tcgen05 / TMEM / TMA (head_dim 128).
+//
+// Same contract as attention.cu (see there and include/fls_b200.h: fls_attn_tile); replaces the
+// reference's two eager attention calls per layer (reference utils.py:272 and :275-279).
+//
+// One CTA = one query tile (<= 128 rows) x one head, 192 threads:
+//   warp 0      TMA producer: Q tile once (2 x [128 x 64] sub-tiles, 128B swizzle), then K/V tiles of
+//               64 keys (K and V each 2 x [64 x 64] sub-tiles) through a 2-stage ring.  A key tile
+//               never straddles the two key segments (prefix rows / option rows).
+//   warp 1      MMA issuer (one elected thread):  S = Q K^T  (tcgen05.mma M128 N64 K16 x 8, K-major
+//               operands) into TMEM columns [0,64);  O += P V (M128 N128 K16 x 4, A = P K-major, B = V
+//               MN-major exactly as it lies in memory - no transpose) into TMEM columns [128,256).
+//   warps 2-5   softmax, one query row per thread: tcgen05.ld S, mask, online softmax in fp32
+//               (base-2), P rounded to fp16 (as HF's softmax(..).to(fp16) @ V) and written with the
+//               128B swizzle over the K tile it came from (K is dead once S is complete), O row
+//               rescaled in TMEM only when the running max grows by more than 2^8, final O / l.
+// Ordering rests on the tensor pipe executing MMAs in issue order: when `s_full` of tile j fires,
+// PV of tile j-1 has retired, so O and the P buffer of the other stage are stable.
+// Shared memory: Q 32 KiB + 2 stages x 32 KiB = 96 KiB -> two CTAs per SM, whose softmax and MMA
+// phases overlap; TMEM: 256 columns per CTA.
+#include <cuda.h>
+
+#include "common.cuh"
+#include "ptx.cuh"
+
+namespace fls {
+
+namespace {
+
+constexpr int D = 128;
+constexpr int BQ = 128;
+constexpr int BKV = 64;
+constexpr int KV_STAGES = 2;
+constexpr int Q_BYTES = BQ * D * 2;                  // 32 KiB: two [128 x 64] sub-tiles
+constexpr int KSUB_BYTES = BKV * 64 * 2;             // 8 KiB: one [64 keys x 64 d] sub-tile
+constexpr int STAGE_BYTES = 4 * KSUB_BYTES;          // K sub0, K sub1, V sub0, V sub1
+constexpr int SMEM_BYTES = Q_BYTES + KV_STAGES * STAGE_BYTES + 256 + 1024;
+constexpr int THREADS = 192;
+constexpr int TMEM_COLS = 256;
+constexpr int S_COL = 0, O_COL = 128;
+constexpr float RESCALE_THRESHOLD = 8.0f;  // log2 units
+
+__global__ void __launch_bounds__(THREADS, 2)
+attention_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant__ CUtensorMap tmap_kv,
+                         int n_q_heads, int n_kv_heads, const AttnTile* __restrict__ tiles, __half* __restrict__ out,
+                         int ld_out, float scale_log2e) {
+    extern __shared__ uint8_t smem_raw[];
+    uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+    uint8_t* sQ = smem;
+    uint8_t* sKV = smem + Q_BYTES;
+    uint64_t* q_full = reinterpret_cast<uint64_t*>(smem + Q_BYTES + KV_STAGES * STAGE_BYTES);
+    uint64_t* kv_full = q_full + 1;
+    uint64_t* kv_empty = kv_full + KV_STAGES;
+    uint64_t* s_full = kv_empty + KV_STAGES;
+    uint64_t* p_ready = s_full + 1;
+    uint64_t* o_full = p_ready + 1;
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(o_full + 1);
+
+    const int warp_idx = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const AttnTile t = tiles[blockIdx.x];
+    const int head = blockIdx.y;
+    const int kvh = head / (n_q_heads / n_kv_heads);
+    const int q_col = head * D;
+    const int k_col = (n_q_heads + kvh) * D;
+    const int v_col = (n_q_heads + n_kv_heads + kvh) * D;
+
+    // key tiles: segment 0 first (only up to the diagonal for a causal prefix tile), then segment 1
+    const int seg0_keys = t.mode == kAttnPrefixCausal ? min(t.seg0_len, t.q_seq0 + t.n_q) : t.seg0_len;
+    const int n0 = (seg0_keys + BKV - 1) / BKV;
+    const int n1 = t.mode == kAttnSuffix ? (t.seg1_len + BKV - 1) / BKV : 0;
+    const int n_tiles = n0 + n1;
+
+    if (warp_idx == 0) {
+        if (ptx::elect_one()) {
+            ptx::prefetch_tensormap(&tmap_q);
+            ptx::prefetch_tensormap(&tmap_kv);
+            ptx::mbar_init(q_full, 1);
+            for (int i = 0; i < KV_STAGES; ++i) {
+                ptx::mbar_init(&kv_full[i], 1);
+                ptx::mbar_init(&kv_empty[i], 1);
+            }
+            ptx::mbar_init(s_full, 1);
+            ptx::mbar_init(p_ready, 4);  // one arrive per softmax warp
+            ptx::mbar_init(o_full, 1);
+            ptx::fence_mbar_init();
+        }
+        __syncwarp();
+        ptx::tmem_alloc<1>(tmem_slot, TMEM_COLS);
+        ptx::tmem_relinquish<1>();
+    }
+    ptx::tc_fence_before_sync();
+    __syncthreads();
+    ptx::tc_fence_after_sync();
+    const uint32_t tmem_base = *tmem_slot;
+
+    if (warp_idx == 0) {
+        // ------------------------------------------------------------------ TMA producer
+        if (ptx::elect_one()) {
+            ptx::mbar_arrive_expect_tx(q_full, Q_BYTES);
+            ptx::tma_load_2d(sQ, &tmap_q, q_full, q_col, t.q_row);
+            ptx::tma_load_2d(sQ + Q_BYTES / 2, &tmap_q, q_full, q_col + 64, t.q_row);
+            for (int j = 0; j < n_tiles; ++j) {
+                const int stage = j % KV_STAGES;
+                ptx::mbar_wait(&kv_empty[stage], ((j / KV_STAGES) & 1) ^ 1);
+                const int row = j < n0 ? t.seg0_row + j * BKV : t.seg1_row + (j - n0) * BKV;
+                uint8_t* st = sKV + stage * STAGE_BYTES;
+                ptx::mbar_arrive_expect_tx(&kv_full[stage], STAGE_BYTES);
+                ptx::tma_load_2d(st, &tmap_kv, &kv_full[stage], k_col, row);
+                ptx::tma_load_2d(st + KSUB_BYTES, &tmap_kv, &kv_full[stage], k_col + 64, row);
+                ptx::tma_load_2d(st + 2 * KSUB_BYTES, &tmap_kv, &kv_full[stage], v_col, row);
+                ptx::tma_load_2d(st + 3 * KSUB_BYTES, &tmap_kv, &kv_full[stage], v_col + 64, row);
+            }
+        }
+    } else if (warp_idx == 1) {
+        // ------------------------------------------------------------------ MMA issuer
+        if (ptx::elect_one()) {
+            constexpr uint32_t idesc_qk = ptx::umma_idesc_f16_f32(BQ, BKV);
+            constexpr uint32_t idesc_pv = ptx::umma_idesc_f16_f32(BQ, D) | ptx::kUmmaBMajorMN;
+            const uint32_t q_addr = ptx::smem_u32(sQ);
+            ptx::mbar_wait(q_full, 0);
+            for (int j = 0; j < n_tiles; ++j) {
+                const int stage = j % KV_STAGES;
+                const uint32_t st = ptx::smem_u32(sKV + stage * STAGE_BYTES);
+                ptx::mbar_wait(&kv_full[stage], (j / KV_STAGES) & 1);
+                ptx::tc_fence_after_sync();
+                // S = Q K^T : d = 128 -> 8 K-steps, 4 per 64-wide sub-tile
+#pragma unroll
+                for (int k = 0; k < D / 16; ++k) {
+                    const uint64_t da = ptx::umma_smem_desc_sw128(q_addr + (k / 4) * (Q_BYTES / 2)) + 2 * (k % 4);
+                    const uint64_t db = ptx::umma_smem_desc_sw128(st + (k / 4) * KSUB_BYTES) + 2 * (k % 4);
+                    ptx::umma_f16<1>(tmem_base + S_COL, da, db, idesc_qk, k != 0);
+                }
+                ptx::umma_commit(s_full);
+                // O += P V : P (fp16, K-major) now lies where K was; V is MN-major as loaded
+                ptx::mbar_wait(p_ready, j & 1);
+                ptx::tc_fence_after_sync();
+#pragma unroll
+                for (int k = 0; k < BKV / 16; ++k) {
+                    const uint64_t da = ptx::umma_smem_desc_sw128(st) + 2 * k;
+                    const uint64_t db =
+                        ptx::umma_smem_desc_sw128_mn(st + 2 * KSUB_BYTES + k * 16 * 128, KSUB_BYTES, 1024);
+                    ptx::umma_f16<1>(tmem_base + O_COL, da, db, idesc_pv, (j | k) != 0);
+                }
+                ptx::umma_commit(&kv_empty[stage]);
+            }
+            ptx::umma_commit(o_full);
+        }
+    } else {
+        // ------------------------------------------------------------------ softmax (warps 2..5)
+        const int quarter = warp_idx & 3;             // TMEM lanes [32*quarter, +32) belong to this warp
+        const int i = quarter * 32 + lane;            // query row inside the tile
+        const uint32_t lane_addr = tmem_base + (static_cast<uint32_t>(quarter * 32) << 16);
+        // visible key ranges of this row, per segment
+        const int lim0 = t.mode == kAttnPrefixCausal ? min(t.seg0_len, t.q_seq0 + i + 1) : t.seg0_len;
+        int lo1 = 0, hi1 = -1;
+        if (t.mode == kAttnSuffix) {
+            const int qa = (t.q_row - t.seg1_row) + i, L = t.q_seq0;
+            lo1 = (qa / L) * L;
+            hi1 = min(qa, t.seg1_len - 1);           // own option, positions <= own
+        }
+        float m_run = -INFINITY, l_run = 0.f;
+        for (int j = 0; j < n_tiles; ++j) {
+            const int stage = j % KV_STAGES;
+            ptx::mbar_wait(s_full, j & 1);
+            ptx::tc_fence_after_sync();
+            uint32_t sr[2][32];
+            ptx::tmem_ld_32x32(lane_addr + S_COL, sr[0]);
+            ptx::tmem_ld_32x32(lane_addr + S_COL + 32, sr[1]);
+            ptx::tmem_ld_wait();
+            const bool in0 = j < n0;
+            const int kbase = in0 ? j * BKV : (j - n0) * BKV;
+            const int lo = in0 ? 0 : lo1, hi = in0 ? lim0 - 1 : hi1;
+            float x[64];
+            float mx = -INFINITY;
+#pragma unroll
+            for (int c = 0; c < 64; ++c) {
+                const int key = kbase + c;
+                const bool vis = key >= lo && key <= hi;
+                x[c] = vis ? __uint_as_float(sr[c >> 5][c & 31]) * scale_log2e : -INFINITY;
+                mx = fmaxf(mx, x[c]);
+            }
+            // lazy rescale: keep the old reference max unless the new one is much larger
+            float m_new = m_run;
+            if (mx > m_run + RESCALE_THRESHOLD) m_new = mx;
+            const bool changed = m_new != m_run;
+            const float m_use = m_new == -INFINITY ? 0.f : m_new;
+            const float alpha = changed ? exp2f(m_run - m_use) : 1.f;   // m_run = -inf -> 0
+            m_run = m_new;
+            float sum = 0.f;
+            uint32_t pk[32];
+#pragma unroll
+            for (int c = 0; c < 64; c += 2) {
+                const float p0 = exp2f(x[c] - m_use), p1 = exp2f(x[c + 1] - m_use);
+                sum += p0 + p1;
+                const __half2 h = __floats2half2_rn(p0, p1);
+                pk[c >> 1] = *reinterpret_cast<const uint32_t*>(&h);
+            }
+            l_run = l_run * alpha + sum;
+            // rescale this row of O (TMEM) if any row of the warp moved its reference max
+            if (j > 0 && __any_sync(0xffffffffu, changed)) {
+#pragma unroll 1
+                for (int c = 0; c < D / 32; ++c) {
+                    uint32_t o[32];
+                    ptx::tmem_ld_32x32(lane_addr + O_COL + c * 32, o);
+                    ptx::tmem_ld_wait();
+#pragma unroll
+                    for (int e = 0; e < 32; ++e) o[e] = __float_as_uint(__uint_as_float(o[e]) * alpha);
+                    ptx::tmem_st_32x32(lane_addr + O_COL + c * 32, o);
+                }
+                ptx::tmem_st_wait();
+            }
+            // P -> shared memory over the (dead) K tile: [128 rows][64 keys] fp16, 128B swizzle
+            uint8_t* sp = sKV + stage * STAGE_BYTES + i * 128;
+#pragma unroll
+            for (int c = 0; c < 8; ++c)
+                *reinterpret_cast<uint4*>(sp + ((c ^ (i & 7)) << 4)) =
+                    make_uint4(pk[c * 4], pk[c * 4 + 1], pk[c * 4 + 2], pk[c * 4 + 3]);
+            ptx::fence_proxy_async_smem();   // generic-proxy writes -> visible to the tensor core's async proxy
+            ptx::tc_fence_before_sync();
+            __syncwarp();
+            if (lane == 0) ptx::mbar_arrive(p_ready);
+        }
+        // ---- epilogue: O / l -> fp16 -> global
+        ptx::mbar_wait(o_full, 0);
+        ptx::tc_fence_after_sync();
+        const float inv = l_run > 0.f ? 1.f / l_run : 0.f;
+        __half* dst = out + static_cast<size_t>(t.q_row + i) * ld_out + head * D;
+#pragma unroll 1
+        for (int c = 0; c < D / 32; ++c) {
+            uint32_t o[32];
+            ptx::tmem_ld_32x32(lane_addr + O_COL + c * 32, o);
+            ptx::tmem_ld_wait();
+            if (i < t.n_q) {
+#pragma unroll
+                for (int v = 0; v < 4; ++v) {
+                    uint32_t w[4];
+#pragma unroll
+                    for (int e = 0; e < 4; ++e) {
+                        const __half2 h = __floats2half2_rn(__uint_as_float(o[v * 8 + e * 2]) * inv,
+                                                            __uint_as_float(o[v * 8 + e * 2 + 1]) * inv);
+                        w[e] = *reinterpret_cast<const uint32_t*>(&h);
+                    }
+                    *reinterpret_cast<uint4*>(dst + c * 32 + v * 8) = make_uint4(w[0], w[1], w[2], w[3]);
+                }
+            }
+        }
+    }
+
+    ptx::tc_fence_before_sync();
+    __syncwarp();
+    __syncthreads();
+    if (warp_idx == 0) {
+        ptx::tc_fence_after_sync();
+        ptx::tmem_dealloc<1>(tmem_base, TMEM_COLS);
+    }
+}
+
+}  // namespace
+
+int attention_sm100_init() {
+    FLS_CUDA(cudaFuncSetAttribute(attention_tcgen05_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_BYTES));
+    return kOk;
+}
+
+int attention_sm100_launch(const __half* qkv, int ld, int n_rows, int n_q_heads, int n_kv_heads, const AttnTile* tiles,
+                           int n_tiles, __half* out, int ld_out, cudaStream_t s) {
+    if (n_tiles <= 0) return kOk;
+    if (ld_out % 8) return fail(kErrInvalid, "attention: ld_out must be a multiple of 8");
+    if (n_kv_heads <= 0 || n_q_heads % n_kv_heads)
+        return fail(kErrInvalid, "attention: heads %d / kv heads %d", n_q_heads, n_kv_heads);
+    CUtensorMap tq, tkv;
+    const int cols = (n_q_heads + 2 * n_kv_heads) * D;
+    FLS_TRY(encode_tmap_2d(&tq, qkv, n_rows, cols, ld, BQ));
+    FLS_TRY(encode_tmap_2d(&tkv, qkv, n_rows, cols, ld, BKV));
+    const float scale_log2e = 1.4426950408889634f / sqrtf(static_cast<float>(D));
+    attention_tcgen05_kernel<<<dim3(n_tiles, n_q_heads), THREADS, SMEM_BYTES, s>>>(tq, tkv, n_q_heads, n_kv_heads, tiles,
+                                                                                  out, ld_out, scale_log2e);
+    FLS_CUDA(cudaGetLastError());
+    return kOk;
+}
+
+}  // namespace fls

@@ -5,6 +5,8 @@
 #include <cuda_fp16.h>
 #include <cuda_runtime.h>
 
+struct CUtensorMap_st;  // <cuda.h>
+
 namespace fls {
 
 // ---- error plumbing: every internal launcher returns 0 or a negative fls status and leaves a
@@ -79,19 +81,28 @@ int gather_logprob_launch(const __half* x, int ldx, const __half* W, int ldw, in
                           const float* lse, int n_rows, float* out, cudaStream_t s);
 
 // ---- attention (attention.cu) ------------------------------------------------------------------
-// One descriptor per (query tile); see include/fls_b200.h fls_attn_tile.
+// One descriptor per query tile; see include/fls_b200.h fls_attn_tile.
+enum AttnMode : int32_t { kAttnPrefix = 0, kAttnPrefixCausal = 1, kAttnSuffix = 2 };
 struct AttnTile {
     int32_t q_row;     // first query row (packed row index)
-    int32_t n_q;       // queries in this tile (<= 64)
-    int32_t q_seq0;    // sequence index of the first query (key t visible iff t <= q_seq0 + i) ...
-    int32_t causal;    // ... when causal != 0; otherwise every key of both segments is visible
+    int32_t n_q;       // queries in this tile (<= 128)
+    int32_t q_seq0;    // mode 1: sequence index of the first query; mode 2: option length (len_s)
+    int32_t mode;      // AttnMode
     int32_t seg0_row;  // first key/value row of segment 0 (the prompt's prefix rows)
     int32_t seg0_len;
-    int32_t seg1_row;  // first key/value row of segment 1 (the option's own rows); len may be 0
-    int32_t seg1_len;
+    int32_t seg1_row;  // mode 2: first row of the (whole) options the queries belong to
+    int32_t seg1_len;  //         rows of those options that can be visible to the tile
 };
 int attention_launch(const __half* qkv, int ld, int n_q_heads, int n_kv_heads, int head_dim, const AttnTile* tiles,
                      int n_tiles, __half* out, int ld_out, cudaStream_t s);
 int attention_init();
+// tcgen05 version (head_dim 128); n_rows = rows of the qkv buffer (bounds the TMA tensor map)
+int attention_sm100_launch(const __half* qkv, int ld, int n_rows, int n_q_heads, int n_kv_heads, const AttnTile* tiles,
+                           int n_tiles, __half* out, int ld_out, cudaStream_t s);
+int attention_sm100_init();
+
+// TMA descriptor over a row-major fp16 matrix [rows, cols] (row stride ld), box = 64 columns x box_rows,
+// 128-byte swizzle (gemm_sm100.cu).
+int encode_tmap_2d(::CUtensorMap_st* tm, const __half* base, int rows, int cols, int ld, int box_rows);
 
 }  // namespace fls

@@ -422,6 +422,11 @@ int set_smem_attr() {
 
 int gemm_lse_blocks(int N) { return (N + BLOCK_N - 1) / BLOCK_N; }
 
+int encode_tmap_2d(::CUtensorMap_st* tm, const __half* base, int rows, int cols, int ld, int box_rows) {
+    if (!g_encode) return fail(kErrState, "gemm_init() has not run");
+    return make_tmap(tm, base, rows, cols, ld, box_rows);
+}
+
 int gemm_init() {
     if (!g_encode) {
         void* fn = nullptr;

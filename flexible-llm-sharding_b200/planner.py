@@ -17,7 +17,7 @@ from dataclasses import dataclass, field
 import numpy as np
 
 MAX_TOKEN_LEN = 4096     # reference utils.py:14
-ATTN_TILE_Q = 64         # queries per attention tile (csrc/attention.cu BQ)
+ATTN_TILE_Q = 128        # max queries per attention tile (csrc/attention_sm100.cu BQ)
 
 
 def shard_plan(n_layers_total: int, layer_num_per_shard: int, data_parallel: bool,
@@ -114,14 +114,32 @@ class PackedPrompts:
     def total_head_rows(self): return int(self.head_row[-1])
 
 
+ATTN_PREFIX, ATTN_PREFIX_CAUSAL, ATTN_SUFFIX = 0, 1, 2
+
+
 def prompt_tiles(base: int, len_p: int, S: int, len_s: int, prefix_causal: bool) -> list[list[int]]:
+    """Attention tiles of one prompt whose rows start at `base` (include/fls_b200.h: fls_attn_tile).
+    Prefix rows: tiles of <= 128 queries over the prefix keys.  Option rows: as many whole options
+    as fit 128 rows share one tile (their common prefix keys are then read once); an option longer
+    than 128 rows is cut into 128-row tiles that see the option's rows up to their own last query."""
+    Q = ATTN_TILE_Q
     t = []
-    for q0 in range(0, len_p, ATTN_TILE_Q):
-        t.append([base + q0, min(ATTN_TILE_Q, len_p - q0), q0, int(prefix_causal), base, len_p, 0, 0])
-    for s in range(S):
-        srow = base + len_p + s * len_s
-        for j0 in range(0, len_s, ATTN_TILE_Q):
-            t.append([srow + j0, min(ATTN_TILE_Q, len_s - j0), len_p + j0, 1, base, len_p, srow, len_s])
+    mode = ATTN_PREFIX_CAUSAL if prefix_causal else ATTN_PREFIX
+    for q0 in range(0, len_p, Q):
+        t.append([base + q0, min(Q, len_p - q0), q0, mode, base, len_p, 0, 0])
+    first = base + len_p
+    if len_s <= Q:
+        per_tile = max(1, Q // len_s)
+        for s0 in range(0, S, per_tile):
+            n_opt = min(per_tile, S - s0)
+            row = first + s0 * len_s
+            t.append([row, n_opt * len_s, len_s, ATTN_SUFFIX, base, len_p, row, n_opt * len_s])
+    else:
+        for s in range(S):
+            row = first + s * len_s
+            for j0 in range(0, len_s, Q):
+                n_q = min(Q, len_s - j0)
+                t.append([row + j0, n_q, len_s, ATTN_SUFFIX, base, len_p, row, j0 + n_q])
     return t
 
 

@@ -58,19 +58,28 @@ typedef struct fls_model_desc {
 #define FLS_LAYER_NORM 2    /* model.norm.safetensors */
 #define FLS_LAYER_HEAD 3    /* lm_head.safetensors */
 
-/* One attention query tile (<= 64 consecutive query rows of one prompt part); built by the host
+/* One attention query tile (<= 128 consecutive query rows of one prompt); built by the host
  * scheduler.  Replaces the reference's per-prompt kv_cache expand + mask slice (utils.py:275-277).
- * Key t of the concatenated segments (seg0 then seg1) is visible to query i of the tile iff
- * `!causal || t <= q_seq0 + i`. */
+ * Keys/values are read in place from the packed qkv rows: segment 0 = the prompt's prefix rows
+ * (shared by every option), segment 1 = the rows of the options the queries belong to.
+ *   mode 0  prefix queries, every prefix key visible   (reference prefix pass: attention_mask=None,
+ *           utils.py:272)
+ *   mode 1  prefix queries, causal: key t visible iff t <= q_seq0 + i (q_seq0 = index of the first query)
+ *   mode 2  option queries: the tile covers rows of whole options of length q_seq0 (= len_s) that
+ *           start at seg1_row; a query sees all prefix keys and the keys of its own option at
+ *           positions <= its own (== the mask slice of utils.py:276 with position offset len_p). */
+#define FLS_ATTN_PREFIX 0
+#define FLS_ATTN_PREFIX_CAUSAL 1
+#define FLS_ATTN_SUFFIX 2
 typedef struct fls_attn_tile {
     int32_t q_row;    /* first query row */
-    int32_t n_q;      /* 1..64 */
-    int32_t q_seq0;   /* sequence index of the first query */
-    int32_t causal;   /* 0: all keys visible (reference prefix pass, utils.py:272); 1: causal */
+    int32_t n_q;      /* 1..128 */
+    int32_t q_seq0;   /* mode 1: sequence index of the first query; mode 2: option length */
+    int32_t mode;     /* FLS_ATTN_* */
     int32_t seg0_row; /* key/value rows of the shared prefix */
     int32_t seg0_len;
-    int32_t seg1_row; /* key/value rows of the option itself (len 0 for prefix tiles) */
-    int32_t seg1_len;
+    int32_t seg1_row; /* mode 2: first row of the covered options */
+    int32_t seg1_len; /*         rows of those options that can be visible to the tile */
 } fls_attn_tile;
 
 typedef struct fls_stats {
@@ -173,8 +182,11 @@ int fls_op_rmsnorm(fls_ctx* ctx, const uint16_t* x_dev, const uint16_t* delta_de
                    void* stream);
 int fls_op_rope(fls_ctx* ctx, uint16_t* qkv_dev, int ld, int n_rows, int n_q_heads, int n_kv_heads, int head_dim,
                 const int32_t* row_pos_dev, void* stream);
-int fls_op_attention(fls_ctx* ctx, const uint16_t* qkv_dev, int ld, int n_q_heads, int n_kv_heads, int head_dim,
-                     const fls_attn_tile* tiles_dev, int n_tiles, uint16_t* out_dev, int ld_out, void* stream);
+/* n_rows = rows of the qkv buffer.  head_dim 128 runs the tcgen05 kernel (option "attention_impl" = 1,
+ * default) or the mma.sync kernel (0); head_dim 64 always the latter. */
+int fls_op_attention(fls_ctx* ctx, const uint16_t* qkv_dev, int ld, int n_rows, int n_q_heads, int n_kv_heads,
+                     int head_dim, const fls_attn_tile* tiles_dev, int n_tiles, uint16_t* out_dev, int ld_out,
+                     void* stream);
 int fls_op_swiglu(fls_ctx* ctx, const uint16_t* gate_dev, const uint16_t* up_dev, int ld_in, int n_rows, int inter,
                   uint16_t* out_dev, int ld_out, void* stream);
 int fls_op_embed(fls_ctx* ctx, const uint16_t* table_dev, const int32_t* ids_dev, int n_rows, int hidden,
@@ -227,7 +239,8 @@ int fls_set_profiling(fls_ctx* ctx, int enabled);
 int fls_get_profile(fls_ctx* ctx, fls_kernel_profile* out);
 
 /* Tuning knobs.  "gemm_cta_group": 2 (default; CTA pairs share a 256x256 tile through
- * tcgen05 cta_group::2) or 1 (one CTA per 128x256 tile). */
+ * tcgen05 cta_group::2) or 1 (one CTA per 128x256 tile).  "attention_impl": 1 (default; tcgen05
+ * kernel for head_dim 128) or 0 (mma.sync kernel). */
 int fls_set_option(fls_ctx* ctx, const char* name, int value);
 
 int fls_get_stats(fls_ctx* ctx, fls_stats* out);

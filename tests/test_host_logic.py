@@ -48,7 +48,7 @@ def _tok(shapes, seed=0):
 
 
 def test_pack_prompts_layout_and_tiles():
-    shapes = [(70, 3, 9), (1, 2, 5), (129, 4, 33), (64, 1, 64), (200, 2, 70)]
+    shapes = [(70, 3, 9), (1, 2, 5), (129, 4, 33), (64, 1, 64), (200, 2, 70), (30, 2, 150)]
     tok = _tok(shapes)
     packed = planner.pack_prompts(tok, max_rows=400, max_head_rows=6, prefix_causal=False)
     assert packed.total_rows == sum(lp + S * ls for lp, S, ls in shapes)
@@ -61,15 +61,18 @@ def test_pack_prompts_layout_and_tiles():
     covered = np.zeros(packed.total_rows, dtype=int)
     for mb in packed.micro_batches:
         assert mb.n_rows <= 400 and mb.n_head <= 6
-        for q_row, n_q, q_seq0, causal, s0r, s0l, s1r, s1l in mb.tiles:
+        for q_row, n_q, q_seq0, mode, s0r, s0l, s1r, s1l in mb.tiles:
             assert 1 <= n_q <= planner.ATTN_TILE_Q
             covered[mb.row_lo + q_row: mb.row_lo + q_row + n_q] += 1
-            # rotary position of a query == its sequence index used for the causal rule
-            assert packed.row_pos[mb.row_lo + q_row] == q_seq0
-            if s1l:      # option tile: causal, own rows follow the prefix in sequence order
-                assert causal == 1 and q_seq0 >= s0l and s1r <= q_row < s1r + s1l
+            if mode == planner.ATTN_SUFFIX:
+                L = q_seq0                         # option length; whole options start at s1r
+                assert (q_row - s1r) >= 0 and s1r >= s0r + s0l and (s1r - (s0r + s0l)) % L == 0
+                assert s1l >= (q_row - s1r) + n_q  # every query's own position is among the visible rows
+                for i in (0, n_q - 1):             # rotary position == len_p + position inside the option
+                    assert packed.row_pos[mb.row_lo + q_row + i] == s0l + ((q_row - s1r) + i) % L
             else:
-                assert causal == 0 and s0r <= q_row < s0r + s0l
+                assert mode == planner.ATTN_PREFIX and s0r <= q_row < s0r + s0l and s1l == 0
+                assert packed.row_pos[mb.row_lo + q_row] == q_seq0
         for j, g in enumerate(mb.gather):
             assert 0 <= g < mb.n_rows
     assert (covered == 1).all()                              # every row is a query exactly once

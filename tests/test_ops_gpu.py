@@ -156,15 +156,16 @@ def test_embed_exact(env):
     assert torch.equal(out, table[ids.long()])
 
 
-@pytest.mark.parametrize("nq,nkv,d", [(4, 4, 128), (4, 2, 128), (8, 2, 64)])
+@pytest.mark.parametrize("nq,nkv,d,impl", [(4, 4, 128, 1), (4, 2, 128, 1), (4, 2, 128, 0), (8, 2, 64, 0)])
 @pytest.mark.parametrize("prefix_causal", [False, True])
-def test_attention_matches_oracle(env, nq, nkv, d, prefix_causal):
+def test_attention_matches_oracle(env, nq, nkv, d, impl, prefix_causal):
     """Prefix + shared-prefix suffix attention for several prompts against the oracle's eager
     attention (softmax in fp32, probabilities rounded to fp16, GQA by repeat_kv)."""
     from oracle import llama_oracle as O
     dev, ctx, planner = env["dev"], env["ctx"], env["planner"]
-    shapes = [(70, 3, 9), (1, 2, 5), (129, 4, 33), (64, 1, 64), (200, 2, 70)]      # (len_p, S, len_s)
-    rows = sum(lp + S * ls for lp, S, ls in shapes)
+    shapes = [(70, 3, 9), (1, 2, 5), (129, 4, 33), (64, 1, 64), (200, 2, 70), (384, 4, 32), (30, 2, 150)]
+    rows = sum(lp + S * ls for lp, S, ls in shapes)                                   # (len_p, S, len_s)
+    ctx.call("fls_set_option", b"attention_impl", impl)
     ld = (nq + 2 * nkv) * d
     qkv = _rand((rows, ld), 1.0, 13, dev)
     tiles, base = [], 0
@@ -173,8 +174,10 @@ def test_attention_matches_oracle(env, nq, nkv, d, prefix_causal):
         base += lp + S * ls
     t = torch.tensor(tiles, dtype=torch.int32, device=dev)
     out = torch.full((rows, nq * d), float("nan"), dtype=torch.float16, device=dev)
-    ctx.call("fls_op_attention", qkv.data_ptr(), ld, nq, nkv, d, t.data_ptr(), len(tiles), out.data_ptr(), nq * d, _sp())
+    ctx.call("fls_op_attention", qkv.data_ptr(), ld, rows, nq, nkv, d, t.data_ptr(), len(tiles), out.data_ptr(), nq * d,
+             _sp())
     torch.cuda.synchronize()
+    ctx.call("fls_set_option", b"attention_impl", 1)
     assert torch.isfinite(out).all()
 
     q_all, k_all, v_all = qkv.cpu().float().split([nq * d, nkv * d, nkv * d], dim=1)
