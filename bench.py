@@ -113,16 +113,17 @@ class ClockSampler:
                 "reasons": sorted(reasons), "samples": len(sm)}
 
 
-def model_dir_for(shape_name: str, rank: int, world: int, device) -> str:
+def model_dir_for(shape_name: str, rank: int, world: int, device, alias_layers: int = 0) -> str:
     """Random-init layer files in prepare_weights.py's layout (written once per box, rank 0)."""
     base = os.environ.get("FLS_BENCH_DIR") or ("/dev/shm" if os.path.isdir("/dev/shm") else tempfile.gettempdir())
-    d = os.path.join(base, f"fls_bench_{shape_name}")
+    d = os.path.join(base, f"fls_bench_{shape_name}" + (f"_alias{alias_layers}" if alias_layers else ""))
     done = os.path.join(d, ".complete")
     if rank == 0 and not os.path.exists(done):
         shutil.rmtree(d, ignore_errors=True)
         shape = synthetic.LlamaShape.named(shape_name)
         synthetic.write_layer_files(d, shape, seed=0, init_std=0.02,
-                                    device=str(device) if torch.cuda.is_available() else "cpu")
+                                    device=str(device) if torch.cuda.is_available() else "cpu",
+                                    alias_decoder_layers=alias_layers)
         open(done, "w").close()
     if world > 1:
         torch.distributed.barrier()
@@ -167,6 +168,46 @@ def cpu_oracle_rate(model_path: str, prompts, n_layers_full: int, sample_prompts
     return sample_prompts / full, dict(t_1layer_s=ts[0], t_2layer_s=ts[1], extrapolated_full_pass_s=full)
 
 
+def bench_model_parallel(a, shape_name, shape, n_prompts, prefix_tokens, n_options, option_tokens, alias,
+                         workload_name, pk):
+    """Layer pipeline over all visible GPUs of ONE process (the reference's default multi-GPU mode,
+    main.py:71-73): shard j on GPU j mod G, activations handed GPU-to-GPU over NVLink.  Steps are
+    whole passes through main.score_all (public API, strings in / numpy out), timed on the host."""
+    import __graft_entry__ as ge
+    ge.build()
+    from flexible_llm_sharding_b200.main import score_all
+    G = torch.cuda.device_count()
+    devices = [f"cuda:{i}" for i in range(G)]
+    md = model_dir_for(shape_name, 0, 1, torch.device("cuda:0"), alias)
+    prompts = synthetic.make_prompts(n_prompts, shape.vocab_size, prefix_tokens, n_options, option_tokens, seed=1234)
+    args = make_args(md, layer_num_per_shard=a.layer_num_per_shard, storage_location="gpu", max_rows=a.max_rows)
+    for _ in range(a.warmup):
+        out = score_all(args, copy.deepcopy(prompts), devices)
+    for d in devices:
+        torch.cuda.synchronize(d)
+    with ClockSampler(0) as clocks:
+        t0 = time.perf_counter()
+        for _ in range(a.steps):
+            out = score_all(args, copy.deepcopy(prompts), devices)
+        for d in devices:
+            torch.cuda.synchronize(d)
+        dt = time.perf_counter() - t0
+    assert len(out) == n_prompts
+    v = n_prompts * a.steps / dt
+    rows_per_prompt = prefix_tokens + n_options * option_tokens
+    print(json.dumps({
+        "metric": "prompts/sec (layer-sharded prompt scoring)", "value": v, "unit": "prompts/s", "n_gpus": G,
+        "steps": a.steps, "warmup": a.warmup, "ms_per_step": 1e3 * dt / a.steps, "higher_is_better": True,
+        "scaling": "strong", "vs_baseline": None, "dtype": "f16 (fp32 accumulate)", "data": "synthetic",
+        "config": {"workload": workload_name + (f" [{alias} distinct decoder layers, others aliased]" if alias else ""),
+                   "parallelism": f"mp{G}: layer pipeline, shard j on GPU j mod {G}, NVLink peer hand-off",
+                   "timing": "host wall clock around main.score_all (includes ShardedLlama construction per pass, "
+                             "tokenisation, D2H of the scores)"},
+        "prefill_tok_per_s": v * rows_per_prompt, "clocks": clocks.summary(),
+        "e2e": {"value": v, "unit": "prompts/s"},
+    }))
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
@@ -181,6 +222,10 @@ def main():
     ap.add_argument("--cpu_sample_prompts", type=int, default=8)
     ap.add_argument("--no_cpu_baseline", action="store_true")
     ap.add_argument("--no_e2e", action="store_true")
+    ap.add_argument("--alias_layers", type=int, default=-1,
+                    help="write only N distinct decoder layers and symlink the rest (default: 4 for 70b, else 0)")
+    ap.add_argument("--parallel", default="dp", choices=["dp", "mp"],
+                    help="mp: ONE process drives all visible GPUs as a layer pipeline (not under torchrun)")
     a = ap.parse_args()
 
     rank = int(os.environ.get("RANK", "0"))
@@ -190,6 +235,7 @@ def main():
     if a.prompts:
         n_prompts = a.prompts
     shape = synthetic.LlamaShape.named(shape_name)
+    alias = a.alias_layers if a.alias_layers >= 0 else (4 if shape_name == "70b" else 0)
     rows_per_prompt = prefix_tokens + n_options * option_tokens
     workload_name = (f"Llama-2-{shape_name} arch random-init fp16, layer_num_per_shard={a.layer_num_per_shard}, "
                      f"storage_location={a.storage_location}, {n_prompts} prompts x {rows_per_prompt} token rows "
@@ -200,7 +246,7 @@ def main():
     if a.impl == "reference":
         if rank != 0:
             return
-        md = model_dir_for(shape_name, 0, 1, "cpu")
+        md = model_dir_for(shape_name, 0, 1, "cpu", 0 if shape_name != "70b" else alias)
         prompts = synthetic.make_prompts(max(a.cpu_sample_prompts, 1), shape.vocab_size, prefix_tokens, n_options,
                                          option_tokens, seed=1234)
         vals = []
@@ -238,7 +284,10 @@ def main():
     from flexible_llm_sharding_b200 import planner
     from flexible_llm_sharding_b200.utils import DeviceManager, ShardedLlama
 
-    md = model_dir_for(shape_name, rank, world, device)
+    if a.parallel == "mp":
+        return bench_model_parallel(a, shape_name, shape, n_prompts, prefix_tokens, n_options, option_tokens, alias,
+                                    workload_name, pk)
+    md = model_dir_for(shape_name, rank, world, device, alias)
     prompts = synthetic.make_prompts(n_prompts, shape.vocab_size, prefix_tokens, n_options, option_tokens,
                                      seed=1234 + rank)
     args = make_args(md, layer_num_per_shard=a.layer_num_per_shard, storage_location=a.storage_location,
@@ -359,7 +408,8 @@ def main():
         "n_gpus": world, "steps": a.steps, "warmup": a.warmup, "ms_per_step": 1e3 * dt / a.steps,
         "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f16 (fp32 accumulate)",
         "data": "synthetic",
-        "config": {"workload": workload_name, "micro_batch_rows": a.max_rows,
+        "config": {"workload": workload_name + (f" [{alias} distinct decoder layers, others aliased]" if alias else ""),
+                   "micro_batch_rows": a.max_rows,
                    "cache": "inputs larger than L2 (activations %.1f GB, weights %.1f GB per step)" % (
                        rows * shape.hidden_size * 2 / 1e9, stats.h2d_bytes / a.steps / 1e9),
                    "parallelism": f"dp{world} (independent prompt partitions, no collective)"},

@@ -11,6 +11,8 @@
 #include <sys/stat.h>
 #include <unistd.h>
 #include <cerrno>
+#include <climits>
+#include <cstdlib>
 
 #include <algorithm>
 #include <atomic>
@@ -242,7 +244,13 @@ int parse_safetensors_header(const std::string& path, std::vector<TensorEntry>* 
     return kOk;
 }
 
-int acquire_host_image(const std::string& path, std::shared_ptr<HostLayerImage>* out) {
+int acquire_host_image(const std::string& path_in, std::shared_ptr<HostLayerImage>* out) {
+    // key by the resolved path: symlinked layer files share one pinned image
+    std::string path = path_in;
+    if (char* rp = realpath(path_in.c_str(), nullptr)) {
+        path = rp;
+        free(rp);
+    }
     {
         std::lock_guard<std::mutex> lk(g_mu);
         auto it = g_cache.find(path);

@@ -72,8 +72,8 @@ class TokenizedPrompt:
     def rows(self): return self.len_p + self.n_options * self.len_s
 
 
-def tokenize_prompts(tokenizer, prompts) -> list[TokenizedPrompt]:
-    """utils.py:246-258 for every prompt up front (the reference tokenises inside the GPU loop)."""
+def tokenize_prompts_serial(tokenizer, prompts) -> list[TokenizedPrompt]:
+    """utils.py:246-258 literally: two tokenizer calls per prompt (kept as the checked-against form)."""
     out = []
     pad = tokenizer.pad_token_id
     for prefix, suffixes in prompts:
@@ -84,6 +84,34 @@ def tokenize_prompts(tokenizer, prompts) -> list[TokenizedPrompt]:
         eos = (s != pad).sum(1) - 1
         out.append(TokenizedPrompt(np.ascontiguousarray(p, dtype=np.int32),
                                    np.ascontiguousarray(s, dtype=np.int32), eos.astype(np.int64)))
+    return out
+
+
+def tokenize_prompts(tokenizer, prompts) -> list[TokenizedPrompt]:
+    """Same result as `tokenize_prompts_serial`, but every prefix and every option goes through the
+    tokenizer in two batched calls (the Rust tokenizers parallelise a batch over the host cores; the
+    reference tokenises one prompt at a time inside its GPU loop, utils.py:246-258).  Padding is
+    redone per prompt: options are right-padded with the pad id to the prompt's longest option and
+    the leading (BOS) column is dropped, exactly what `padding=True` followed by `[:, 1:]` yields."""
+    prompts = list(prompts)
+    if not prompts:
+        return []
+    pad = tokenizer.pad_token_id
+    kw = dict(return_attention_mask=False, truncation=True, max_length=MAX_TOKEN_LEN)
+    pre = tokenizer([p for p, _ in prompts], **kw)["input_ids"]
+    flat = tokenizer([s for _, ss in prompts for s in ss], **kw)["input_ids"]
+    out, k = [], 0
+    for i, (_, ss) in enumerate(prompts):
+        S = len(ss)
+        opts = flat[k:k + S]
+        k += S
+        width = max(len(o) for o in opts)
+        s = np.full((S, width), pad, dtype=np.int32)
+        for j, o in enumerate(opts):
+            s[j, :len(o)] = o
+        s = np.ascontiguousarray(s[:, 1:])
+        eos = (s != pad).sum(1) - 1
+        out.append(TokenizedPrompt(np.asarray(pre[i], dtype=np.int32), s, eos.astype(np.int64)))
     return out
 
 

@@ -221,10 +221,14 @@ class ShardedLlama:
         src = out["probs"] if want_probs else out["lp"]
         if return_device:
             return src, 0
-        host = torch.empty(src.shape, dtype=src.dtype).pin_memory()
-        host.copy_(src, non_blocking=True)
+        # page-locked result buffer, kept across calls (pinning 262 MB costs ~0.1 s)
+        key = (tuple(src.shape), src.dtype)
+        if getattr(self, "_host_out_key", None) != key:
+            self._host_out = torch.empty(src.shape, dtype=src.dtype).pin_memory()
+            self._host_out_key = key
+        self._host_out.copy_(src, non_blocking=True)
         stream.synchronize()
-        return host.numpy(), host.numel() * host.element_size()
+        return self._host_out.numpy().copy(), src.numel() * src.element_size()
 
     def run(self, inputs, want_probs=True, answer_ids=None, packed=None, return_device=False):
         shards, num_gpu, rank, dp = self._plan()

@@ -107,6 +107,23 @@ def test_tokenize_matches_oracle(tiny):
         assert g.suffix_eos.tolist() == e.tolist()
 
 
+def test_batched_tokenisation_equals_per_prompt_tokenisation(tiny):
+    from transformers import AutoTokenizer
+    from flexible_llm_sharding_b200 import synthetic
+    tok = AutoTokenizer.from_pretrained(tiny["layer_dir"])
+    tok.pad_token = tok.eos_token
+    tok.padding_side = "right"
+    prompts = synthetic.make_prompts(9, 1000, 30, 3, 11, seed=3, ragged=True) + [("w5", ("w6", "w7 w8 w9", ""))]
+    a = planner.tokenize_prompts(tok, prompts)
+    b = planner.tokenize_prompts_serial(tok, prompts)
+    assert len(a) == len(b)
+    for x, y in zip(a, b):
+        assert x.prefix_ids.tolist() == y.prefix_ids.tolist()
+        assert x.suffix_ids.tolist() == y.suffix_ids.tolist() and x.suffix_ids.dtype == np.int32
+        assert x.suffix_eos.tolist() == y.suffix_eos.tolist()
+    assert a[-1].suffix_eos.tolist() == [0, 2, -1]          # an empty option: index -1, wraps like the reference
+
+
 def test_cabi_library_exports_every_declared_symbol():
     """No compute: the library must load on a CPU box and export exactly what the header declares."""
     import __graft_entry__ as ge
