@@ -96,6 +96,7 @@ struct fls_ctx {
     unsigned long long peer_enabled_mask = 0;
     int gemm_cg = 2;  // tcgen05 cta_group of the GEMM kernels (2 = CTA pairs, 1 = single CTA)
     int attn_impl = 1;  // 1 = tcgen05 attention (head_dim 128), 0 = mma.sync attention
+    int fuse_rope = 1;  // 1 = rotary embedding in the QKV GEMM epilogue (head_dim 128), 0 = separate kernel
 };
 
 namespace {
@@ -587,11 +588,18 @@ int fls_decoder_layer(fls_ctx* c, int slot, int layer_idx, uint16_t* x_dev, int 
     GemmArgs a{};
     a.A = c->xn, a.lda = Hd, a.B = r->dec.wqkv, a.ldb = Hd, a.b_rows = c->qkv_dim;
     a.M = n_rows, a.N = c->qkv_dim, a.K = Hd, a.C = c->qkv, a.ldc = c->qkv_dim;
+    const bool fused_rope = c->fuse_rope && m.head_dim == 128;
     {
         ProfScope ps(c, FLS_PROF_GEMM_QKV, 2.0 * R * c->qkv_dim * Hd, st);
-        CTX_TRY(c, gemm_launch(kEpiStore, a, c->num_sms, st, c->gemm_cg));
+        if (fused_rope) {
+            a.row_pos = row_pos, a.cos_tab = c->rope_cos, a.sin_tab = c->rope_sin;
+            a.rope_cols = c->q_dim + c->kv_dim;
+            CTX_TRY(c, gemm_launch(kEpiStoreRope, a, c->num_sms, st, c->gemm_cg));
+        } else {
+            CTX_TRY(c, gemm_launch(kEpiStore, a, c->num_sms, st, c->gemm_cg));
+        }
     }
-    {
+    if (!fused_rope) {
         ProfScope ps(c, FLS_PROF_ROPE, R * (c->q_dim + c->kv_dim) * 4.0, st);
         CTX_TRY(c, rope_launch(c->qkv, c->qkv_dim, n_rows, m.num_attention_heads, m.num_key_value_heads, m.head_dim,
                                row_pos, c->rope_cos, c->rope_sin, c->rope_n_pos, st));
@@ -629,7 +637,7 @@ int fls_decoder_layer(fls_ctx* c, int slot, int layer_idx, uint16_t* x_dev, int 
         ProfScope ps(c, FLS_PROF_GEMM_DOWN, 2.0 * R * Hd * I, st);
         CTX_TRY(c, gemm_launch(kEpiResidual, a, c->num_sms, st, c->gemm_cg));
     }
-    c->stats.kernel_launches += 8;
+    c->stats.kernel_launches += fused_rope ? 7 : 8;
     return kOk;
 }
 
@@ -752,6 +760,10 @@ int fls_set_option(fls_ctx* c, const char* name, int value) {
     if (strcmp(name, "gemm_cta_group") == 0) {
         if (value != 1 && value != 2) return ctx_fail(c, fail(kErrInvalid, "gemm_cta_group must be 1 or 2"));
         c->gemm_cg = value;
+        return kOk;
+    }
+    if (strcmp(name, "fuse_rope") == 0) {
+        c->fuse_rope = value != 0;
         return kOk;
     }
     if (strcmp(name, "attention_impl") == 0) {

@@ -43,6 +43,7 @@ enum GemmEpilogue : int {
     kEpiSwiGLU = 2,      // C[M,N] = fp16(silu(fp16(acc_gate))) * fp16(acc_up); B rows [0,N) = gate, [up_off, up_off+N) = up
     kEpiLsePartial = 3,  // partial[row, n_blk] = (max, sum exp) of fp16(acc) over the tile's columns
     kEpiProbs = 4,       // C = fp16(exp(fp16(acc) - lse[row]))
+    kEpiStoreRope = 5,   // C = fp16(acc), with HF rotary embedding applied to the 128-wide heads in columns [0, rope_cols)
 };
 
 struct GemmArgs {
@@ -59,6 +60,11 @@ struct GemmArgs {
     float2* partial;  // [M, ceil(N/256)]
     const float* lse;  // [M]
     int up_off;
+    // kEpiStoreRope: rotary position of every row and the fp16 cos/sin tables [n_pos, 128]
+    const int32_t* row_pos;
+    const __half* cos_tab;
+    const __half* sin_tab;
+    int rope_cols;
 };
 int gemm_launch(GemmEpilogue epi, const GemmArgs& a, int num_sms, cudaStream_t stream, int cta_group = 2);
 int gemm_init();  // resolves cuTensorMapEncodeTiled and opts kernels into large dynamic smem

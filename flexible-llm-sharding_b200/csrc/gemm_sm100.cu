@@ -62,6 +62,10 @@ struct KParams {
     const float* lse;
     int up_off;
     int num_m_blocks, num_n_blocks;
+    const int32_t* row_pos;
+    const __half* cos_tab;
+    const __half* sin_tab;
+    int rope_cols;
 };
 
 template <int EPI>
@@ -263,6 +267,58 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_con
                         }
                     }
                 }
+            } else if constexpr (EPI == kEpiStoreRope) {
+                // q/k heads (128 columns each, two per tile): HF apply_rotary_pos_emb on the fp16-rounded
+                // projection, half-split convention, every product and the sum rounded on their own
+                // (bit-identical to rope_kernel).  Columns >= rope_cols (the v heads) are stored as is.
+                const int pos = row_ok ? p.row_pos[row] : 0;
+#pragma unroll 1
+                for (int h = 0; h < BLOCK_N / 128; ++h) {
+                    const int hcol = col0 + h * 128;
+                    const bool rotate = hcol < p.rope_cols;
+#pragma unroll 1
+                    for (int c = 0; c < 2; ++c) {
+                        uint32_t a[32], b[32];  // dims [c*32, +32) and their partners [64 + c*32, +32)
+                        ptx::tmem_ld_32x32(taddr + h * 128 + c * 32, a);
+                        ptx::tmem_ld_32x32(taddr + h * 128 + 64 + c * 32, b);
+                        ptx::tmem_ld_wait();
+                        if (row_ok && hcol < p.N) {
+                            __half* dst = p.C + static_cast<size_t>(row) * p.ldc + hcol + c * 32;
+                            const __half* ct = p.cos_tab + static_cast<size_t>(pos) * 128 + c * 32;
+                            const __half* st = p.sin_tab + static_cast<size_t>(pos) * 128 + c * 32;
+#pragma unroll
+                            for (int v = 0; v < 4; ++v) {
+                                uint4 c1 = make_uint4(0, 0, 0, 0), s1 = c1, c2 = c1, s2 = c1;
+                                if (rotate) {
+                                    c1 = *reinterpret_cast<const uint4*>(ct + v * 8);
+                                    s1 = *reinterpret_cast<const uint4*>(st + v * 8);
+                                    c2 = *reinterpret_cast<const uint4*>(ct + 64 + v * 8);
+                                    s2 = *reinterpret_cast<const uint4*>(st + 64 + v * 8);
+                                }
+                                const __half2* hc1 = reinterpret_cast<const __half2*>(&c1);
+                                const __half2* hs1 = reinterpret_cast<const __half2*>(&s1);
+                                const __half2* hc2 = reinterpret_cast<const __half2*>(&c2);
+                                const __half2* hs2 = reinterpret_cast<const __half2*>(&s2);
+                                uint32_t o1[4], o2[4];
+#pragma unroll
+                                for (int j = 0; j < 4; ++j) {
+                                    const int i = v * 8 + j * 2;
+                                    __half2 x1 = __floats2half2_rn(__uint_as_float(a[i]), __uint_as_float(a[i + 1]));
+                                    __half2 x2 = __floats2half2_rn(__uint_as_float(b[i]), __uint_as_float(b[i + 1]));
+                                    if (rotate) {
+                                        const __half2 r1 = __hadd2_rn(__hmul2_rn(x1, hc1[j]), __hmul2_rn(__hneg2(x2), hs1[j]));
+                                        const __half2 r2 = __hadd2_rn(__hmul2_rn(x2, hc2[j]), __hmul2_rn(x1, hs2[j]));
+                                        x1 = r1, x2 = r2;
+                                    }
+                                    o1[j] = *reinterpret_cast<const uint32_t*>(&x1);
+                                    o2[j] = *reinterpret_cast<const uint32_t*>(&x2);
+                                }
+                                *reinterpret_cast<uint4*>(dst + v * 8) = make_uint4(o1[0], o1[1], o1[2], o1[3]);
+                                *reinterpret_cast<uint4*>(dst + 64 + v * 8) = make_uint4(o2[0], o2[1], o2[2], o2[3]);
+                            }
+                        }
+                    }
+                }
             } else if constexpr (EPI == kEpiLsePartial) {
                 // running (max, sum exp) over this tile's columns of the fp16-rounded logits
                 float m_run = -INFINITY, s_run = 0.f;
@@ -384,6 +440,7 @@ int launch_t(const GemmArgs& a, int num_sms, cudaStream_t stream) {
     p.M = a.M, p.N = a.N, p.K = a.K;
     p.C = a.C, p.ldc = a.ldc, p.R = a.R, p.ldr = a.ldr;
     p.partial = a.partial, p.lse = a.lse, p.up_off = a.up_off;
+    p.row_pos = a.row_pos, p.cos_tab = a.cos_tab, p.sin_tab = a.sin_tab, p.rope_cols = a.rope_cols;
     p.num_m_blocks = (a.M + BLOCK_M * CG - 1) / (BLOCK_M * CG);
     p.num_n_blocks = (a.N + OUT_COLS - 1) / OUT_COLS;
     const int tiles = p.num_m_blocks * p.num_n_blocks;
@@ -441,6 +498,7 @@ int gemm_init() {
     FLS_TRY(set_smem_attr<kEpiSwiGLU>());
     FLS_TRY(set_smem_attr<kEpiLsePartial>());
     FLS_TRY(set_smem_attr<kEpiProbs>());
+    FLS_TRY(set_smem_attr<kEpiStoreRope>());
     return kOk;
 }
 
@@ -464,6 +522,10 @@ int gemm_launch(GemmEpilogue epi, const GemmArgs& a, int num_sms, cudaStream_t s
         case kEpiProbs:
             if (!a.lse) return fail(kErrInvalid, "gemm: probs epilogue needs lse");
             return launch_cg<kEpiProbs>(a, num_sms, cta_group, stream);
+        case kEpiStoreRope:
+            if (!a.row_pos || !a.cos_tab || !a.sin_tab || a.rope_cols % 128 || a.N % 128)
+                return fail(kErrInvalid, "gemm: rope epilogue needs positions, tables and 128-wide heads");
+            return launch_cg<kEpiStoreRope>(a, num_sms, cta_group, stream);
     }
     return fail(kErrInvalid, "gemm: unknown epilogue %d", static_cast<int>(epi));
 }

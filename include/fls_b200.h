@@ -240,7 +240,8 @@ int fls_get_profile(fls_ctx* ctx, fls_kernel_profile* out);
 
 /* Tuning knobs.  "gemm_cta_group": 2 (default; CTA pairs share a 256x256 tile through
  * tcgen05 cta_group::2) or 1 (one CTA per 128x256 tile).  "attention_impl": 1 (default; tcgen05
- * kernel for head_dim 128) or 0 (mma.sync kernel). */
+ * kernel for head_dim 128) or 0 (mma.sync kernel).  "fuse_rope": 1 (default; rotary embedding applied in the
+ * QKV GEMM epilogue when head_dim is 128) or 0 (separate kernel). */
 int fls_set_option(fls_ctx* ctx, const char* name, int value);
 
 int fls_get_stats(fls_ctx* ctx, fls_stats* out);

@@ -101,6 +101,24 @@ def test_schedule_does_not_change_scores(tiny, k, storage, num_batch, max_rows, 
         assert not [f for f in os.listdir(tmp_path / "act") if f.endswith(".npy")]      # cleaned up
 
 
+def test_kernel_variants_give_identical_scores(tiny_gqa):
+    """RoPE in the QKV epilogue vs the stand-alone kernel, and cta_group 1 vs 2 GEMMs, are the same
+    arithmetic: bit-identical scores.  tcgen05 vs mma.sync attention differ only in summation order."""
+    from flexible_llm_sharding_b200.utils import DeviceManager, ShardedLlama
+    args = make_args(tiny_gqa["layer_dir"])
+    model = ShardedLlama(args, DeviceManager(args, ["cuda:0"]), device="cuda:0")
+    base = model(copy.deepcopy(tiny_gqa["prompts"]))
+    for opt, val in [(b"fuse_rope", 0), (b"gemm_cta_group", 1)]:
+        model.ctx.call("fls_set_option", opt, val)
+        out = model(copy.deepcopy(tiny_gqa["prompts"]))
+        model.ctx.call("fls_set_option", opt, 1 if opt == b"fuse_rope" else 2)
+        for a, b in zip(out, base):
+            assert np.array_equal(a, b), opt
+    model.ctx.call("fls_set_option", b"attention_impl", 0)
+    out = model(copy.deepcopy(tiny_gqa["prompts"]))
+    check_against_reference(out, tiny_gqa["golden"]["probs32_ref"])
+
+
 def test_fused_answer_token_logprobs(tiny):
     """lm_head + log-softmax + gather without the full-vocabulary output."""
     model, out = run_model(tiny)
