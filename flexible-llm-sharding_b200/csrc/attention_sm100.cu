@@ -14,8 +14,8 @@
 //               (base-2), P rounded to fp16 (as HF's softmax(..).to(fp16) @ V) and written with the
 //               128B swizzle over the K tile it came from (K is dead once S is complete), O row
 //               rescaled in TMEM only when the running max grows by more than 2^8, final O / l.
-// Ordering rests on the tensor pipe executing MMAs in issue order: when `s_full` of tile j fires,
-// PV of tile j-1 has retired, so O and the P buffer of the other stage are stable.
+// S is double buffered: Q K^T of tile j+1 is issued before P V of tile j, so it runs while the
+// softmax warps work on tile j.  `pv_done` tells the softmax warps when O may be rescaled/read.
 // Shared memory: Q 32 KiB + 2 stages x 32 KiB = 96 KiB -> two CTAs per SM, whose softmax and MMA
 // phases overlap; TMEM: 256 columns per CTA.
 #include <cuda.h>
@@ -37,7 +37,7 @@ constexpr int STAGE_BYTES = 4 * KSUB_BYTES;          // K sub0, K sub1, V sub0, 
 constexpr int SMEM_BYTES = Q_BYTES + KV_STAGES * STAGE_BYTES + 256 + 1024;
 constexpr int THREADS = 192;
 constexpr int TMEM_COLS = 256;
-constexpr int S_COL = 0, O_COL = 128;
+constexpr int S_COL = 0, O_COL = 128;  // S: two buffers of 64 columns at 0 and 64; O: 128 columns
 constexpr float RESCALE_THRESHOLD = 8.0f;  // log2 units
 
 __global__ void __launch_bounds__(THREADS, 2)
@@ -51,10 +51,10 @@ attention_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_q, const __gri
     uint64_t* q_full = reinterpret_cast<uint64_t*>(smem + Q_BYTES + KV_STAGES * STAGE_BYTES);
     uint64_t* kv_full = q_full + 1;
     uint64_t* kv_empty = kv_full + KV_STAGES;
-    uint64_t* s_full = kv_empty + KV_STAGES;
-    uint64_t* p_ready = s_full + 1;
-    uint64_t* o_full = p_ready + 1;
-    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(o_full + 1);
+    uint64_t* s_full = kv_empty + KV_STAGES;   // [2]: S buffer b = tile & 1 is complete
+    uint64_t* p_ready = s_full + 2;
+    uint64_t* pv_done = p_ready + 1;           // O += P V of a tile has retired
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(pv_done + 1);
 
     const int warp_idx = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const AttnTile t = tiles[blockIdx.x];
@@ -79,9 +79,10 @@ attention_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_q, const __gri
                 ptx::mbar_init(&kv_full[i], 1);
                 ptx::mbar_init(&kv_empty[i], 1);
             }
-            ptx::mbar_init(s_full, 1);
+            ptx::mbar_init(&s_full[0], 1);
+            ptx::mbar_init(&s_full[1], 1);
             ptx::mbar_init(p_ready, 4);  // one arrive per softmax warp
-            ptx::mbar_init(o_full, 1);
+            ptx::mbar_init(pv_done, 1);
             ptx::fence_mbar_init();
         }
         __syncwarp();
@@ -118,20 +119,27 @@ attention_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_q, const __gri
             constexpr uint32_t idesc_pv = ptx::umma_idesc_f16_f32(BQ, D) | ptx::kUmmaBMajorMN;
             const uint32_t q_addr = ptx::smem_u32(sQ);
             ptx::mbar_wait(q_full, 0);
-            for (int j = 0; j < n_tiles; ++j) {
+            // S(j) = Q K(j)^T into S buffer j & 1: d = 128 -> 8 K-steps, 4 per 64-wide sub-tile
+            auto issue_qk = [&](int j) {
                 const int stage = j % KV_STAGES;
                 const uint32_t st = ptx::smem_u32(sKV + stage * STAGE_BYTES);
                 ptx::mbar_wait(&kv_full[stage], (j / KV_STAGES) & 1);
                 ptx::tc_fence_after_sync();
-                // S = Q K^T : d = 128 -> 8 K-steps, 4 per 64-wide sub-tile
 #pragma unroll
                 for (int k = 0; k < D / 16; ++k) {
                     const uint64_t da = ptx::umma_smem_desc_sw128(q_addr + (k / 4) * (Q_BYTES / 2)) + 2 * (k % 4);
                     const uint64_t db = ptx::umma_smem_desc_sw128(st + (k / 4) * KSUB_BYTES) + 2 * (k % 4);
-                    ptx::umma_f16<1>(tmem_base + S_COL, da, db, idesc_qk, k != 0);
+                    ptx::umma_f16<1>(tmem_base + S_COL + (j & 1) * BKV, da, db, idesc_qk, k != 0);
                 }
-                ptx::umma_commit(s_full);
-                // O += P V : P (fp16, K-major) now lies where K was; V is MN-major as loaded
+                ptx::umma_commit(&s_full[j & 1]);
+            };
+            if (n_tiles > 0) issue_qk(0);
+            for (int j = 0; j < n_tiles; ++j) {
+                // the next tile's scores are computed while the softmax warps work on this one
+                if (j + 1 < n_tiles) issue_qk(j + 1);
+                const int stage = j % KV_STAGES;
+                const uint32_t st = ptx::smem_u32(sKV + stage * STAGE_BYTES);
+                // O += P V : P (fp16, K-major) now lies where K(j) was; V is MN-major as loaded
                 ptx::mbar_wait(p_ready, j & 1);
                 ptx::tc_fence_after_sync();
 #pragma unroll
@@ -142,8 +150,8 @@ attention_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_q, const __gri
                     ptx::umma_f16<1>(tmem_base + O_COL, da, db, idesc_pv, (j | k) != 0);
                 }
                 ptx::umma_commit(&kv_empty[stage]);
+                ptx::umma_commit(pv_done);
             }
-            ptx::umma_commit(o_full);
         }
     } else {
         // ------------------------------------------------------------------ softmax (warps 2..5)
@@ -158,56 +166,67 @@ attention_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_q, const __gri
             lo1 = (qa / L) * L;
             hi1 = min(qa, t.seg1_len - 1);           // own option, positions <= own
         }
+        // running reference max m_run is kept in RAW score units; p = exp2(s * c - m_run * c), c = scale * log2(e)
         float m_run = -INFINITY, l_run = 0.f;
+        const float thr = RESCALE_THRESHOLD / scale_log2e;
         for (int j = 0; j < n_tiles; ++j) {
             const int stage = j % KV_STAGES;
-            ptx::mbar_wait(s_full, j & 1);
+            ptx::mbar_wait(&s_full[j & 1], (j >> 1) & 1);
             ptx::tc_fence_after_sync();
             uint32_t sr[2][32];
-            ptx::tmem_ld_32x32(lane_addr + S_COL, sr[0]);
-            ptx::tmem_ld_32x32(lane_addr + S_COL + 32, sr[1]);
+            ptx::tmem_ld_32x32(lane_addr + S_COL + (j & 1) * BKV, sr[0]);
+            ptx::tmem_ld_32x32(lane_addr + S_COL + (j & 1) * BKV + 32, sr[1]);
             ptx::tmem_ld_wait();
             const bool in0 = j < n0;
             const int kbase = in0 ? j * BKV : (j - n0) * BKV;
             const int lo = in0 ? 0 : lo1, hi = in0 ? lim0 - 1 : hi1;
-            float x[64];
+            // masking only where a row of this warp has an invisible key in the tile (warp-uniform branch)
+            if (__any_sync(0xffffffffu, kbase < lo || kbase + BKV - 1 > hi)) {
+#pragma unroll
+                for (int c = 0; c < 64; ++c) {
+                    const int key = kbase + c;
+                    if (key < lo || key > hi) sr[c >> 5][c & 31] = 0xff800000u;  // -inf
+                }
+            }
             float mx = -INFINITY;
 #pragma unroll
-            for (int c = 0; c < 64; ++c) {
-                const int key = kbase + c;
-                const bool vis = key >= lo && key <= hi;
-                x[c] = vis ? __uint_as_float(sr[c >> 5][c & 31]) * scale_log2e : -INFINITY;
-                mx = fmaxf(mx, x[c]);
-            }
+            for (int c = 0; c < 64; ++c) mx = fmaxf(mx, __uint_as_float(sr[c >> 5][c & 31]));
             // lazy rescale: keep the old reference max unless the new one is much larger
             float m_new = m_run;
-            if (mx > m_run + RESCALE_THRESHOLD) m_new = mx;
+            if (mx > m_run + thr) m_new = mx;
             const bool changed = m_new != m_run;
             const float m_use = m_new == -INFINITY ? 0.f : m_new;
-            const float alpha = changed ? exp2f(m_run - m_use) : 1.f;   // m_run = -inf -> 0
+            const float alpha = changed ? exp2f((m_run - m_use) * scale_log2e) : 1.f;   // m_run = -inf -> 0
             m_run = m_new;
+            const float mc = m_use * scale_log2e;
             float sum = 0.f;
             uint32_t pk[32];
 #pragma unroll
             for (int c = 0; c < 64; c += 2) {
-                const float p0 = exp2f(x[c] - m_use), p1 = exp2f(x[c + 1] - m_use);
+                const float p0 = exp2f(fmaf(__uint_as_float(sr[c >> 5][c & 31]), scale_log2e, -mc));
+                const float p1 = exp2f(fmaf(__uint_as_float(sr[(c + 1) >> 5][(c + 1) & 31]), scale_log2e, -mc));
                 sum += p0 + p1;
                 const __half2 h = __floats2half2_rn(p0, p1);
                 pk[c >> 1] = *reinterpret_cast<const uint32_t*>(&h);
             }
             l_run = l_run * alpha + sum;
-            // rescale this row of O (TMEM) if any row of the warp moved its reference max
-            if (j > 0 && __any_sync(0xffffffffu, changed)) {
+            if (j > 0) {
+                // O is touched by the tensor core until P V of the previous tile has retired
+                ptx::mbar_wait(pv_done, (j - 1) & 1);
+                ptx::tc_fence_after_sync();
+                // rescale this row of O (TMEM) if any row of the warp moved its reference max
+                if (__any_sync(0xffffffffu, changed)) {
 #pragma unroll 1
-                for (int c = 0; c < D / 32; ++c) {
-                    uint32_t o[32];
-                    ptx::tmem_ld_32x32(lane_addr + O_COL + c * 32, o);
-                    ptx::tmem_ld_wait();
+                    for (int c = 0; c < D / 32; ++c) {
+                        uint32_t o[32];
+                        ptx::tmem_ld_32x32(lane_addr + O_COL + c * 32, o);
+                        ptx::tmem_ld_wait();
 #pragma unroll
-                    for (int e = 0; e < 32; ++e) o[e] = __float_as_uint(__uint_as_float(o[e]) * alpha);
-                    ptx::tmem_st_32x32(lane_addr + O_COL + c * 32, o);
+                        for (int e = 0; e < 32; ++e) o[e] = __float_as_uint(__uint_as_float(o[e]) * alpha);
+                        ptx::tmem_st_32x32(lane_addr + O_COL + c * 32, o);
+                    }
+                    ptx::tmem_st_wait();
                 }
-                ptx::tmem_st_wait();
             }
             // P -> shared memory over the (dead) K tile: [128 rows][64 keys] fp16, 128B swizzle
             uint8_t* sp = sKV + stage * STAGE_BYTES + i * 128;
@@ -221,7 +240,7 @@ attention_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_q, const __gri
             if (lane == 0) ptx::mbar_arrive(p_ready);
         }
         // ---- epilogue: O / l -> fp16 -> global
-        ptx::mbar_wait(o_full, 0);
+        if (n_tiles > 0) ptx::mbar_wait(pv_done, (n_tiles - 1) & 1);
         ptx::tc_fence_after_sync();
         const float inv = l_run > 0.f ? 1.f / l_run : 0.f;
         __half* dst = out + static_cast<size_t>(t.q_row + i) * ld_out + head * D;
