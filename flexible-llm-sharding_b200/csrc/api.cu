@@ -246,7 +246,7 @@ inline __half* H(uint16_t* p) { return reinterpret_cast<__half*>(p); }
 int attention_dispatch(fls_ctx* c, const __half* qkv, int ld, int n_rows, int n_q_heads, int n_kv_heads, int head_dim,
                        const AttnTile* tiles, int n_tiles, __half* out, int ld_out, cudaStream_t st) {
     if (c->attn_impl == 1 && head_dim == 128)
-        return attention_sm100_launch(qkv, ld, n_rows, n_q_heads, n_kv_heads, tiles, n_tiles, out, ld_out, st);
+        return attention_sm100_launch(qkv, ld, n_rows, n_q_heads, n_kv_heads, tiles, n_tiles, out, ld_out, c->num_sms, st);
     return attention_launch(qkv, ld, n_q_heads, n_kv_heads, head_dim, tiles, n_tiles, out, ld_out, st);
 }
 
