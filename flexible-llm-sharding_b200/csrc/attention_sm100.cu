@@ -57,7 +57,7 @@ __device__ __forceinline__ TileShape tile_shape(const AttnTile& t) {
 __global__ void __launch_bounds__(THREADS, 1)
 attention_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant__ CUtensorMap tmap_kv,
                          int n_q_heads, int n_kv_heads, const AttnTile* __restrict__ tiles, int n_tiles,
-                         __half* __restrict__ out, int ld_out, float scale_log2e) {
+                         __half* __restrict__ out, int ld_out, float scale_log2e, unsigned long long* dbg) {
     extern __shared__ uint8_t smem_raw[];
     uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
     uint8_t* sQ = smem;                      // two Q buffers
@@ -205,12 +205,17 @@ attention_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_q, const __gri
             float m_run = -INFINITY, l_run = 0.f;
             for (int j = 0; j < n; ++j, ++g) {
                 const uint32_t stage = g % KV_STAGES;
+                const bool probe = dbg != nullptr && warp_idx == 2 && lane == 0;
+                long long tk0 = 0, tk1 = 0, tk2 = 0, tk3 = 0, tk4 = 0;
+                if (probe) tk0 = clock64();
                 ptx::mbar_wait(&s_full[g & 1], (g >> 1) & 1);
                 ptx::tc_fence_after_sync();
+                if (probe) tk1 = clock64();
                 uint32_t sr[2][32];
                 ptx::tmem_ld_32x32(lane_addr + S_COL + (g & 1) * BKV, sr[0]);
                 ptx::tmem_ld_32x32(lane_addr + S_COL + (g & 1) * BKV + 32, sr[1]);
                 ptx::tmem_ld_wait();
+                if (probe) tk2 = clock64();
                 const bool in0 = j < n0;
                 const int kbase = in0 ? j * BKV : (j - n0) * BKV;
                 const int lo = in0 ? 0 : lo1, hi = in0 ? lim0 - 1 : hi1;
@@ -244,6 +249,7 @@ attention_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_q, const __gri
                     pk[c >> 1] = *reinterpret_cast<const uint32_t*>(&h);
                 }
                 l_run = l_run * alpha + sum;
+                if (probe) tk3 = clock64();
                 if (j > 0) {
                     // O is touched by the tensor core until P V of the previous key tile has retired
                     ptx::mbar_wait(pv_done, (g - 1) & 1);
@@ -262,6 +268,7 @@ attention_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_q, const __gri
                         ptx::tmem_st_wait();
                     }
                 }
+                if (probe) tk4 = clock64();
                 // P -> shared memory over the (dead) K tile: [128 rows][64 keys] fp16, 128B swizzle
                 uint8_t* sp = sKV + stage * STAGE_BYTES + i * 128;
 #pragma unroll
@@ -272,7 +279,17 @@ attention_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_q, const __gri
                 ptx::tc_fence_before_sync();
                 __syncwarp();
                 if (lane == 0) ptx::mbar_arrive(p_ready);
+                if (probe) {  // cycles: wait S | tcgen05.ld | softmax math | wait PV (+rescale) | store P + fences
+                    const long long tk5 = clock64();
+                    atomicAdd(&dbg[0], static_cast<unsigned long long>(tk1 - tk0));
+                    atomicAdd(&dbg[1], static_cast<unsigned long long>(tk2 - tk1));
+                    atomicAdd(&dbg[2], static_cast<unsigned long long>(tk3 - tk2));
+                    atomicAdd(&dbg[3], static_cast<unsigned long long>(tk4 - tk3));
+                    atomicAdd(&dbg[4], static_cast<unsigned long long>(tk5 - tk4));
+                    atomicAdd(&dbg[5], 1ull);
+                }
             }
+            const long long te0 = (dbg != nullptr && warp_idx == 2 && lane == 0) ? clock64() : 0;
             // ---- item epilogue: O / l -> fp16 -> global (the next item's first P V cannot start before
             // these warps send its p_ready, so O is stable here)
             if (n > 0) ptx::mbar_wait(pv_done, (g - 1) & 1);
@@ -299,6 +316,10 @@ attention_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_q, const __gri
                 }
             }
             ptx::tc_fence_before_sync();  // O reads ordered before the p_ready that lets the next item overwrite O
+            if (dbg != nullptr && warp_idx == 2 && lane == 0) {
+                atomicAdd(&dbg[6], static_cast<unsigned long long>(clock64() - te0));  // item epilogue
+                atomicAdd(&dbg[7], 1ull);
+            }
         }
     }
 
@@ -319,7 +340,7 @@ int attention_sm100_init() {
 }
 
 int attention_sm100_launch(const __half* qkv, int ld, int n_rows, int n_q_heads, int n_kv_heads, const AttnTile* tiles,
-                           int n_tiles, __half* out, int ld_out, int num_sms, cudaStream_t s) {
+                           int n_tiles, __half* out, int ld_out, int num_sms, cudaStream_t s, unsigned long long* dbg) {
     if (n_tiles <= 0) return kOk;
     if (ld_out % 8) return fail(kErrInvalid, "attention: ld_out must be a multiple of 8");
     if (n_kv_heads <= 0 || n_q_heads % n_kv_heads)
@@ -332,7 +353,7 @@ int attention_sm100_launch(const __half* qkv, int ld, int n_rows, int n_q_heads,
     const long long items = static_cast<long long>(n_tiles) * n_q_heads;
     const int grid = static_cast<int>(items < num_sms ? items : num_sms);
     attention_tcgen05_kernel<<<grid, THREADS, SMEM_BYTES, s>>>(tq, tkv, n_q_heads, n_kv_heads, tiles, n_tiles, out,
-                                                              ld_out, scale_log2e);
+                                                              ld_out, scale_log2e, dbg);
     FLS_CUDA(cudaGetLastError());
     return kOk;
 }
