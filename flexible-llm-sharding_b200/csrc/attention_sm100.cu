@@ -34,11 +34,19 @@ constexpr int KV_STAGES = 4;
 constexpr int Q_BYTES = BQ * D * 2;                  // 32 KiB: two [128 x 64] sub-tiles
 constexpr int KSUB_BYTES = BKV * 64 * 2;             // 8 KiB: one [64 keys x 64 d] sub-tile
 constexpr int STAGE_BYTES = 4 * KSUB_BYTES;          // K sub0, K sub1, V sub0, V sub1
-constexpr int SMEM_BYTES = 2 * Q_BYTES + KV_STAGES * STAGE_BYTES + 256 + 1024;
+constexpr int OST_ROW_BYTES = 144;                   // epilogue staging: 64 fp16 per row + 16 B pad (bank spread)
+constexpr int OST_BYTES = BQ * OST_ROW_BYTES;        // 18 KiB
+constexpr int SMEM_BYTES = 2 * Q_BYTES + KV_STAGES * STAGE_BYTES + OST_BYTES + 256 + 1024;
 constexpr int THREADS = 192;
 constexpr int TMEM_COLS = 256;
 constexpr int S_COL = 0, O_COL = 128;  // S: two buffers of 64 columns at 0 and 64; O: 128 columns
 constexpr float RESCALE_THRESHOLD = 8.0f;  // log2 units
+
+__device__ __forceinline__ float ex2_approx(float x) {  // 2^x, one MUFU op; 2^-inf = 0
+    float y;
+    asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+    return y;
+}
 
 struct TileShape {
     int n0, n1;  // key tiles in segment 0 / segment 1
@@ -62,7 +70,8 @@ attention_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_q, const __gri
     uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
     uint8_t* sQ = smem;                      // two Q buffers
     uint8_t* sKV = smem + 2 * Q_BYTES;
-    uint64_t* q_full = reinterpret_cast<uint64_t*>(smem + 2 * Q_BYTES + KV_STAGES * STAGE_BYTES);  // [2]
+    uint8_t* sO = smem + 2 * Q_BYTES + KV_STAGES * STAGE_BYTES;   // epilogue staging
+    uint64_t* q_full = reinterpret_cast<uint64_t*>(sO + OST_BYTES);  // [2]
     uint64_t* q_empty = q_full + 2;          // [2]: all Q K^T MMAs of the item using this buffer have retired
     uint64_t* kv_full = q_empty + 2;         // [KV_STAGES]
     uint64_t* kv_empty = kv_full + KV_STAGES;
@@ -235,15 +244,15 @@ attention_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_q, const __gri
                 if (mx > m_run + thr) m_new = mx;
                 const bool changed = m_new != m_run;
                 const float m_use = m_new == -INFINITY ? 0.f : m_new;
-                const float alpha = changed ? exp2f((m_run - m_use) * scale_log2e) : 1.f;   // m_run = -inf -> 0
+                const float alpha = changed ? ex2_approx((m_run - m_use) * scale_log2e) : 1.f;   // m_run = -inf -> 0
                 m_run = m_new;
                 const float mc = m_use * scale_log2e;
                 float sum = 0.f;
                 uint32_t pk[32];
 #pragma unroll
                 for (int c = 0; c < 64; c += 2) {
-                    const float p0 = exp2f(fmaf(__uint_as_float(sr[c >> 5][c & 31]), scale_log2e, -mc));
-                    const float p1 = exp2f(fmaf(__uint_as_float(sr[(c + 1) >> 5][(c + 1) & 31]), scale_log2e, -mc));
+                    const float p0 = ex2_approx(fmaf(__uint_as_float(sr[c >> 5][c & 31]), scale_log2e, -mc));
+                    const float p1 = ex2_approx(fmaf(__uint_as_float(sr[(c + 1) >> 5][(c + 1) & 31]), scale_log2e, -mc));
                     sum += p0 + p1;
                     const __half2 h = __floats2half2_rn(p0, p1);
                     pk[c >> 1] = *reinterpret_cast<const uint32_t*>(&h);
@@ -295,13 +304,17 @@ attention_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_q, const __gri
             if (n > 0) ptx::mbar_wait(pv_done, (g - 1) & 1);
             ptx::tc_fence_after_sync();
             const float inv = l_run > 0.f ? 1.f / l_run : 0.f;
-            __half* dst = out + static_cast<size_t>(t.q_row + i) * ld_out + head * D;
+            // Each warp stages its own 32 rows (64 columns at a time) in shared memory and writes them out
+            // as full 128-byte lines: 4 rows per store instruction instead of 32 scattered 16-byte pieces.
+            uint8_t* my_row = sO + i * OST_ROW_BYTES;
+            const int rows_here = min(32, t.n_q - quarter * 32);      // valid rows of this warp (may be <= 0)
 #pragma unroll 1
-            for (int c = 0; c < D / 32; ++c) {
-                uint32_t o[32];
-                ptx::tmem_ld_32x32(lane_addr + O_COL + c * 32, o);
-                ptx::tmem_ld_wait();
-                if (i < t.n_q) {
+            for (int hcol = 0; hcol < D; hcol += 64) {
+#pragma unroll
+                for (int c = 0; c < 2; ++c) {
+                    uint32_t o[32];
+                    ptx::tmem_ld_32x32(lane_addr + O_COL + hcol + c * 32, o);
+                    ptx::tmem_ld_wait();
 #pragma unroll
                     for (int v = 0; v < 4; ++v) {
                         uint32_t wv[4];
@@ -311,9 +324,21 @@ attention_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_q, const __gri
                                                                 __uint_as_float(o[v * 8 + e * 2 + 1]) * inv);
                             wv[e] = *reinterpret_cast<const uint32_t*>(&h);
                         }
-                        *reinterpret_cast<uint4*>(dst + c * 32 + v * 8) = make_uint4(wv[0], wv[1], wv[2], wv[3]);
+                        *reinterpret_cast<uint4*>(my_row + c * 64 + v * 16) = make_uint4(wv[0], wv[1], wv[2], wv[3]);
                     }
                 }
+                __syncwarp();
+#pragma unroll
+                for (int rr = 0; rr < 32; rr += 4) {
+                    const int r = rr + (lane >> 3);                     // row inside this warp's 32
+                    if (r < rows_here) {
+                        const uint4 v4 = *reinterpret_cast<const uint4*>(sO + (quarter * 32 + r) * OST_ROW_BYTES +
+                                                                         (lane & 7) * 16);
+                        *reinterpret_cast<uint4*>(out + static_cast<size_t>(t.q_row + quarter * 32 + r) * ld_out +
+                                                  head * D + hcol + (lane & 7) * 8) = v4;
+                    }
+                }
+                __syncwarp();
             }
             ptx::tc_fence_before_sync();  // O reads ordered before the p_ready that lets the next item overwrite O
             if (dbg != nullptr && warp_idx == 2 && lane == 0) {
