@@ -3,10 +3,9 @@
 // Same contract as attention.cu (see there and include/fls_b200.h: fls_attn_tile); replaces the
 // reference's two eager attention calls per layer (reference utils.py:272 and :275-279).
 //
-// Persistent CTAs (one per SM, 192 threads); a work item = one query tile (<= 128 rows) x one head:
+// One CTA = one query tile (<= 128 rows) x one head, 192 threads:
 //   warp 0      TMA producer: Q tile once (2 x [128 x 64] sub-tiles, 128B swizzle), then K/V tiles of
-//               64 keys (K and V each 2 x [64 x 64] sub-tiles) through a 4-stage ring that runs on
-//               across work items (the next item's Q goes to the other of two Q buffers).  A key tile
+//               64 keys (K and V each 2 x [64 x 64] sub-tiles) through a 2-stage ring.  A key tile
 //               never straddles the two key segments (prefix rows / option rows).
 //   warp 1      MMA issuer (one elected thread):  S = Q K^T  (tcgen05.mma M128 N64 K16 x 8, K-major
 //               operands) into TMEM columns [0,64);  O += P V (M128 N128 K16 x 4, A = P K-major, B = V
@@ -17,7 +16,8 @@
 //               rescaled in TMEM only when the running max grows by more than 2^8, final O / l.
 // S is double buffered: Q K^T of tile j+1 is issued before P V of tile j, so it runs while the
 // softmax warps work on tile j.  `pv_done` tells the softmax warps when O may be rescaled/read.
-// Shared memory: 2 x 32 KiB Q + 4 stages x 32 KiB = 192 KiB; TMEM: 256 columns.
+// Shared memory: Q 32 KiB + 2 stages x 32 KiB = 96 KiB -> two CTAs per SM, whose softmax and MMA
+// phases overlap; TMEM: 256 columns per CTA.
 #include <cuda.h>
 
 #include "common.cuh"
@@ -30,17 +30,16 @@ namespace {
 constexpr int D = 128;
 constexpr int BQ = 128;
 constexpr int BKV = 64;
-constexpr int KV_STAGES = 4;
+constexpr int KV_STAGES = 2;
 constexpr int Q_BYTES = BQ * D * 2;                  // 32 KiB: two [128 x 64] sub-tiles
 constexpr int KSUB_BYTES = BKV * 64 * 2;             // 8 KiB: one [64 keys x 64 d] sub-tile
 constexpr int STAGE_BYTES = 4 * KSUB_BYTES;          // K sub0, K sub1, V sub0, V sub1
-constexpr int OST_ROW_BYTES = 144;                   // epilogue staging: 64 fp16 per row + 16 B pad (bank spread)
-constexpr int OST_BYTES = BQ * OST_ROW_BYTES;        // 18 KiB
-constexpr int SMEM_BYTES = 2 * Q_BYTES + KV_STAGES * STAGE_BYTES + OST_BYTES + 256 + 1024;
+constexpr int SMEM_BYTES = Q_BYTES + KV_STAGES * STAGE_BYTES + 256 + 1024;
 constexpr int THREADS = 192;
 constexpr int TMEM_COLS = 256;
 constexpr int S_COL = 0, O_COL = 128;  // S: two buffers of 64 columns at 0 and 64; O: 128 columns
 constexpr float RESCALE_THRESHOLD = 8.0f;  // log2 units
+constexpr int OST_ROW_BYTES = 144;         // epilogue staging (in the dead Q buffer): 64 fp16 per row + 16 B pad
 
 __device__ __forceinline__ float ex2_approx(float x) {  // 2^x, one MUFU op; 2^-inf = 0
     float y;
@@ -48,55 +47,47 @@ __device__ __forceinline__ float ex2_approx(float x) {  // 2^x, one MUFU op; 2^-
     return y;
 }
 
-struct TileShape {
-    int n0, n1;  // key tiles in segment 0 / segment 1
-};
-__device__ __forceinline__ TileShape tile_shape(const AttnTile& t) {
-    const int seg0_keys = t.mode == kAttnPrefixCausal ? min(t.seg0_len, t.q_seq0 + t.n_q) : t.seg0_len;
-    TileShape r;
-    r.n0 = (seg0_keys + BKV - 1) / BKV;
-    r.n1 = t.mode == kAttnSuffix ? (t.seg1_len + BKV - 1) / BKV : 0;
-    return r;
-}
-
-// Persistent: CTA b handles work items b, b + gridDim.x, ...; item w = (head = w / n_tiles, tile = w % n_tiles),
-// so CTAs running at the same time share a head and neighbouring tiles (the 3 prefix tiles and the option
-// tile of a prompt read the same prefix K/V -> L2 hits).
-__global__ void __launch_bounds__(THREADS, 1)
+__global__ void __launch_bounds__(THREADS, 2)
 attention_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant__ CUtensorMap tmap_kv,
-                         int n_q_heads, int n_kv_heads, const AttnTile* __restrict__ tiles, int n_tiles,
-                         __half* __restrict__ out, int ld_out, float scale_log2e, unsigned long long* dbg) {
+                         int n_q_heads, int n_kv_heads, const AttnTile* __restrict__ tiles, __half* __restrict__ out,
+                         int ld_out, float scale_log2e, unsigned long long* dbg) {
     extern __shared__ uint8_t smem_raw[];
     uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
-    uint8_t* sQ = smem;                      // two Q buffers
-    uint8_t* sKV = smem + 2 * Q_BYTES;
-    uint8_t* sO = smem + 2 * Q_BYTES + KV_STAGES * STAGE_BYTES;   // epilogue staging
-    uint64_t* q_full = reinterpret_cast<uint64_t*>(sO + OST_BYTES);  // [2]
-    uint64_t* q_empty = q_full + 2;          // [2]: all Q K^T MMAs of the item using this buffer have retired
-    uint64_t* kv_full = q_empty + 2;         // [KV_STAGES]
+    uint8_t* sQ = smem;
+    uint8_t* sKV = smem + Q_BYTES;
+    uint64_t* q_full = reinterpret_cast<uint64_t*>(smem + Q_BYTES + KV_STAGES * STAGE_BYTES);
+    uint64_t* kv_full = q_full + 1;
     uint64_t* kv_empty = kv_full + KV_STAGES;
-    uint64_t* s_full = kv_empty + KV_STAGES;  // [2]: S buffer (key tile counter & 1) is complete
+    uint64_t* s_full = kv_empty + KV_STAGES;   // [2]: S buffer b = tile & 1 is complete
     uint64_t* p_ready = s_full + 2;
-    uint64_t* pv_done = p_ready + 1;         // O += P V of a key tile has retired
+    uint64_t* pv_done = p_ready + 1;           // O += P V of a tile has retired
     uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(pv_done + 1);
 
     const int warp_idx = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    const int n_items = n_tiles * n_q_heads;
-    const int group = n_q_heads / n_kv_heads;
+    const AttnTile t = tiles[blockIdx.x];
+    const int head = blockIdx.y;
+    const int kvh = head / (n_q_heads / n_kv_heads);
+    const int q_col = head * D;
+    const int k_col = (n_q_heads + kvh) * D;
+    const int v_col = (n_q_heads + n_kv_heads + kvh) * D;
+
+    // key tiles: segment 0 first (only up to the diagonal for a causal prefix tile), then segment 1
+    const int seg0_keys = t.mode == kAttnPrefixCausal ? min(t.seg0_len, t.q_seq0 + t.n_q) : t.seg0_len;
+    const int n0 = (seg0_keys + BKV - 1) / BKV;
+    const int n1 = t.mode == kAttnSuffix ? (t.seg1_len + BKV - 1) / BKV : 0;
+    const int n_tiles = n0 + n1;
 
     if (warp_idx == 0) {
         if (ptx::elect_one()) {
             ptx::prefetch_tensormap(&tmap_q);
             ptx::prefetch_tensormap(&tmap_kv);
-            for (int i = 0; i < 2; ++i) {
-                ptx::mbar_init(&q_full[i], 1);
-                ptx::mbar_init(&q_empty[i], 1);
-                ptx::mbar_init(&s_full[i], 1);
-            }
+            ptx::mbar_init(q_full, 1);
             for (int i = 0; i < KV_STAGES; ++i) {
                 ptx::mbar_init(&kv_full[i], 1);
                 ptx::mbar_init(&kv_empty[i], 1);
             }
+            ptx::mbar_init(&s_full[0], 1);
+            ptx::mbar_init(&s_full[1], 1);
             ptx::mbar_init(p_ready, 4);  // one arrive per softmax warp
             ptx::mbar_init(pv_done, 1);
             ptx::fence_mbar_init();
@@ -113,29 +104,19 @@ attention_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_q, const __gri
     if (warp_idx == 0) {
         // ------------------------------------------------------------------ TMA producer
         if (ptx::elect_one()) {
-            uint32_t g = 0, it = 0;  // key-tile counter / item counter of this CTA
-            for (int w = blockIdx.x; w < n_items; w += gridDim.x, ++it) {
-                const int head = w / n_tiles;
-                const AttnTile t = tiles[w - head * n_tiles];
-                const TileShape ts = tile_shape(t);
-                const int kvh = head / group;
-                const int q_col = head * D, k_col = (n_q_heads + kvh) * D, v_col = (n_q_heads + n_kv_heads + kvh) * D;
-                const uint32_t qb = it & 1;
-                ptx::mbar_wait(&q_empty[qb], ((it >> 1) & 1) ^ 1);
-                ptx::mbar_arrive_expect_tx(&q_full[qb], Q_BYTES);
-                ptx::tma_load_2d(sQ + qb * Q_BYTES, &tmap_q, &q_full[qb], q_col, t.q_row);
-                ptx::tma_load_2d(sQ + qb * Q_BYTES + Q_BYTES / 2, &tmap_q, &q_full[qb], q_col + 64, t.q_row);
-                for (int j = 0; j < ts.n0 + ts.n1; ++j, ++g) {
-                    const uint32_t stage = g % KV_STAGES;
-                    ptx::mbar_wait(&kv_empty[stage], ((g / KV_STAGES) & 1) ^ 1);
-                    const int row = j < ts.n0 ? t.seg0_row + j * BKV : t.seg1_row + (j - ts.n0) * BKV;
-                    uint8_t* st = sKV + stage * STAGE_BYTES;
-                    ptx::mbar_arrive_expect_tx(&kv_full[stage], STAGE_BYTES);
-                    ptx::tma_load_2d(st, &tmap_kv, &kv_full[stage], k_col, row);
-                    ptx::tma_load_2d(st + KSUB_BYTES, &tmap_kv, &kv_full[stage], k_col + 64, row);
-                    ptx::tma_load_2d(st + 2 * KSUB_BYTES, &tmap_kv, &kv_full[stage], v_col, row);
-                    ptx::tma_load_2d(st + 3 * KSUB_BYTES, &tmap_kv, &kv_full[stage], v_col + 64, row);
-                }
+            ptx::mbar_arrive_expect_tx(q_full, Q_BYTES);
+            ptx::tma_load_2d(sQ, &tmap_q, q_full, q_col, t.q_row);
+            ptx::tma_load_2d(sQ + Q_BYTES / 2, &tmap_q, q_full, q_col + 64, t.q_row);
+            for (int j = 0; j < n_tiles; ++j) {
+                const int stage = j % KV_STAGES;
+                ptx::mbar_wait(&kv_empty[stage], ((j / KV_STAGES) & 1) ^ 1);
+                const int row = j < n0 ? t.seg0_row + j * BKV : t.seg1_row + (j - n0) * BKV;
+                uint8_t* st = sKV + stage * STAGE_BYTES;
+                ptx::mbar_arrive_expect_tx(&kv_full[stage], STAGE_BYTES);
+                ptx::tma_load_2d(st, &tmap_kv, &kv_full[stage], k_col, row);
+                ptx::tma_load_2d(st + KSUB_BYTES, &tmap_kv, &kv_full[stage], k_col + 64, row);
+                ptx::tma_load_2d(st + 2 * KSUB_BYTES, &tmap_kv, &kv_full[stage], v_col, row);
+                ptx::tma_load_2d(st + 3 * KSUB_BYTES, &tmap_kv, &kv_full[stage], v_col + 64, row);
             }
         }
     } else if (warp_idx == 1) {
@@ -143,51 +124,40 @@ attention_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_q, const __gri
         if (ptx::elect_one()) {
             constexpr uint32_t idesc_qk = ptx::umma_idesc_f16_f32(BQ, BKV);
             constexpr uint32_t idesc_pv = ptx::umma_idesc_f16_f32(BQ, D) | ptx::kUmmaBMajorMN;
-            uint32_t g = 0, it = 0;
-            for (int w = blockIdx.x; w < n_items; w += gridDim.x, ++it) {
-                const int head = w / n_tiles;
-                const TileShape ts = tile_shape(tiles[w - head * n_tiles]);
-                const int n = ts.n0 + ts.n1;
-                const uint32_t qb = it & 1;
-                const uint32_t q_addr = ptx::smem_u32(sQ + qb * Q_BYTES);
-                ptx::mbar_wait(&q_full[qb], (it >> 1) & 1);
-                // S(gg) = Q K^T into S buffer gg & 1: d = 128 -> 8 K-steps, 4 per 64-wide sub-tile
-                auto issue_qk = [&](uint32_t gg) {
-                    const uint32_t stage = gg % KV_STAGES;
-                    const uint32_t st = ptx::smem_u32(sKV + stage * STAGE_BYTES);
-                    ptx::mbar_wait(&kv_full[stage], (gg / KV_STAGES) & 1);
-                    ptx::tc_fence_after_sync();
+            const uint32_t q_addr = ptx::smem_u32(sQ);
+            ptx::mbar_wait(q_full, 0);
+            // S(j) = Q K(j)^T into S buffer j & 1: d = 128 -> 8 K-steps, 4 per 64-wide sub-tile
+            auto issue_qk = [&](int j) {
+                const int stage = j % KV_STAGES;
+                const uint32_t st = ptx::smem_u32(sKV + stage * STAGE_BYTES);
+                ptx::mbar_wait(&kv_full[stage], (j / KV_STAGES) & 1);
+                ptx::tc_fence_after_sync();
 #pragma unroll
-                    for (int k = 0; k < D / 16; ++k) {
-                        const uint64_t da = ptx::umma_smem_desc_sw128(q_addr + (k / 4) * (Q_BYTES / 2)) + 2 * (k % 4);
-                        const uint64_t db = ptx::umma_smem_desc_sw128(st + (k / 4) * KSUB_BYTES) + 2 * (k % 4);
-                        ptx::umma_f16<1>(tmem_base + S_COL + (gg & 1) * BKV, da, db, idesc_qk, k != 0);
-                    }
-                    ptx::umma_commit(&s_full[gg & 1]);
-                };
-                if (n > 0) issue_qk(g);
-                if (n <= 1) ptx::umma_commit(&q_empty[qb]);
-                for (int j = 0; j < n; ++j, ++g) {
-                    // the next key tile's scores are computed while the softmax warps work on this one
-                    if (j + 1 < n) {
-                        issue_qk(g + 1);
-                        if (j + 2 == n) ptx::umma_commit(&q_empty[qb]);  // last Q K^T of the item issued
-                    }
-                    const uint32_t stage = g % KV_STAGES;
-                    const uint32_t st = ptx::smem_u32(sKV + stage * STAGE_BYTES);
-                    // O += P V : P (fp16, K-major) now lies where K was; V is MN-major as loaded
-                    ptx::mbar_wait(p_ready, g & 1);
-                    ptx::tc_fence_after_sync();
-#pragma unroll
-                    for (int k = 0; k < BKV / 16; ++k) {
-                        const uint64_t da = ptx::umma_smem_desc_sw128(st) + 2 * k;
-                        const uint64_t db =
-                            ptx::umma_smem_desc_sw128_mn(st + 2 * KSUB_BYTES + k * 16 * 128, KSUB_BYTES, 1024);
-                        ptx::umma_f16<1>(tmem_base + O_COL, da, db, idesc_pv, (j | k) != 0);
-                    }
-                    ptx::umma_commit(&kv_empty[stage]);
-                    ptx::umma_commit(pv_done);
+                for (int k = 0; k < D / 16; ++k) {
+                    const uint64_t da = ptx::umma_smem_desc_sw128(q_addr + (k / 4) * (Q_BYTES / 2)) + 2 * (k % 4);
+                    const uint64_t db = ptx::umma_smem_desc_sw128(st + (k / 4) * KSUB_BYTES) + 2 * (k % 4);
+                    ptx::umma_f16<1>(tmem_base + S_COL + (j & 1) * BKV, da, db, idesc_qk, k != 0);
                 }
+                ptx::umma_commit(&s_full[j & 1]);
+            };
+            if (n_tiles > 0) issue_qk(0);
+            for (int j = 0; j < n_tiles; ++j) {
+                // the next tile's scores are computed while the softmax warps work on this one
+                if (j + 1 < n_tiles) issue_qk(j + 1);
+                const int stage = j % KV_STAGES;
+                const uint32_t st = ptx::smem_u32(sKV + stage * STAGE_BYTES);
+                // O += P V : P (fp16, K-major) now lies where K(j) was; V is MN-major as loaded
+                ptx::mbar_wait(p_ready, j & 1);
+                ptx::tc_fence_after_sync();
+#pragma unroll
+                for (int k = 0; k < BKV / 16; ++k) {
+                    const uint64_t da = ptx::umma_smem_desc_sw128(st) + 2 * k;
+                    const uint64_t db =
+                        ptx::umma_smem_desc_sw128_mn(st + 2 * KSUB_BYTES + k * 16 * 128, KSUB_BYTES, 1024);
+                    ptx::umma_f16<1>(tmem_base + O_COL, da, db, idesc_pv, (j | k) != 0);
+                }
+                ptx::umma_commit(&kv_empty[stage]);
+                ptx::umma_commit(pv_done);
             }
         }
     } else {
@@ -195,156 +165,126 @@ attention_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_q, const __gri
         const int quarter = warp_idx & 3;             // TMEM lanes [32*quarter, +32) belong to this warp
         const int i = quarter * 32 + lane;            // query row inside the tile
         const uint32_t lane_addr = tmem_base + (static_cast<uint32_t>(quarter * 32) << 16);
+        // visible key ranges of this row, per segment
+        const int lim0 = t.mode == kAttnPrefixCausal ? min(t.seg0_len, t.q_seq0 + i + 1) : t.seg0_len;
+        int lo1 = 0, hi1 = -1;
+        if (t.mode == kAttnSuffix) {
+            const int qa = (t.q_row - t.seg1_row) + i, L = t.q_seq0;
+            lo1 = (qa / L) * L;
+            hi1 = min(qa, t.seg1_len - 1);           // own option, positions <= own
+        }
+        // running reference max m_run is kept in RAW score units; p = exp2(s * c - m_run * c), c = scale * log2(e)
+        float m_run = -INFINITY, l_run = 0.f;
         const float thr = RESCALE_THRESHOLD / scale_log2e;
-        uint32_t g = 0;
-        for (int w = blockIdx.x; w < n_items; w += gridDim.x) {
-            const int head = w / n_tiles;
-            const AttnTile t = tiles[w - head * n_tiles];
-            const TileShape ts = tile_shape(t);
-            const int n0 = ts.n0, n = ts.n0 + ts.n1;
-            // visible key ranges of this row, per segment
-            const int lim0 = t.mode == kAttnPrefixCausal ? min(t.seg0_len, t.q_seq0 + i + 1) : t.seg0_len;
-            int lo1 = 0, hi1 = -1;
-            if (t.mode == kAttnSuffix) {
-                const int qa = (t.q_row - t.seg1_row) + i, L = t.q_seq0;
-                lo1 = (qa / L) * L;
-                hi1 = min(qa, t.seg1_len - 1);       // own option, positions <= own
-            }
-            // running reference max m_run is kept in RAW score units; p = exp2(s * c - m_run * c), c = scale * log2(e)
-            float m_run = -INFINITY, l_run = 0.f;
-            for (int j = 0; j < n; ++j, ++g) {
-                const uint32_t stage = g % KV_STAGES;
-                const bool probe = dbg != nullptr && warp_idx == 2 && lane == 0;
-                long long tk0 = 0, tk1 = 0, tk2 = 0, tk3 = 0, tk4 = 0;
-                if (probe) tk0 = clock64();
-                ptx::mbar_wait(&s_full[g & 1], (g >> 1) & 1);
-                ptx::tc_fence_after_sync();
-                if (probe) tk1 = clock64();
-                uint32_t sr[2][32];
-                ptx::tmem_ld_32x32(lane_addr + S_COL + (g & 1) * BKV, sr[0]);
-                ptx::tmem_ld_32x32(lane_addr + S_COL + (g & 1) * BKV + 32, sr[1]);
-                ptx::tmem_ld_wait();
-                if (probe) tk2 = clock64();
-                const bool in0 = j < n0;
-                const int kbase = in0 ? j * BKV : (j - n0) * BKV;
-                const int lo = in0 ? 0 : lo1, hi = in0 ? lim0 - 1 : hi1;
-                // masking only where a row of this warp has an invisible key in the tile (warp-uniform branch)
-                if (__any_sync(0xffffffffu, kbase < lo || kbase + BKV - 1 > hi)) {
-#pragma unroll
-                    for (int c = 0; c < 64; ++c) {
-                        const int key = kbase + c;
-                        if (key < lo || key > hi) sr[c >> 5][c & 31] = 0xff800000u;  // -inf
-                    }
-                }
-                float mx = -INFINITY;
-#pragma unroll
-                for (int c = 0; c < 64; ++c) mx = fmaxf(mx, __uint_as_float(sr[c >> 5][c & 31]));
-                // lazy rescale: keep the old reference max unless the new one is much larger
-                float m_new = m_run;
-                if (mx > m_run + thr) m_new = mx;
-                const bool changed = m_new != m_run;
-                const float m_use = m_new == -INFINITY ? 0.f : m_new;
-                const float alpha = changed ? ex2_approx((m_run - m_use) * scale_log2e) : 1.f;   // m_run = -inf -> 0
-                m_run = m_new;
-                const float mc = m_use * scale_log2e;
-                float sum = 0.f;
-                uint32_t pk[32];
-#pragma unroll
-                for (int c = 0; c < 64; c += 2) {
-                    const float p0 = ex2_approx(fmaf(__uint_as_float(sr[c >> 5][c & 31]), scale_log2e, -mc));
-                    const float p1 = ex2_approx(fmaf(__uint_as_float(sr[(c + 1) >> 5][(c + 1) & 31]), scale_log2e, -mc));
-                    sum += p0 + p1;
-                    const __half2 h = __floats2half2_rn(p0, p1);
-                    pk[c >> 1] = *reinterpret_cast<const uint32_t*>(&h);
-                }
-                l_run = l_run * alpha + sum;
-                if (probe) tk3 = clock64();
-                if (j > 0) {
-                    // O is touched by the tensor core until P V of the previous key tile has retired
-                    ptx::mbar_wait(pv_done, (g - 1) & 1);
-                    ptx::tc_fence_after_sync();
-                    // rescale this row of O (TMEM) if any row of the warp moved its reference max
-                    if (__any_sync(0xffffffffu, changed)) {
-#pragma unroll 1
-                        for (int c = 0; c < D / 32; ++c) {
-                            uint32_t o[32];
-                            ptx::tmem_ld_32x32(lane_addr + O_COL + c * 32, o);
-                            ptx::tmem_ld_wait();
-#pragma unroll
-                            for (int e = 0; e < 32; ++e) o[e] = __float_as_uint(__uint_as_float(o[e]) * alpha);
-                            ptx::tmem_st_32x32(lane_addr + O_COL + c * 32, o);
-                        }
-                        ptx::tmem_st_wait();
-                    }
-                }
-                if (probe) tk4 = clock64();
-                // P -> shared memory over the (dead) K tile: [128 rows][64 keys] fp16, 128B swizzle
-                uint8_t* sp = sKV + stage * STAGE_BYTES + i * 128;
-#pragma unroll
-                for (int c = 0; c < 8; ++c)
-                    *reinterpret_cast<uint4*>(sp + ((c ^ (i & 7)) << 4)) =
-                        make_uint4(pk[c * 4], pk[c * 4 + 1], pk[c * 4 + 2], pk[c * 4 + 3]);
-                ptx::fence_proxy_async_smem();   // generic-proxy writes -> visible to the tensor core's async proxy
-                ptx::tc_fence_before_sync();
-                __syncwarp();
-                if (lane == 0) ptx::mbar_arrive(p_ready);
-                if (probe) {  // cycles: wait S | tcgen05.ld | softmax math | wait PV (+rescale) | store P + fences
-                    const long long tk5 = clock64();
-                    atomicAdd(&dbg[0], static_cast<unsigned long long>(tk1 - tk0));
-                    atomicAdd(&dbg[1], static_cast<unsigned long long>(tk2 - tk1));
-                    atomicAdd(&dbg[2], static_cast<unsigned long long>(tk3 - tk2));
-                    atomicAdd(&dbg[3], static_cast<unsigned long long>(tk4 - tk3));
-                    atomicAdd(&dbg[4], static_cast<unsigned long long>(tk5 - tk4));
-                    atomicAdd(&dbg[5], 1ull);
-                }
-            }
-            const long long te0 = (dbg != nullptr && warp_idx == 2 && lane == 0) ? clock64() : 0;
-            // ---- item epilogue: O / l -> fp16 -> global (the next item's first P V cannot start before
-            // these warps send its p_ready, so O is stable here)
-            if (n > 0) ptx::mbar_wait(pv_done, (g - 1) & 1);
+        for (int j = 0; j < n_tiles; ++j) {
+            const int stage = j % KV_STAGES;
+            ptx::mbar_wait(&s_full[j & 1], (j >> 1) & 1);
             ptx::tc_fence_after_sync();
-            const float inv = l_run > 0.f ? 1.f / l_run : 0.f;
-            // Each warp stages its own 32 rows (64 columns at a time) in shared memory and writes them out
-            // as full 128-byte lines: 4 rows per store instruction instead of 32 scattered 16-byte pieces.
-            uint8_t* my_row = sO + i * OST_ROW_BYTES;
-            const int rows_here = min(32, t.n_q - quarter * 32);      // valid rows of this warp (may be <= 0)
+            uint32_t sr[2][32];
+            ptx::tmem_ld_32x32(lane_addr + S_COL + (j & 1) * BKV, sr[0]);
+            ptx::tmem_ld_32x32(lane_addr + S_COL + (j & 1) * BKV + 32, sr[1]);
+            ptx::tmem_ld_wait();
+            const bool in0 = j < n0;
+            const int kbase = in0 ? j * BKV : (j - n0) * BKV;
+            const int lo = in0 ? 0 : lo1, hi = in0 ? lim0 - 1 : hi1;
+            // masking only where a row of this warp has an invisible key in the tile (warp-uniform branch)
+            if (__any_sync(0xffffffffu, kbase < lo || kbase + BKV - 1 > hi)) {
+#pragma unroll
+                for (int c = 0; c < 64; ++c) {
+                    const int key = kbase + c;
+                    if (key < lo || key > hi) sr[c >> 5][c & 31] = 0xff800000u;  // -inf
+                }
+            }
+            float mx = -INFINITY;
+#pragma unroll
+            for (int c = 0; c < 64; ++c) mx = fmaxf(mx, __uint_as_float(sr[c >> 5][c & 31]));
+            // lazy rescale: keep the old reference max unless the new one is much larger
+            float m_new = m_run;
+            if (mx > m_run + thr) m_new = mx;
+            const bool changed = m_new != m_run;
+            const float m_use = m_new == -INFINITY ? 0.f : m_new;
+            const float alpha = changed ? ex2_approx((m_run - m_use) * scale_log2e) : 1.f;   // m_run = -inf -> 0
+            m_run = m_new;
+            const float mc = m_use * scale_log2e;
+            float sum = 0.f;
+            uint32_t pk[32];
+#pragma unroll
+            for (int c = 0; c < 64; c += 2) {
+                const float p0 = ex2_approx(fmaf(__uint_as_float(sr[c >> 5][c & 31]), scale_log2e, -mc));
+                const float p1 = ex2_approx(fmaf(__uint_as_float(sr[(c + 1) >> 5][(c + 1) & 31]), scale_log2e, -mc));
+                sum += p0 + p1;
+                const __half2 h = __floats2half2_rn(p0, p1);
+                pk[c >> 1] = *reinterpret_cast<const uint32_t*>(&h);
+            }
+            l_run = l_run * alpha + sum;
+            if (j > 0) {
+                // O is touched by the tensor core until P V of the previous tile has retired
+                ptx::mbar_wait(pv_done, (j - 1) & 1);
+                ptx::tc_fence_after_sync();
+                // rescale this row of O (TMEM) if any row of the warp moved its reference max
+                if (__any_sync(0xffffffffu, changed)) {
 #pragma unroll 1
-            for (int hcol = 0; hcol < D; hcol += 64) {
+                    for (int c = 0; c < D / 32; ++c) {
+                        uint32_t o[32];
+                        ptx::tmem_ld_32x32(lane_addr + O_COL + c * 32, o);
+                        ptx::tmem_ld_wait();
 #pragma unroll
-                for (int c = 0; c < 2; ++c) {
-                    uint32_t o[32];
-                    ptx::tmem_ld_32x32(lane_addr + O_COL + hcol + c * 32, o);
-                    ptx::tmem_ld_wait();
-#pragma unroll
-                    for (int v = 0; v < 4; ++v) {
-                        uint32_t wv[4];
-#pragma unroll
-                        for (int e = 0; e < 4; ++e) {
-                            const __half2 h = __floats2half2_rn(__uint_as_float(o[v * 8 + e * 2]) * inv,
-                                                                __uint_as_float(o[v * 8 + e * 2 + 1]) * inv);
-                            wv[e] = *reinterpret_cast<const uint32_t*>(&h);
-                        }
-                        *reinterpret_cast<uint4*>(my_row + c * 64 + v * 16) = make_uint4(wv[0], wv[1], wv[2], wv[3]);
+                        for (int e = 0; e < 32; ++e) o[e] = __float_as_uint(__uint_as_float(o[e]) * alpha);
+                        ptx::tmem_st_32x32(lane_addr + O_COL + c * 32, o);
                     }
+                    ptx::tmem_st_wait();
                 }
-                __syncwarp();
+            }
+            // P -> shared memory over the (dead) K tile: [128 rows][64 keys] fp16, 128B swizzle
+            uint8_t* sp = sKV + stage * STAGE_BYTES + i * 128;
 #pragma unroll
-                for (int rr = 0; rr < 32; rr += 4) {
-                    const int r = rr + (lane >> 3);                     // row inside this warp's 32
-                    if (r < rows_here) {
-                        const uint4 v4 = *reinterpret_cast<const uint4*>(sO + (quarter * 32 + r) * OST_ROW_BYTES +
-                                                                         (lane & 7) * 16);
-                        *reinterpret_cast<uint4*>(out + static_cast<size_t>(t.q_row + quarter * 32 + r) * ld_out +
-                                                  head * D + hcol + (lane & 7) * 8) = v4;
+            for (int c = 0; c < 8; ++c)
+                *reinterpret_cast<uint4*>(sp + ((c ^ (i & 7)) << 4)) =
+                    make_uint4(pk[c * 4], pk[c * 4 + 1], pk[c * 4 + 2], pk[c * 4 + 3]);
+            ptx::fence_proxy_async_smem();   // generic-proxy writes -> visible to the tensor core's async proxy
+            ptx::tc_fence_before_sync();
+            __syncwarp();
+            if (lane == 0) ptx::mbar_arrive(p_ready);
+        }
+        // ---- epilogue: O / l -> fp16 -> global
+        if (n_tiles > 0) ptx::mbar_wait(pv_done, (n_tiles - 1) & 1);
+        ptx::tc_fence_after_sync();
+        const float inv = l_run > 0.f ? 1.f / l_run : 0.f;
+        // Every Q K^T has retired by now, so the Q buffer is free: each warp stages its own 32 rows there
+        // (64 columns at a time) and writes them out as full 128-byte lines, 4 rows per store instruction.
+        uint8_t* my_row = sQ + i * OST_ROW_BYTES;
+        const int rows_here = min(32, t.n_q - quarter * 32);      // valid rows of this warp (may be <= 0)
+#pragma unroll 1
+        for (int hcol = 0; hcol < D; hcol += 64) {
+#pragma unroll
+            for (int c = 0; c < 2; ++c) {
+                uint32_t o[32];
+                ptx::tmem_ld_32x32(lane_addr + O_COL + hcol + c * 32, o);
+                ptx::tmem_ld_wait();
+#pragma unroll
+                for (int v = 0; v < 4; ++v) {
+                    uint32_t wv[4];
+#pragma unroll
+                    for (int e = 0; e < 4; ++e) {
+                        const __half2 h = __floats2half2_rn(__uint_as_float(o[v * 8 + e * 2]) * inv,
+                                                            __uint_as_float(o[v * 8 + e * 2 + 1]) * inv);
+                        wv[e] = *reinterpret_cast<const uint32_t*>(&h);
                     }
+                    *reinterpret_cast<uint4*>(my_row + c * 64 + v * 16) = make_uint4(wv[0], wv[1], wv[2], wv[3]);
                 }
-                __syncwarp();
             }
-            ptx::tc_fence_before_sync();  // O reads ordered before the p_ready that lets the next item overwrite O
-            if (dbg != nullptr && warp_idx == 2 && lane == 0) {
-                atomicAdd(&dbg[6], static_cast<unsigned long long>(clock64() - te0));  // item epilogue
-                atomicAdd(&dbg[7], 1ull);
+            __syncwarp();
+#pragma unroll
+            for (int rr = 0; rr < 32; rr += 4) {
+                const int r = rr + (lane >> 3);                     // row inside this warp's 32
+                if (r < rows_here) {
+                    const uint4 v4 = *reinterpret_cast<const uint4*>(sQ + (quarter * 32 + r) * OST_ROW_BYTES +
+                                                                     (lane & 7) * 16);
+                    *reinterpret_cast<uint4*>(out + static_cast<size_t>(t.q_row + quarter * 32 + r) * ld_out +
+                                              head * D + hcol + (lane & 7) * 8) = v4;
+                }
             }
+            __syncwarp();
         }
     }
 
@@ -366,6 +306,7 @@ int attention_sm100_init() {
 
 int attention_sm100_launch(const __half* qkv, int ld, int n_rows, int n_q_heads, int n_kv_heads, const AttnTile* tiles,
                            int n_tiles, __half* out, int ld_out, int num_sms, cudaStream_t s, unsigned long long* dbg) {
+    (void)num_sms;
     if (n_tiles <= 0) return kOk;
     if (ld_out % 8) return fail(kErrInvalid, "attention: ld_out must be a multiple of 8");
     if (n_kv_heads <= 0 || n_q_heads % n_kv_heads)
@@ -375,10 +316,8 @@ int attention_sm100_launch(const __half* qkv, int ld, int n_rows, int n_q_heads,
     FLS_TRY(encode_tmap_2d(&tq, qkv, n_rows, cols, ld, BQ));
     FLS_TRY(encode_tmap_2d(&tkv, qkv, n_rows, cols, ld, BKV));
     const float scale_log2e = 1.4426950408889634f / sqrtf(static_cast<float>(D));
-    const long long items = static_cast<long long>(n_tiles) * n_q_heads;
-    const int grid = static_cast<int>(items < num_sms ? items : num_sms);
-    attention_tcgen05_kernel<<<grid, THREADS, SMEM_BYTES, s>>>(tq, tkv, n_q_heads, n_kv_heads, tiles, n_tiles, out,
-                                                              ld_out, scale_log2e, dbg);
+    attention_tcgen05_kernel<<<dim3(n_tiles, n_q_heads), THREADS, SMEM_BYTES, s>>>(tq, tkv, n_q_heads, n_kv_heads, tiles,
+                                                                                  out, ld_out, scale_log2e, dbg);
     FLS_CUDA(cudaGetLastError());
     return kOk;
 }
