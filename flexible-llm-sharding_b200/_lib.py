@@ -99,7 +99,6 @@ _SIGNATURES = {
     "fls_op_head": (_I, [_P, _P, _P, _I, _I, _I, _P, _P, _I, _P, _P, _P]),
     "fls_op_head_noalloc": (_I, [_P, _P, _I, _I, _I, _P, _P, _I, _P, _P, _P]),
     "fls_set_option": (_I, [_P, C.c_char_p, _I]),
-    "fls_get_attention_timing": (_I, [_P, _P]),
     "fls_set_profiling": (_I, [_P, _I]),
     "fls_get_profile": (_I, [_P, _P]),
     "fls_get_stats": (_I, [_P, C.POINTER(Stats)]),

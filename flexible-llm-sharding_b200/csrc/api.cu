@@ -96,7 +96,6 @@ struct fls_ctx {
     unsigned long long peer_enabled_mask = 0;
     int gemm_cg = 2;  // tcgen05 cta_group of the GEMM kernels (2 = CTA pairs, 1 = single CTA)
     int attn_impl = 1;  // 1 = tcgen05 attention (head_dim 128), 0 = mma.sync attention
-    unsigned long long* attn_dbg = nullptr;  // optional in-kernel phase timing of the attention kernel (8 counters)
     int fuse_rope = 1;  // 1 = rotary embedding in the QKV GEMM epilogue (head_dim 128), 0 = separate kernel
 };
 
@@ -247,8 +246,7 @@ inline __half* H(uint16_t* p) { return reinterpret_cast<__half*>(p); }
 int attention_dispatch(fls_ctx* c, const __half* qkv, int ld, int n_rows, int n_q_heads, int n_kv_heads, int head_dim,
                        const AttnTile* tiles, int n_tiles, __half* out, int ld_out, cudaStream_t st) {
     if (c->attn_impl == 1 && head_dim == 128)
-        return attention_sm100_launch(qkv, ld, n_rows, n_q_heads, n_kv_heads, tiles, n_tiles, out, ld_out, c->num_sms, st,
-                                      c->attn_dbg);
+        return attention_sm100_launch(qkv, ld, n_rows, n_q_heads, n_kv_heads, tiles, n_tiles, out, ld_out, st);
     return attention_launch(qkv, ld, n_q_heads, n_kv_heads, head_dim, tiles, n_tiles, out, ld_out, st);
 }
 
@@ -764,16 +762,6 @@ int fls_set_option(fls_ctx* c, const char* name, int value) {
         c->gemm_cg = value;
         return kOk;
     }
-    if (strcmp(name, "attention_timing") == 0) {  // value 1: start/reset, 0: stop
-        FLS_CUDA(cudaSetDevice(c->device));
-        if (value && !c->attn_dbg) FLS_CUDA(cudaMalloc(reinterpret_cast<void**>(&c->attn_dbg), 8 * sizeof(unsigned long long)));
-        if (c->attn_dbg) FLS_CUDA(cudaMemset(c->attn_dbg, 0, 8 * sizeof(unsigned long long)));
-        if (!value && c->attn_dbg) {
-            cudaFree(c->attn_dbg);
-            c->attn_dbg = nullptr;
-        }
-        return kOk;
-    }
     if (strcmp(name, "fuse_rope") == 0) {
         c->fuse_rope = value != 0;
         return kOk;
@@ -784,14 +772,6 @@ int fls_set_option(fls_ctx* c, const char* name, int value) {
         return kOk;
     }
     return ctx_fail(c, fail(kErrInvalid, "fls_set_option: unknown option '%s'", name));
-}
-
-int fls_get_attention_timing(fls_ctx* c, uint64_t* out8) {
-    ENTER(c);
-    if (!out8 || !c->attn_dbg) return ctx_fail(c, fail(kErrState, "attention timing is not enabled"));
-    CTX_CUDA(c, cudaDeviceSynchronize());
-    CTX_CUDA(c, cudaMemcpy(out8, c->attn_dbg, 8 * sizeof(uint64_t), cudaMemcpyDeviceToHost));
-    return kOk;
 }
 
 int fls_set_profiling(fls_ctx* c, int enabled) {

@@ -13,7 +13,8 @@
 //   warps 2-5   softmax, one query row per thread: tcgen05.ld S, mask, online softmax in fp32
 //               (base-2), P rounded to fp16 (as HF's softmax(..).to(fp16) @ V) and written with the
 //               128B swizzle over the K tile it came from (K is dead once S is complete), O row
-//               rescaled in TMEM only when the running max grows by more than 2^8, final O / l.
+//               rescaled in TMEM only when the running max grows by more than 2^8; final O / l staged
+//               through the (by then dead) Q buffer and written as full 128-byte lines.
 // S is double buffered: Q K^T of tile j+1 is issued before P V of tile j, so it runs while the
 // softmax warps work on tile j.  `pv_done` tells the softmax warps when O may be rescaled/read.
 // Shared memory: Q 32 KiB + 2 stages x 32 KiB = 96 KiB -> two CTAs per SM, whose softmax and MMA
@@ -50,7 +51,7 @@ __device__ __forceinline__ float ex2_approx(float x) {  // 2^x, one MUFU op; 2^-
 __global__ void __launch_bounds__(THREADS, 2)
 attention_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant__ CUtensorMap tmap_kv,
                          int n_q_heads, int n_kv_heads, const AttnTile* __restrict__ tiles, __half* __restrict__ out,
-                         int ld_out, float scale_log2e, unsigned long long* dbg) {
+                         int ld_out, float scale_log2e) {
     extern __shared__ uint8_t smem_raw[];
     uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
     uint8_t* sQ = smem;
@@ -305,8 +306,7 @@ int attention_sm100_init() {
 }
 
 int attention_sm100_launch(const __half* qkv, int ld, int n_rows, int n_q_heads, int n_kv_heads, const AttnTile* tiles,
-                           int n_tiles, __half* out, int ld_out, int num_sms, cudaStream_t s, unsigned long long* dbg) {
-    (void)num_sms;
+                           int n_tiles, __half* out, int ld_out, cudaStream_t s) {
     if (n_tiles <= 0) return kOk;
     if (ld_out % 8) return fail(kErrInvalid, "attention: ld_out must be a multiple of 8");
     if (n_kv_heads <= 0 || n_q_heads % n_kv_heads)
@@ -317,7 +317,7 @@ int attention_sm100_launch(const __half* qkv, int ld, int n_rows, int n_q_heads,
     FLS_TRY(encode_tmap_2d(&tkv, qkv, n_rows, cols, ld, BKV));
     const float scale_log2e = 1.4426950408889634f / sqrtf(static_cast<float>(D));
     attention_tcgen05_kernel<<<dim3(n_tiles, n_q_heads), THREADS, SMEM_BYTES, s>>>(tq, tkv, n_q_heads, n_kv_heads, tiles,
-                                                                                  out, ld_out, scale_log2e, dbg);
+                                                                                  out, ld_out, scale_log2e);
     FLS_CUDA(cudaGetLastError());
     return kOk;
 }

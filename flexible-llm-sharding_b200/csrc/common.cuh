@@ -104,8 +104,7 @@ int attention_launch(const __half* qkv, int ld, int n_q_heads, int n_kv_heads, i
 int attention_init();
 // tcgen05 version (head_dim 128); n_rows = rows of the qkv buffer (bounds the TMA tensor map)
 int attention_sm100_launch(const __half* qkv, int ld, int n_rows, int n_q_heads, int n_kv_heads, const AttnTile* tiles,
-                           int n_tiles, __half* out, int ld_out, int num_sms, cudaStream_t s,
-                           unsigned long long* dbg = nullptr);
+                           int n_tiles, __half* out, int ld_out, cudaStream_t s);
 int attention_sm100_init();
 
 // TMA descriptor over a row-major fp16 matrix [rows, cols] (row stride ld), box = 64 columns x box_rows,

@@ -244,12 +244,6 @@ int fls_get_profile(fls_ctx* ctx, fls_kernel_profile* out);
  * QKV GEMM epilogue when head_dim is 128) or 0 (separate kernel). */
 int fls_set_option(fls_ctx* ctx, const char* name, int value);
 
-/* In-kernel phase timing of the tcgen05 attention kernel (profiling aid; option "attention_timing" = 1
- * starts/resets it, 0 stops).  out8 = SM cycles summed over the sampled softmax warp of every CTA:
- * [0] wait for S, [1] tcgen05.ld of S, [2] softmax math, [3] wait for the previous P V (+ O rescale),
- * [4] P store + fences + arrive, [5] key tiles sampled, [6] item epilogue (O / l -> global), [7] items. */
-int fls_get_attention_timing(fls_ctx* ctx, uint64_t* out8);
-
 int fls_get_stats(fls_ctx* ctx, fls_stats* out);
 int fls_reset_stats(fls_ctx* ctx);
 

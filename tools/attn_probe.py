@@ -1,5 +1,5 @@
 """Micro-benchmark of the attention kernels on the 7B C2 shape (32 prompts x (384 + 4x32) rows, 32 heads)
-with the in-kernel phase timing of the tcgen05 kernel.  Run on a GPU box: python tools/attn_probe.py"""
+(tcgen05 kernel vs mma.sync kernel).  Run on a GPU box: python tools/attn_probe.py"""
 import ctypes as C
 import os
 import sys
@@ -41,12 +41,3 @@ for impl in (1, 0):
     run(3)
     us = run(20)
     print(f"impl {impl}: {us:.1f} us per launch, {flops / us / 1e6:.0f} TFLOP/s useful")
-ctx.call("fls_set_option", b"attention_impl", 1)
-ctx.call("fls_set_option", b"attention_timing", 1)
-run(1)
-buf = (C.c_uint64 * 8)()
-ctx.call("fls_get_attention_timing", C.cast(buf, C.c_void_p))
-v = list(buf)
-n = max(v[5], 1)
-print("cycles per key tile: waitS %.0f | ldS %.0f | math %.0f | waitPV+rescale %.0f | storeP+fence %.0f  (tiles %d); "
-      "item epilogue %.0f (items %d)" % (v[0] / n, v[1] / n, v[2] / n, v[3] / n, v[4] / n, v[5], v[6] / max(v[7], 1), v[7]))
