@@ -227,6 +227,9 @@ def main():
     ap.add_argument("--parallel", default="dp", choices=["dp", "mp"],
                     help="mp: ONE process drives all visible GPUs as a layer pipeline (not under torchrun)")
     a = ap.parse_args()
+    if os.environ.get("FLS_WATCHDOG_S"):      # debugging aid: dump every thread's stack and exit if the run stalls
+        import faulthandler
+        faulthandler.dump_traceback_later(int(os.environ["FLS_WATCHDOG_S"]), exit=True)
 
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
