@@ -329,6 +329,15 @@ int fls_create(const fls_model_desc* d, int device, fls_ctx** out) {
 
 int fls_destroy(fls_ctx* c) {
     if (!c) return kOk;
+    // may run from a garbage collector on any thread: leave that thread's current device as it was
+    int prev = -1;
+    cudaGetDevice(&prev);
+    struct Restore {
+        int d;
+        ~Restore() {
+            if (d >= 0) cudaSetDevice(d);
+        }
+    } restore{prev};
     cudaSetDevice(c->device);
     cudaDeviceSynchronize();
     free_workspace(c);

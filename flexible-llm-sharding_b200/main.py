@@ -62,7 +62,16 @@ def score_all(args, input_prompts, devices):
     """One pass over all prompts on all devices of this process (main.py:66-76)."""
     from .utils import DeviceManager
     device_manager = DeviceManager(args, devices)
-    run = partial(run_sharded_llama, device_manager=device_manager, args=args)
+
+    def run(device, prompt_list):
+        try:
+            return run_sharded_llama(device, prompt_list, device_manager=device_manager, args=args)
+        except BaseException as e:      # a dead worker must not leave its pipeline peers waiting (reference: they spin forever)
+            with device_manager.condition:
+                device_manager.failed = e
+                device_manager.condition.notify_all()
+            raise
+
     if len(devices) > 1:
         if args.data_parallel:
             parts = [input_prompts[lo:hi] for lo, hi in planner.partition_prompts(len(input_prompts), len(devices))]
