@@ -278,6 +278,8 @@ def main():
     torch.cuda.set_device(local)
     device = torch.device(f"cuda:{local}")
     if world > 1:
+        # stdout carries exactly one JSON line: keep NCCL's version banner out of it
+        os.environ["NCCL_DEBUG"] = os.environ.get("FLS_NCCL_DEBUG", "WARN")
         torch.distributed.init_process_group("nccl", device_id=device)
     import __graft_entry__ as ge
     if rank == 0:

@@ -128,7 +128,6 @@ def main(argv=None):
         if not devices:
             raise SystemExit("no CUDA device visible: this implementation has no CPU path")
 
-    from transformers import AutoTokenizer
     output_scores, tokenizer = [], None
     for i_new in range(args.num_gen_token):
         prompts_now = list(input_prompts)
@@ -136,7 +135,8 @@ def main(argv=None):
         if is_root:
             if i_new == 0:
                 output_scores = outputs
-                tokenizer = AutoTokenizer.from_pretrained(args.model_path)
+                from .utils import load_tokenizer
+                tokenizer = load_tokenizer(args.model_path)
                 tokenizer.pad_token = tokenizer.eos_token
             else:
                 output_scores = [np.concatenate((old, new), axis=1) for old, new in zip(output_scores, outputs)]

@@ -28,6 +28,16 @@ from .activation_store import ActivationStore
 
 max_token_len = planner.MAX_TOKEN_LEN  # reference utils.py:14
 
+_tokenizer_lock = threading.Lock()
+
+
+def load_tokenizer(model_path):
+    """AutoTokenizer.from_pretrained under a lock: the per-GPU worker threads construct their models at
+    the same time and transformers' lazy module import is not thread-safe."""
+    with _tokenizer_lock:
+        from transformers import AutoTokenizer
+        return AutoTokenizer.from_pretrained(model_path)
+
 
 def clean_memory():
     """Kept for API compatibility (reference utils.py:18-21).  Nothing to do: weight slots and
@@ -96,8 +106,7 @@ class ShardedLlama:
 
         with open(os.path.join(args.model_path, "config.json")) as f:
             self.config = json.load(f)
-        from transformers import AutoTokenizer
-        self.tokenizer = AutoTokenizer.from_pretrained(args.model_path)
+        self.tokenizer = load_tokenizer(args.model_path)
         self.tokenizer.pad_token = self.tokenizer.eos_token      # utils.py:103
         self.tokenizer.padding_side = "right"                    # utils.py:104
         cfg = self.config
