@@ -133,7 +133,8 @@ def model_dir_for(shape_name: str, rank: int, world: int, device, alias_layers: 
 def make_args(model_path, **kw):
     d = dict(model_path=model_path, num_batch=1, layer_num_per_shard=1, storage_location="gpu",
              max_activation_in_cpu=100, data_parallel=False, disk_folder="./temp", num_gen_token=1,
-             max_rows=16384, max_head_rows=4096)
+             max_rows=16384, max_head_rows=4096,
+             resident_weights="never")     # a bench step streams every shard from pinned host memory
     d.update(kw)
     return types.SimpleNamespace(**d)
 

@@ -358,7 +358,7 @@ int fls_destroy(fls_ctx* c) {
 
 int fls_configure(fls_ctx* c, int n_slots, size_t slot_bytes, int max_rows, int max_head_rows) {
     ENTER(c);
-    if (n_slots < 1 || n_slots > 8 || max_rows < 1 || max_head_rows < 1)
+    if (n_slots < 1 || n_slots > 512 || max_rows < 1 || max_head_rows < 1)
         return ctx_fail(c, fail(kErrInvalid, "fls_configure: n_slots %d, max_rows %d, max_head_rows %d", n_slots,
                                 max_rows, max_head_rows));
     CTX_CUDA(c, cudaDeviceSynchronize());
@@ -530,8 +530,11 @@ int fls_prefetch_shard(fls_ctx* c, int slot, const int32_t* layer_ids, int n) {
 
 int fls_acquire_shard(fls_ctx* c, int slot, void* stream) {
     ENTER(c);
-    if (slot < 0 || slot >= static_cast<int>(c->slots.size()) || !c->slots[slot].in_use)
+    if (slot < 0 || slot >= static_cast<int>(c->slots.size()) ||
+        (!c->slots[slot].in_use && c->slots[slot].layers.empty()))
         return ctx_fail(c, fail(kErrState, "fls_acquire_shard: slot %d has no prefetched shard", slot));
+    // a released slot that still holds its layers may be acquired again without a new copy (resident weights)
+    c->slots[slot].in_use = true;
     CTX_CUDA(c, cudaStreamWaitEvent(as_stream(stream), c->slots[slot].ready, 0));
     return kOk;
 }

@@ -30,7 +30,14 @@ from . import planner
 def run_sharded_llama(device, prompt_list, device_manager, args):
     """reference main.py:14-25."""
     from .utils import ShardedLlama
-    model = ShardedLlama(args, device_manager, device=device)
+    # The reference builds a new ShardedLlama per call (main.py:15); here the per-device model (CUDA context,
+    # pinned/HBM-resident weights) is kept on the DeviceManager and reused for later batches and tokens.
+    models = getattr(device_manager, "models", None)
+    model = models.get(device) if models is not None else None
+    if model is None:
+        model = ShardedLlama(args, device_manager, device=device)
+        if models is not None:
+            models[device] = model
     if not args.data_parallel and device != device_manager.devices[0]:  # don't need actual prompts
         prompt_list = [None] * len(prompt_list)
     outputs = []
@@ -58,10 +65,11 @@ def build_parser() -> argparse.ArgumentParser:
     return parser
 
 
-def score_all(args, input_prompts, devices):
+def score_all(args, input_prompts, devices, device_manager=None):
     """One pass over all prompts on all devices of this process (main.py:66-76)."""
     from .utils import DeviceManager
-    device_manager = DeviceManager(args, devices)
+    if device_manager is None:
+        device_manager = DeviceManager(args, devices)
 
     def run(device, prompt_list):
         try:
@@ -84,7 +92,7 @@ def score_all(args, input_prompts, devices):
     return run(devices[0], input_prompts)
 
 
-def score_all_distributed(args, input_prompts):
+def score_all_distributed(args, input_prompts, device_manager=None):
     """torchrun mode: rank r scores its np.array_split part on its own GPU; rank 0 gathers."""
     import torch
     import torch.distributed as dist
@@ -93,7 +101,7 @@ def score_all_distributed(args, input_prompts):
     lo, hi = planner.partition_prompts(len(input_prompts), world)[rank]
     from .utils import DeviceManager
     device = f"cuda:{local}"
-    dm = DeviceManager(args, [device])
+    dm = device_manager if device_manager is not None else DeviceManager(args, [device])
     mine = run_sharded_llama(device, input_prompts[lo:hi], dm, args)
     gathered = [None] * world if rank == 0 else None
     dist.gather_object(mine, gathered, dst=0)
@@ -128,10 +136,16 @@ def main(argv=None):
         if not devices:
             raise SystemExit("no CUDA device visible: this implementation has no CPU path")
 
+    from .utils import DeviceManager
+    if distributed:
+        device_manager = DeviceManager(args, [f"cuda:{int(os.environ.get('LOCAL_RANK', 0))}"])
+    else:
+        device_manager = DeviceManager(args, devices)          # created once, like main.py:61
     output_scores, tokenizer = [], None
     for i_new in range(args.num_gen_token):
         prompts_now = list(input_prompts)
-        outputs = score_all_distributed(args, prompts_now) if distributed else score_all(args, prompts_now, devices)
+        outputs = (score_all_distributed(args, prompts_now, device_manager) if distributed
+                   else score_all(args, prompts_now, devices, device_manager))
         if is_root:
             if i_new == 0:
                 output_scores = outputs

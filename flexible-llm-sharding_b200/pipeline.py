@@ -106,16 +106,13 @@ def _run(model, dm, inputs, shards, G, rank, serial, want_probs, answer_ids, ret
         nxt = None
         p2p_bytes = 0
 
-        def prefetch(i):
-            arr = (C.c_int32 * len(mine[i][1]))(*mine[i][1])
-            call("fls_prefetch_shard", i % 2, arr, len(mine[i][1]))
-
+        my_live = [s for _, s in mine]
         if mine:
-            prefetch(0)
+            model._stage_shard(my_live, 0)
         for i, (g, shard) in enumerate(mine):
-            slot = i % 2
+            slot = i % model._n_slots
             if i + 1 < len(mine):
-                prefetch(i + 1)
+                model._stage_shard(my_live, i + 1)
             call("fls_acquire_shard", slot, sp)
             tokens_in = shard[0] <= n_total - 2
             for bi, mb in enumerate(packed.micro_batches):

@@ -68,8 +68,9 @@ class DeviceManager:
         self.shared_activation_dict = dict()
         self.prompt2layer = defaultdict(lambda: -1)
         self.suffix_eos = []
-        self.handoff = {}          # (batch_serial, micro_batch, layer_idx) -> (tensor, event)
-        self.batch_serial = defaultdict(int)
+        self.handoff = {}          # pipeline hand-off board: packed prompts, peer buffers, events
+        self.models = {}           # device -> ShardedLlama, reused across batches / generated tokens
+        self.failed = None
 
     def send_device_request(self, device, layer):
         """Ask for `layer` to be resident in host memory (pinned)."""
@@ -120,6 +121,11 @@ class ShardedLlama:
         self.max_head_rows = int(getattr(args, "max_head_rows", 4096))
         self.force_tier = bool(getattr(args, "force_storage_tier", False) or os.environ.get("FLS_FORCE_STORAGE"))
         self.hbm_activation_budget = getattr(args, "hbm_activation_budget", None)
+        # Weight residency: "auto" keeps every shard of this rank in HBM across calls when they
+        # fit `resident_weight_fraction` of the free HBM (one slot per shard, streamed once); "never" always
+        # streams through two slots like the reference re-loads per call; "always" insists.
+        self.resident_weights = str(getattr(args, "resident_weights", os.environ.get("FLS_RESIDENT_WEIGHTS", "auto")))
+        self.resident_weight_fraction = float(getattr(args, "resident_weight_fraction", 0.5))
 
         H = cfg["hidden_size"]
         nh = cfg["num_attention_heads"]
@@ -154,11 +160,30 @@ class ShardedLlama:
         return shards, num_gpu, rank, dp
 
     def _configure(self, shards):
-        slot_bytes = max([sum(self._layer_bytes[i] for i in s) for s in shards if len(s)] + [256])
-        key = (slot_bytes, self.max_rows, self.max_head_rows)
+        live = [s for s in shards if len(s)]
+        slot_bytes = max([sum(self._layer_bytes[i] for i in s) for s in live] + [256])
+        n_slots = 2
+        if self.resident_weights in ("auto", "always") and len(live) > 2:
+            need = slot_bytes * len(live)
+            free = torch.cuda.mem_get_info(self.torch_device)[0] + (self._configured[0] * self._configured[3]
+                                                                    if self._configured else 0)
+            if self.resident_weights == "always" or need <= free * self.resident_weight_fraction:
+                n_slots = len(live)
+        key = (slot_bytes, self.max_rows, self.max_head_rows, n_slots)
         if self._configured != key:
-            self.ctx.call("fls_configure", 2, C.c_size_t(slot_bytes), self.max_rows, self.max_head_rows)
+            self.ctx.call("fls_configure", n_slots, C.c_size_t(slot_bytes), self.max_rows, self.max_head_rows)
             self._configured = key
+            self._slot_holds = {}            # slot -> shard currently held there
+        self._n_slots = n_slots
+
+    def _stage_shard(self, live, si):
+        """Start the H2D stream of shard `si` unless its slot already holds it (resident weights)."""
+        slot = si % self._n_slots
+        if self._slot_holds.get(slot) != live[si]:
+            arr = (C.c_int32 * len(live[si]))(*live[si])
+            self.ctx.call("fls_prefetch_shard", slot, arr, len(live[si]))
+            self._slot_holds[slot] = live[si]
+        return slot
 
     # ------------------------------------------------------------------ public call
     def __call__(self, inputs):
@@ -268,17 +293,12 @@ class ShardedLlama:
                                     hbm_budget_bytes=self.hbm_activation_budget, force_tier=self.force_tier)
             out = self._alloc_outputs(packed, dev, want_probs, answer_ids)
             live = [s for s in shards if len(s)]
-
-            def prefetch(si):
-                arr = (C.c_int32 * len(live[si]))(*live[si])
-                call("fls_prefetch_shard", si % 2, arr, len(live[si]))
-
             if live:
-                prefetch(0)
+                self._stage_shard(live, 0)
             for si, shard in enumerate(live):
-                slot = si % 2
+                slot = si % self._n_slots
                 if si + 1 < len(live):
-                    prefetch(si + 1)            # H2D of shard si+1 overlaps this shard's compute
+                    self._stage_shard(live, si + 1)   # H2D of shard si+1 overlaps this shard's compute
                 call("fls_acquire_shard", slot, sp)
                 has_input = shard[0] != 0
                 tokens_in = shard[0] <= n_layers_total - 2      # input is token-stage rows (incl. norm layer)

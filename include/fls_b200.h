@@ -100,8 +100,8 @@ const char* fls_last_error(const fls_ctx* ctx);
 int fls_create(const fls_model_desc* desc, int device, fls_ctx** out);
 int fls_destroy(fls_ctx* ctx);
 
-/* Reserve HBM: `n_slots` weight slots of `slot_bytes` each (2 = double buffering: shard k+1 is
- * copied while shard k computes) and workspace for micro-batches of up to `max_rows` token rows
+/* Reserve HBM: `n_slots` (1..512) weight slots of `slot_bytes` each (2 = double buffering: shard k+1 is
+ * copied while shard k computes; one per shard = resident weights) and workspace for micro-batches of up to `max_rows` token rows
  * and `max_head_rows` scored rows.  May be called again to resize (frees the old reservation). */
 int fls_configure(fls_ctx* ctx, int n_slots, size_t slot_bytes, int max_rows, int max_head_rows);
 
@@ -125,7 +125,10 @@ int fls_layer_slot_bytes(fls_ctx* ctx, int layer_idx, size_t* out_bytes);
 /* Enqueue the H2D copies of `n` layers into `slot` on the copy stream.  Waits (on the device) for
  * the slot's previous user to have released it. */
 int fls_prefetch_shard(fls_ctx* ctx, int slot, const int32_t* layer_ids, int n);
-/* Make `stream` wait until the slot's copies have landed (no host blocking). */
+/* Make `stream` wait until the slot's copies have landed (no host blocking).  A slot that was released
+ * but not overwritten still holds its layers and may be acquired again without a new prefetch: with one
+ * slot per shard the weights stay resident in HBM across passes (the reference re-reads
+ * every layer per batch and per generated token, main.py:22-23,65). */
 int fls_acquire_shard(fls_ctx* ctx, int slot, void* stream);
 /* Mark the slot reusable once everything enqueued on `stream` so far has finished.  Replaces
  * `layer.to("meta")` + clean_memory (utils.py:299-302). */

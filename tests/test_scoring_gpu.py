@@ -26,7 +26,8 @@ ANSWER_TOKEN = 5
 
 def make_args(model_path, **kw):
     d = dict(model_path=model_path, num_batch=1, layer_num_per_shard=1, storage_location="gpu",
-             max_activation_in_cpu=100, data_parallel=False, disk_folder="./temp", num_gen_token=1)
+             max_activation_in_cpu=100, data_parallel=False, disk_folder="./temp", num_gen_token=1,
+             resident_weights="never")
     d.update(kw)
     return types.SimpleNamespace(**d)
 
@@ -117,6 +118,24 @@ def test_kernel_variants_give_identical_scores(tiny_gqa):
     model.ctx.call("fls_set_option", b"attention_impl", 0)
     out = model(copy.deepcopy(tiny_gqa["prompts"]))
     check_against_reference(out, tiny_gqa["golden"]["probs32_ref"])
+
+
+def test_resident_weights_stream_once(tiny):
+    """with one HBM slot per shard the weights are streamed on the first pass only; later
+    passes (more batches, more generated tokens) reuse them and give the same scores."""
+    from flexible_llm_sharding_b200.utils import DeviceManager, ShardedLlama
+    _, base = run_model(tiny)
+    args = make_args(tiny["layer_dir"], resident_weights="always", layer_num_per_shard=2)
+    model = ShardedLlama(args, DeviceManager(args, ["cuda:0"]), device="cuda:0")
+    first = model(copy.deepcopy(tiny["prompts"]))
+    streamed = model.ctx.stats().h2d_bytes
+    assert streamed > 0
+    second = model(copy.deepcopy(tiny["prompts"][:2]))
+    assert model.ctx.stats().h2d_bytes == streamed            # nothing streamed again
+    for a, b in zip(first, base):
+        assert np.array_equal(a, b)
+    for a, b in zip(second, base[:2]):
+        assert np.array_equal(a, b)
 
 
 def test_fused_answer_token_logprobs(tiny):
