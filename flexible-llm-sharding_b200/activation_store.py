@@ -27,7 +27,7 @@ import torch
 class ActivationStore:
     def __init__(self, location: str, packed, hidden: int, device: torch.device, compute_stream,
                  disk_folder: str = "./temp", rank_tag: str = "", hbm_budget_bytes: int | None = None,
-                 force_tier: bool = False, max_rows: int = 0):
+                 force_tier: bool = False, max_rows: int = 0, pinned_pool: dict | None = None):
         assert location in ("gpu", "cpu", "disk"), location
         self.packed = packed
         self.H = hidden
@@ -59,10 +59,22 @@ class ActivationStore:
             self.d2h_done = [None] * 3
             self.loaded = {}     # micro-batch index -> staging slot holding it
             if tier == "cpu":
-                self.x_host = torch.empty((packed.total_rows, hidden), dtype=torch.float16).pin_memory()
+                self.x_host = self._pinned(pinned_pool, "x_host", packed.total_rows, hidden)
             else:
                 os.makedirs(disk_folder, exist_ok=True)
-                self.host_stage = torch.empty((cap, hidden), dtype=torch.float16).pin_memory()
+                self.host_stage = self._pinned(pinned_pool, "host_stage", cap, hidden)
+
+    @staticmethod
+    def _pinned(pool, name, rows, hidden):
+        """Page-locked [rows, hidden] fp16 buffer; page-locking a GB costs tenths of a second, so the owner
+        (ShardedLlama) keeps the largest one per name and hands it back on the next call."""
+        need = rows * hidden
+        if pool is not None and name in pool and pool[name].numel() >= need:
+            return pool[name][:need].view(rows, hidden)
+        buf = torch.empty(need, dtype=torch.float16).pin_memory()
+        if pool is not None:
+            pool[name] = buf
+        return buf.view(rows, hidden)
 
     # ------------------------------------------------------------------ token-stage rows
     def _slot(self, i: int) -> int:

@@ -149,6 +149,7 @@ class ShardedLlama:
                                        else max_token_len, self.head_dim, float(cfg.get("rope_theta", 10000.0)))
         self.ctx.call("fls_set_rope_table", cos.data_ptr(), sin.data_ptr(), cos.shape[0])
         self._configured = None
+        self._pinned_pool = {}
         self.last_timing = {}
 
     # ------------------------------------------------------------------ plan
@@ -290,7 +291,8 @@ class ShardedLlama:
             rank_tag = str(rank) if self.args.data_parallel else ""
             store = ActivationStore(self.args.storage_location, packed, self.hidden, dev, stream,
                                     disk_folder=getattr(self.args, "disk_folder", "./temp"), rank_tag=rank_tag,
-                                    hbm_budget_bytes=self.hbm_activation_budget, force_tier=self.force_tier)
+                                    hbm_budget_bytes=self.hbm_activation_budget, force_tier=self.force_tier,
+                                    pinned_pool=self._pinned_pool)
             out = self._alloc_outputs(packed, dev, want_probs, answer_ids)
             live = [s for s in shards if len(s)]
             if live:
