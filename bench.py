@@ -250,7 +250,8 @@ def main():
     if a.impl == "reference":
         if rank != 0:
             return
-        md = model_dir_for(shape_name, 0, 1, "cpu", 0 if shape_name != "70b" else alias)
+        gen_dev = torch.device("cuda:0") if torch.cuda.is_available() else "cpu"    # weight generation only
+        md = model_dir_for(shape_name, 0, 1, gen_dev, alias)
         prompts = synthetic.make_prompts(max(a.cpu_sample_prompts, 1), shape.vocab_size, prefix_tokens, n_options,
                                          option_tokens, seed=1234)
         vals = []

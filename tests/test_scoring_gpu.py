@@ -163,6 +163,32 @@ def test_oracle_on_fresh_inputs(tiny_gqa):
     check_against_reference(out, want)
 
 
+@pytest.mark.parametrize("causal", [False, True])
+def test_long_prompts_many_key_tiles(tiny_gqa, causal):
+    """Long prefix (11+ key tiles of 64, 6 query tiles) and options longer than one 128-row query tile
+    (an option is then cut into several tiles that see their own earlier rows), ragged lengths, one
+    micro-batch per prompt: CUDA vs the CPU oracle."""
+    from flexible_llm_sharding_b200 import synthetic
+    from oracle import llama_oracle as O
+    V = tiny_gqa["shape"].vocab_size
+    prompts = synthetic.make_prompts(2, V, 700, 2, 300, seed=11, ragged=True) + \
+        synthetic.make_prompts(1, V, 1, 3, 129, seed=12, ragged=True)          # BOS-only prefix
+    case = dict(tiny_gqa, prompts=prompts)
+    _, out = run_model(case, layer_num_per_shard=7, max_rows=1400, prefix_causal=causal)
+    orc = O.OracleShardedLlama(tiny_gqa["layer_dir"], dtype=torch.float32, prefix_causal=causal)
+    want = [s[:, 0] for s in orc(copy.deepcopy(prompts))]
+    for o, w in zip(out, want):
+        check_against_reference([o], w[None])
+
+
+def test_prompt_larger_than_a_micro_batch_is_rejected(tiny):
+    from flexible_llm_sharding_b200.utils import DeviceManager, ShardedLlama
+    args = make_args(tiny["layer_dir"], max_rows=64)
+    model = ShardedLlama(args, DeviceManager(args, ["cuda:0"]), device="cuda:0")
+    with pytest.raises(ValueError, match="raise max_rows"):
+        model(copy.deepcopy(tiny["prompts"]))
+
+
 def test_cli_round_trip(tiny, tmp_path):
     """main.py: pickle in -> pickles out, two generated tokens (reference main.py:55-56,65-98)."""
     from flexible_llm_sharding_b200.main import main
