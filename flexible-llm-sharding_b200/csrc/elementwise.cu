@@ -99,72 +99,6 @@ rmsnorm_kernel(const __half* __restrict__ x_in, const __half* __restrict__ delta
     }
 }
 
-// Warp-per-row variant (the hot one): a warp keeps its whole row in registers (VPL 16-byte vectors per
-// lane, all loads issued up front -> VPL independent 128-bit requests in flight per lane), reduces with
-// shuffles only (no block barrier), 8 rows per CTA.
-template <int VPL>
-__global__ void __launch_bounds__(256)
-rmsnorm_warp_kernel(const __half* __restrict__ x_in, const __half* __restrict__ delta,
-                    const int32_t* __restrict__ gather, const __half* __restrict__ w, float eps, int n_rows, int H,
-                    __half* __restrict__ x_sum, __half* __restrict__ out) {
-    const int r = blockIdx.x * 8 + (threadIdx.x >> 5);
-    if (r >= n_rows) return;
-    const int lane = threadIdx.x & 31;
-    const int src = gather ? gather[r] : r;
-    const int nvec = H / 8;
-    const __half* xr = x_in + static_cast<size_t>(src) * H;
-    uint4 v[VPL];
-#pragma unroll
-    for (int i = 0; i < VPL; ++i) {
-        const int vi = lane + i * 32;
-        v[i] = vi < nvec ? ptx::ld_nc_v4(xr + vi * 8) : make_uint4(0, 0, 0, 0);
-    }
-    if (delta) {
-#pragma unroll
-        for (int i = 0; i < VPL; ++i) {
-            const int vi = lane + i * 32;
-            if (vi < nvec) {
-                const uint4 d = ptx::ld_nc_v4(delta + static_cast<size_t>(r) * H + vi * 8);
-                __half2* a = reinterpret_cast<__half2*>(&v[i]);
-                const __half2* b = reinterpret_cast<const __half2*>(&d);
-#pragma unroll
-                for (int j = 0; j < 4; ++j) a[j] = __hadd2(a[j], b[j]);
-                *reinterpret_cast<uint4*>(x_sum + static_cast<size_t>(r) * H + vi * 8) = v[i];
-            }
-        }
-    }
-    float ss = 0.f;
-#pragma unroll
-    for (int i = 0; i < VPL; ++i) {
-        const __half2* h = reinterpret_cast<const __half2*>(&v[i]);
-#pragma unroll
-        for (int j = 0; j < 4; ++j) {
-            const float2 f = __half22float2(h[j]);
-            ss += f.x * f.x + f.y * f.y;
-        }
-    }
-    ss = warp_sum(ss);
-    const float rstd = rsqrtf(ss / static_cast<float>(H) + eps);
-#pragma unroll
-    for (int i = 0; i < VPL; ++i) {
-        const int vi = lane + i * 32;
-        if (vi < nvec) {
-            const uint4 wv = *reinterpret_cast<const uint4*>(w + vi * 8);
-            const __half2* h = reinterpret_cast<const __half2*>(&v[i]);
-            const __half2* wh = reinterpret_cast<const __half2*>(&wv);
-            uint4 o;
-            __half2* oh = reinterpret_cast<__half2*>(&o);
-#pragma unroll
-            for (int j = 0; j < 4; ++j) {
-                const float2 f = __half22float2(h[j]);
-                const __half2 y = __floats2half2_rn(f.x * rstd, f.y * rstd);  // .to(fp16) before the gain
-                oh[j] = __hmul2(wh[j], y);
-            }
-            *reinterpret_cast<uint4*>(out + static_cast<size_t>(r) * H + vi * 8) = o;
-        }
-    }
-}
-
 // ---------------------------------------------------------------------------------- RoPE
 // HF apply_rotary_pos_emb, half-split convention, evaluated in fp16 with a rounding after each
 // product and after the sum:  out[i]     = x[i]*cos[i]     + (-x[i+d/2])*sin[i]
@@ -310,25 +244,6 @@ int rmsnorm_launch(const __half* x_in, const __half* delta, const int32_t* gathe
     if (delta && !x_sum) return fail(kErrInvalid, "rmsnorm: residual input needs an x_sum output");
     if (n_rows <= 0) return kOk;
     const int nvec = H / 8;
-    const int vpl = (nvec + 31) / 32;
-    const int grid8 = (n_rows + 7) / 8;
-#define FLS_NORM_WARP(V)                                                                                        \
-    rmsnorm_warp_kernel<V><<<grid8, 256, 0, s>>>(x_in, delta, gather, w, eps, n_rows, H, x_sum, out_norm)
-    if (x_in != x_sum || !gather) {  // (a gathered in-place residual update would race between rows)
-        bool done = true;
-        if (vpl <= 2) FLS_NORM_WARP(2);
-        else if (vpl <= 4) FLS_NORM_WARP(4);
-        else if (vpl <= 8) FLS_NORM_WARP(8);
-        else if (vpl <= 16) FLS_NORM_WARP(16);
-        else if (vpl <= 20) FLS_NORM_WARP(20);
-        else if (vpl <= 32) FLS_NORM_WARP(32);
-        else done = false;
-        if (done) {
-            FLS_CUDA(cudaGetLastError());
-            return kOk;
-        }
-    }
-#undef FLS_NORM_WARP
     if (nvec <= 128)
         rmsnorm_kernel<128, 1><<<n_rows, 128, 0, s>>>(x_in, delta, gather, w, eps, n_rows, H, x_sum, out_norm);
     else if (nvec <= 256)
