@@ -53,8 +53,9 @@ class ActivationStore:
         else:
             cap = max(mb.n_rows for mb in packed.micro_batches)
             self.staging = [torch.empty((cap, hidden), dtype=torch.float16, device=device) for _ in range(3)]
-            self.h2d_stream = torch.cuda.Stream(device)
-            self.d2h_stream = torch.cuda.Stream(device)
+            # high priority: these copies gate compute, the (low-priority) weight stream does not
+            self.h2d_stream = torch.cuda.Stream(device, priority=-1)
+            self.d2h_stream = torch.cuda.Stream(device, priority=-1)
             self.h2d_done = [None] * 3
             self.d2h_done = [None] * 3
             self.loaded = {}     # micro-batch index -> staging slot holding it

@@ -1,4 +1,5 @@
 // C-ABI entry points (include/fls_b200.h): context, weight slots + copy stream, layer orchestration.
+#include <algorithm>
 #include <cstdarg>
 #include <cstring>
 #include <memory>
@@ -318,7 +319,10 @@ int fls_create(const fls_model_desc* d, int device, fls_ctx** out) {
     c->kv_dim = d->num_key_value_heads * d->head_dim;
     c->qkv_dim = c->q_dim + 2 * c->kv_dim;
     c->layers.resize(d->num_hidden_layers + 3);
-    cudaError_t e = cudaStreamCreateWithFlags(&c->copy_stream, cudaStreamNonBlocking);
+    // the weight stream yields to everything else that uses the copy engines (activation tiers, score D2H)
+    int prio_least = 0, prio_greatest = 0;
+    cudaDeviceGetStreamPriorityRange(&prio_least, &prio_greatest);
+    cudaError_t e = cudaStreamCreateWithPriority(&c->copy_stream, cudaStreamNonBlocking, prio_least);
     if (e != cudaSuccess) {
         delete c;
         return fail(kErrCuda, "cudaStreamCreate: %s", cudaGetErrorString(e));
@@ -488,8 +492,12 @@ int fls_prefetch_shard(fls_ctx* c, int slot, const int32_t* layer_ids, int n) {
     auto put = [&](const HostLayerImage& img, const char* suffix, const __half** dst) -> int {
         const TensorEntry* t = img.find(suffix);
         if (!t) return fail(kErrIo, "%s: tensor *%s is missing", img.path.c_str(), suffix);
-        FLS_CUDA(cudaMemcpyAsync(s.dev + off, img.pinned + t->host_off, t->numel * 2, cudaMemcpyHostToDevice,
-                                 c->copy_stream));
+        // 32 MiB pieces: other streams' copies (activation tiers) can slip in between instead of queueing
+        // behind a whole shard
+        const size_t total = t->numel * 2, piece = size_t(32) << 20;
+        for (size_t o = 0; o < total; o += piece)
+            FLS_CUDA(cudaMemcpyAsync(s.dev + off + o, img.pinned + t->host_off + o, std::min(piece, total - o),
+                                     cudaMemcpyHostToDevice, c->copy_stream));
         *dst = reinterpret_cast<const __half*>(s.dev + off);
         off += align256(t->numel * 2);
         return kOk;
