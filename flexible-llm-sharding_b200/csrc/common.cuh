@@ -60,6 +60,7 @@ struct GemmArgs {
     float2* partial;  // [M, ceil(N/256)]
     const float* lse;  // [M]
     int up_off;
+    int group_m;  // m-blocks per raster group (0 = default 16)
     // kEpiStoreRope: rotary position of every row and the fp16 cos/sin tables [n_pos, 128]
     const int32_t* row_pos;
     const __half* cos_tab;

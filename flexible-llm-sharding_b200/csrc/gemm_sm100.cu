@@ -50,7 +50,7 @@ struct Cfg {
 };
 constexpr int NUM_THREADS = 256;
 constexpr int EPI_WARP0 = 4;
-constexpr int GROUP_M = 16;  // m-blocks per raster group: A bands of a group stay in L2 while n sweeps
+constexpr int GROUP_M = 16;  // default m-blocks per raster group: A bands of a group stay in L2 while n sweeps
 
 struct KParams {
     int M, N, K;
@@ -61,6 +61,7 @@ struct KParams {
     float2* partial;
     const float* lse;
     int up_off;
+    int group_m;
     int num_m_blocks, num_n_blocks;
     const int32_t* row_pos;
     const __half* cos_tab;
@@ -73,11 +74,12 @@ __device__ __forceinline__ constexpr int out_cols_per_tile() {
     return EPI == kEpiSwiGLU ? BLOCK_N / 2 : BLOCK_N;
 }
 
-__device__ __forceinline__ void tile_coords(int tile, int num_m_blocks, int num_n_blocks, int& m_blk, int& n_blk) {
-    const int per_group = GROUP_M * num_n_blocks;
+__device__ __forceinline__ void tile_coords(int tile, int num_m_blocks, int num_n_blocks, int group_m, int& m_blk,
+                                            int& n_blk) {
+    const int per_group = group_m * num_n_blocks;
     const int group = tile / per_group;
-    const int first_m = group * GROUP_M;
-    const int gsize = min(num_m_blocks - first_m, GROUP_M);
+    const int first_m = group * group_m;
+    const int gsize = min(num_m_blocks - first_m, group_m);
     const int local = tile - group * per_group;
     m_blk = first_m + local % gsize;
     n_blk = local / gsize;
@@ -144,7 +146,7 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_con
             uint32_t phase = 0;
             for (int tile = worker; tile < num_tiles; tile += n_workers) {
                 int m_blk, n_blk;
-                tile_coords(tile, p.num_m_blocks, p.num_n_blocks, m_blk, n_blk);
+                tile_coords(tile, p.num_m_blocks, p.num_n_blocks, p.group_m, m_blk, n_blk);
                 const int a_row = (m_blk * CG + static_cast<int>(cta_rank)) * BLOCK_M;
                 int b_row;
                 if constexpr (EPI == kEpiSwiGLU)  // CG 2: leader stages the gate rows, its peer the up rows
@@ -227,7 +229,7 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_con
         uint32_t acc_phase = 0;
         for (int tile = worker; tile < num_tiles; tile += n_workers) {
             int m_blk, n_blk;
-            tile_coords(tile, p.num_m_blocks, p.num_n_blocks, m_blk, n_blk);
+            tile_coords(tile, p.num_m_blocks, p.num_n_blocks, p.group_m, m_blk, n_blk);
             ptx::mbar_wait(&tmem_full_bar[acc], acc_phase);
             ptx::tc_fence_after_sync();
             const int row = (m_blk * CG + static_cast<int>(cta_rank)) * BLOCK_M + ew * 32 + lane;
@@ -440,6 +442,7 @@ int launch_t(const GemmArgs& a, int num_sms, cudaStream_t stream) {
     p.M = a.M, p.N = a.N, p.K = a.K;
     p.C = a.C, p.ldc = a.ldc, p.R = a.R, p.ldr = a.ldr;
     p.partial = a.partial, p.lse = a.lse, p.up_off = a.up_off;
+    p.group_m = a.group_m > 0 ? a.group_m : GROUP_M;
     p.row_pos = a.row_pos, p.cos_tab = a.cos_tab, p.sin_tab = a.sin_tab, p.rope_cols = a.rope_cols;
     p.num_m_blocks = (a.M + BLOCK_M * CG - 1) / (BLOCK_M * CG);
     p.num_n_blocks = (a.N + OUT_COLS - 1) / OUT_COLS;
