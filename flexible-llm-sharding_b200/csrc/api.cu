@@ -98,6 +98,7 @@ struct fls_ctx {
     int gemm_cg = 2;  // tcgen05 cta_group of the GEMM kernels (2 = CTA pairs, 1 = single CTA)
     int attn_impl = 1;  // 1 = tcgen05 attention (head_dim 128), 0 = mma.sync attention
     int gemm_group_m = 0;  // raster group of the GEMM (0 = kernel default)
+    int gemm_cache_hints = 0;
     int fuse_rope = 1;  // 1 = rotary embedding in the QKV GEMM epilogue (head_dim 128), 0 = separate kernel
 };
 
@@ -718,6 +719,7 @@ int fls_op_gemm(fls_ctx* c, int epilogue, const uint16_t* a_dev, int lda, const 
     a.A = H(a_dev), a.lda = lda, a.B = H(b_dev), a.ldb = ldb, a.b_rows = b_rows, a.M = m, a.N = n, a.K = k;
     a.C = H(c_dev), a.ldc = ldc, a.R = H(r_dev), a.ldr = ldr, a.up_off = up_off;
     a.group_m = c->gemm_group_m;
+    a.cache_hints = c->gemm_cache_hints;
     CTX_TRY(c, gemm_launch(static_cast<GemmEpilogue>(epilogue), a, c->num_sms, as_stream(stream), c->gemm_cg));
     c->stats.kernel_launches += 1;
     return kOk;
@@ -782,6 +784,11 @@ int fls_set_option(fls_ctx* c, const char* name, int value) {
     if (strcmp(name, "gemm_cta_group") == 0) {
         if (value != 1 && value != 2) return ctx_fail(c, fail(kErrInvalid, "gemm_cta_group must be 1 or 2"));
         c->gemm_cg = value;
+        return kOk;
+    }
+    if (strcmp(name, "gemm_cache_hints") == 0) {
+        if (value < 0 || value > 2) return ctx_fail(c, fail(kErrInvalid, "gemm_cache_hints must be 0, 1 or 2"));
+        c->gemm_cache_hints = value;
         return kOk;
     }
     if (strcmp(name, "gemm_group_m") == 0) {

@@ -62,6 +62,7 @@ struct KParams {
     const float* lse;
     int up_off;
     int group_m;
+    int cache_hints;
     int num_m_blocks, num_n_blocks;
     const int32_t* row_pos;
     const __half* cos_tab;
@@ -172,8 +173,15 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_con
                         // both CTAs' bytes are credited to the leader's barrier (peer bit cleared)
                         if (is_leader) ptx::mbar_arrive_expect_tx(&full_bar[stage], 2 * STAGE_BYTES);
                         const uint32_t bar = ptx::smem_u32(&full_bar[stage]) & 0xFEFFFFFFu;
-                        ptx::tma_load_2d_cta2(sa, &tmap_a, bar, kb * BLOCK_K, a_row);
-                        ptx::tma_load_2d_cta2(sb, &tmap_b, bar, kb * BLOCK_K, b_row);
+                        if (p.cache_hints == 0) {
+                            ptx::tma_load_2d_cta2(sa, &tmap_a, bar, kb * BLOCK_K, a_row);
+                            ptx::tma_load_2d_cta2(sb, &tmap_b, bar, kb * BLOCK_K, b_row);
+                        } else {  // 1: stream A, keep B in L2;  2: keep A, stream B
+                            const uint64_t ha = p.cache_hints == 1 ? ptx::kL2EvictFirst : ptx::kL2EvictLast;
+                            const uint64_t hb = p.cache_hints == 1 ? ptx::kL2EvictLast : ptx::kL2EvictFirst;
+                            ptx::tma_load_2d_cta2_hint(sa, &tmap_a, bar, kb * BLOCK_K, a_row, ha);
+                            ptx::tma_load_2d_cta2_hint(sb, &tmap_b, bar, kb * BLOCK_K, b_row, hb);
+                        }
                     }
                     if (++stage == STAGES) {
                         stage = 0;
@@ -443,6 +451,7 @@ int launch_t(const GemmArgs& a, int num_sms, cudaStream_t stream) {
     p.C = a.C, p.ldc = a.ldc, p.R = a.R, p.ldr = a.ldr;
     p.partial = a.partial, p.lse = a.lse, p.up_off = a.up_off;
     p.group_m = a.group_m > 0 ? a.group_m : GROUP_M;
+    p.cache_hints = a.cache_hints;
     p.row_pos = a.row_pos, p.cos_tab = a.cos_tab, p.sin_tab = a.sin_tab, p.rope_cols = a.rope_cols;
     p.num_m_blocks = (a.M + BLOCK_M * CG - 1) / (BLOCK_M * CG);
     p.num_n_blocks = (a.N + OUT_COLS - 1) / OUT_COLS;

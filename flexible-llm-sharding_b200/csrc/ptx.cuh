@@ -87,6 +87,18 @@ __device__ __forceinline__ void tma_load_2d_cta2(void* smem_dst, const void* tma
         "l"(reinterpret_cast<uint64_t>(tmap)), "r"(bar_cluster_addr), "r"(c_inner), "r"(c_outer)
         : "memory");
 }
+// Same, with an L2 eviction-priority hint (createpolicy encodings: evict_first / evict_last / normal).
+constexpr uint64_t kL2EvictNormal = 0x1000000000000000ull;
+constexpr uint64_t kL2EvictFirst = 0x12F0000000000000ull;
+constexpr uint64_t kL2EvictLast = 0x14F0000000000000ull;
+__device__ __forceinline__ void tma_load_2d_cta2_hint(void* smem_dst, const void* tmap, uint32_t bar_cluster_addr,
+                                                      int32_t c_inner, int32_t c_outer, uint64_t policy) {
+    asm volatile(
+        "cp.async.bulk.tensor.2d.cta_group::2.shared::cluster.global.mbarrier::complete_tx::bytes.L2::cache_hint [%0], [%1, {%3, %4}], [%2], %5;\n" ::
+            "r"(smem_u32(smem_dst)),
+        "l"(reinterpret_cast<uint64_t>(tmap)), "r"(bar_cluster_addr), "r"(c_inner), "r"(c_outer), "l"(policy)
+        : "memory");
+}
 __device__ __forceinline__ uint32_t mapa_u32(uint32_t smem_addr, uint32_t cta_rank) {
     uint32_t r;
     asm volatile("mapa.shared::cluster.u32 %0, %1, %2;\n" : "=r"(r) : "r"(smem_addr), "r"(cta_rank));
