@@ -84,6 +84,7 @@ _SIGNATURES = {
     "fls_acquire_shard": (_I, [_P, _I, _P]),
     "fls_release_shard": (_I, [_P, _I, _P]),
     "fls_preload_layer_file": (_I, [C.c_char_p]),
+    "fls_set_host_cache_limit": (_I, [C.c_size_t]),
     "fls_trim_host_cache": (_I, [C.c_size_t]),
     "fls_peer_copy": (_I, [_P, _P, _I, _P, C.c_size_t, _P]),
     "fls_embed": (_I, [_P, _I, _I, _P, _I, _P, _P]),

@@ -528,6 +528,7 @@ int fls_prefetch_shard(fls_ctx* c, int slot, const int32_t* layer_ids, int n) {
         }
         s.layers.push_back(r);
         s.pins.push_back(L.img);
+        L.img.reset();  // the slot keeps the image alive while its copies fly; afterwards the cache may evict it
     }
     CTX_CUDA(c, cudaEventRecord(timing.b, c->copy_stream));
     timing.bytes = off;
@@ -564,6 +565,11 @@ int fls_preload_layer_file(const char* path) {
     if (!path) return fail(kErrInvalid, "fls_preload_layer_file: null path");
     std::shared_ptr<HostLayerImage> img;
     return acquire_host_image(path, &img);
+}
+
+int fls_set_host_cache_limit(size_t max_bytes) {
+    set_host_cache_limit(max_bytes);
+    return kOk;
 }
 
 int fls_trim_host_cache(size_t keep_bytes) {

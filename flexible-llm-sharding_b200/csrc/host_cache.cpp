@@ -118,6 +118,7 @@ std::unordered_map<std::string, CacheEntry> g_cache;
 std::atomic<uint64_t> g_clock{0};
 std::atomic<uint64_t> g_file_bytes{0};
 std::atomic<uint64_t> g_pinned_bytes{0};
+std::atomic<size_t> g_limit{0};
 
 int parallel_pread(int fd, char* dst, size_t off, size_t n) {
     const size_t chunk = size_t(32) << 20;
@@ -309,13 +310,19 @@ int acquire_host_image(const std::string& path_in, std::shared_ptr<HostLayerImag
     close(fd);
     if (rc != kOk) return rc;
 
-    std::lock_guard<std::mutex> lk(g_mu);
-    auto& slot = g_cache[path];
-    if (!slot.img) slot.img = img;
-    slot.last_use = ++g_clock;
-    *out = slot.img;
+    {
+        std::lock_guard<std::mutex> lk(g_mu);
+        auto& slot = g_cache[path];
+        if (!slot.img) slot.img = img;
+        slot.last_use = ++g_clock;
+        *out = slot.img;
+    }
+    img.reset();
+    if (const size_t lim = g_limit.load()) trim_host_cache(lim);  // `*out` is in use, so it survives
     return kOk;
 }
+
+void set_host_cache_limit(size_t max_bytes) { g_limit.store(max_bytes); }
 
 size_t trim_host_cache(size_t keep_bytes) {
     std::lock_guard<std::mutex> lk(g_mu);

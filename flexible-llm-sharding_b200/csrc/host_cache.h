@@ -37,6 +37,9 @@ int parse_safetensors_header(const std::string& path, std::vector<TensorEntry>* 
 int acquire_host_image(const std::string& path, std::shared_ptr<HostLayerImage>* out);
 // Evicts least-recently-used images nobody holds until at most keep_bytes remain; returns bytes held.
 size_t trim_host_cache(size_t keep_bytes);
+// Upper bound for the pinned bytes the cache keeps (0 = unlimited): beyond it, least-recently-used images that no
+// context is copying from are dropped whenever a new one is loaded (they are re-read from their files on next use).
+void set_host_cache_limit(size_t max_bytes);
 uint64_t host_cache_file_bytes();
 uint64_t host_cache_pinned_bytes();
 

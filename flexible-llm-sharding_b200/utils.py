@@ -148,9 +148,29 @@ class ShardedLlama:
                                        cfg.get("max_position_embeddings", max_token_len) >= max_token_len
                                        else max_token_len, self.head_dim, float(cfg.get("rope_theta", 10000.0)))
         self.ctx.call("fls_set_rope_table", cos.data_ptr(), sin.data_ptr(), cos.shape[0])
+        self._set_pinned_limit(getattr(args, "pinned_limit_bytes", os.environ.get("FLS_PINNED_LIMIT_BYTES", "auto")))
         self._configured = None
         self._pinned_pool = {}
         self.last_timing = {}
+
+    def _set_pinned_limit(self, limit):
+        """Bound the pinned host copies of the layer files (the reference's `max_layer_num`, utils.py:31, in bytes).
+        "auto": unlimited when the whole model fits 60 % of this process's share of the available host RAM,
+        otherwise that share - evicted layers are re-read from their files on the next pass."""
+        if limit == "auto":
+            limit = 0
+            try:
+                with open("/proc/meminfo") as f:
+                    avail_kb = next(int(l.split()[1]) for l in f if l.startswith("MemAvailable"))
+                share = int(avail_kb * 1024 * 0.6 / max(1, int(os.environ.get("LOCAL_WORLD_SIZE", "1"))))
+                if sum(self._layer_bytes) > share:
+                    limit = share
+            except (OSError, StopIteration, ValueError):
+                limit = 0
+        self.pinned_limit_bytes = int(limit)
+        rc = self.ctx.lib.fls_set_host_cache_limit(C.c_size_t(self.pinned_limit_bytes))
+        if rc != 0:
+            raise _lib.FlsError(rc, "fls_set_host_cache_limit failed")
 
     # ------------------------------------------------------------------ plan
     def _plan(self):

@@ -137,6 +137,11 @@ int fls_release_shard(fls_ctx* ctx, int slot, void* stream);
  * analogue of DeviceManager.send_device_request/clean_waiting_queue (utils.py:61-75).  Safe to call
  * from a reader thread running ahead of the GPU loop. */
 int fls_preload_layer_file(const char* path);
+/* Bound the pinned host memory of the process-wide layer cache (0 = unlimited, the default).  Beyond the bound
+ * the least recently used images that no slot is copying from are dropped and re-read from their files when
+ * needed again - the analogue of DeviceManager's max_layer_num (utils.py:31,70) for hosts that cannot hold the
+ * whole model in RAM. */
+int fls_set_host_cache_limit(size_t max_bytes);
 /* Drop pinned images no context needs any more (process-wide cache). */
 int fls_trim_host_cache(size_t keep_bytes);
 

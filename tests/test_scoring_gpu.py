@@ -138,6 +138,27 @@ def test_resident_weights_stream_once(tiny):
         assert np.array_equal(a, b)
 
 
+def test_bounded_pinned_cache_rereads_layers(tiny):
+    """With a pinned-host bound smaller than the model (hosts with little RAM: the reference's raison d'etre)
+    layer images are evicted after use and read from their files again on the next pass; scores unchanged."""
+    from flexible_llm_sharding_b200 import _lib
+    from flexible_llm_sharding_b200.utils import DeviceManager, ShardedLlama
+    _, base = run_model(tiny)
+    args = make_args(tiny["layer_dir"], pinned_limit_bytes=1)
+    model = ShardedLlama(args, DeviceManager(args, ["cuda:0"]), device="cuda:0")
+    try:
+        out1 = model(copy.deepcopy(tiny["prompts"]))
+        r1 = model.ctx.stats().file_bytes_read
+        out2 = model(copy.deepcopy(tiny["prompts"]))
+        st = model.ctx.stats()
+        assert st.file_bytes_read > r1                        # layers were read again
+        assert st.pinned_bytes < sum(model._layer_bytes)      # and not all of them are held
+        for a, b, c in zip(out1, out2, base):
+            assert np.array_equal(a, c) and np.array_equal(b, c)
+    finally:
+        _lib.load().fls_set_host_cache_limit(0)
+
+
 def test_fused_answer_token_logprobs(tiny):
     """lm_head + log-softmax + gather without the full-vocabulary output."""
     model, out = run_model(tiny)
