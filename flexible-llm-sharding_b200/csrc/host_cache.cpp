@@ -322,7 +322,10 @@ int acquire_host_image(const std::string& path_in, std::shared_ptr<HostLayerImag
     return kOk;
 }
 
-void set_host_cache_limit(size_t max_bytes) { g_limit.store(max_bytes); }
+void set_host_cache_limit(size_t max_bytes) {
+    g_limit.store(max_bytes);
+    if (max_bytes) trim_host_cache(max_bytes);
+}
 
 size_t trim_host_cache(size_t keep_bytes) {
     std::lock_guard<std::mutex> lk(g_mu);
