@@ -793,7 +793,7 @@ int fls_set_option(fls_ctx* c, const char* name, int value) {
         return kOk;
     }
     if (strcmp(name, "gemm_cache_hints") == 0) {
-        if (value < 0 || value > 2) return ctx_fail(c, fail(kErrInvalid, "gemm_cache_hints must be 0, 1 or 2"));
+        if (value < 0 || value > 4) return ctx_fail(c, fail(kErrInvalid, "gemm_cache_hints must be 0..4"));
         c->gemm_cache_hints = value;
         return kOk;
     }

@@ -176,9 +176,11 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_con
                         if (p.cache_hints == 0) {
                             ptx::tma_load_2d_cta2(sa, &tmap_a, bar, kb * BLOCK_K, a_row);
                             ptx::tma_load_2d_cta2(sb, &tmap_b, bar, kb * BLOCK_K, b_row);
-                        } else {  // 1: stream A, keep B in L2;  2: keep A, stream B
-                            const uint64_t ha = p.cache_hints == 1 ? ptx::kL2EvictFirst : ptx::kL2EvictLast;
-                            const uint64_t hb = p.cache_hints == 1 ? ptx::kL2EvictLast : ptx::kL2EvictFirst;
+                        } else {  // 1: stream A, keep B in L2;  2: keep A, stream B;  3: A normal, keep B;  4: keep A, B normal
+                            const uint64_t ha = p.cache_hints == 1 ? ptx::kL2EvictFirst
+                                                : p.cache_hints == 3 ? ptx::kL2EvictNormal : ptx::kL2EvictLast;
+                            const uint64_t hb = p.cache_hints == 2 ? ptx::kL2EvictFirst
+                                                : p.cache_hints == 4 ? ptx::kL2EvictNormal : ptx::kL2EvictLast;
                             ptx::tma_load_2d_cta2_hint(sa, &tmap_a, bar, kb * BLOCK_K, a_row, ha);
                             ptx::tma_load_2d_cta2_hint(sb, &tmap_b, bar, kb * BLOCK_K, b_row, hb);
                         }

@@ -14,6 +14,8 @@ from flexible_llm_sharding_b200 import _lib
 ap = argparse.ArgumentParser()
 ap.add_argument("--secs", type=float, default=1.5)
 ap.add_argument("--groups", type=int, nargs="+", default=[16])
+ap.add_argument("--hints", type=int, nargs="*", default=[])
+ap.add_argument("--hint_groups", type=int, nargs="*", default=[16])
 a = ap.parse_args()
 
 ctx = _lib.Context(_lib.ModelDesc(4096, 11008, 32, 32, 128, 32000, 2, 1e-5), 0)
@@ -57,6 +59,13 @@ for name, epi, N, K in SHAPES:
             ctx.call("fls_set_option", b"gemm_group_m", g)
             res[f"cg{cg}/group{g}"] = round(sustained(ours, flops))
     ctx.call("fls_set_option", b"gemm_cta_group", 2)
+    ctx.call("fls_set_option", b"gemm_group_m", 0)
+    for hint in a.hints:
+        ctx.call("fls_set_option", b"gemm_cache_hints", hint)
+        for g in a.hint_groups:
+            ctx.call("fls_set_option", b"gemm_group_m", g)
+            res[f"cg2/group{g}/hint{hint}"] = round(sustained(ours, flops))
+    ctx.call("fls_set_option", b"gemm_cache_hints", 0)
     ctx.call("fls_set_option", b"gemm_group_m", 0)
     if epi == 1:      # the same shape with the plain-store epilogue: what does the fused residual cost?
         def plain():
