@@ -50,6 +50,15 @@ struct Slot {
     bool freed_valid = false;  // `freed` has been recorded at least once since the last prefetch
     std::vector<ResidentLayer> layers;
     std::vector<std::shared_ptr<HostLayerImage>> pins;  // keep host images alive while copies fly
+    // paced weight stream: copies prepared by fls_prefetch_shard but enqueued piecewise by fls_prefetch_pump
+    struct CopyOp {
+        char* dst;
+        const char* src;
+        size_t bytes;
+    };
+    std::vector<CopyOp> pending_ops;
+    size_t next_op = 0;
+    int timing_idx = -1;
 };
 
 }  // namespace
@@ -97,6 +106,7 @@ struct fls_ctx {
     unsigned long long peer_enabled_mask = 0;
     int gemm_cg = 2;  // tcgen05 cta_group of the GEMM kernels (2 = CTA pairs, 1 = single CTA)
     int attn_impl = 1;  // 1 = tcgen05 attention (head_dim 128), 0 = mma.sync attention
+    int paced_stream = 0;  // 1: fls_prefetch_shard only prepares the copies; fls_prefetch_pump enqueues them
     int gemm_group_m = 0;  // raster group of the GEMM (0 = kernel default)
     int gemm_cache_hints = 0;
     int fuse_rope = 1;  // 1 = rotary embedding in the QKV GEMM epilogue (head_dim 128), 0 = separate kernel
@@ -287,6 +297,31 @@ int head_impl(fls_ctx* c, const __half* x, const __half* W, int n_rows, int V, i
     return kOk;
 }
 
+}  // namespace
+
+namespace {
+// Enqueue up to `max_bytes` of a slot's prepared weight copies on the copy stream; once the last one is
+// in, record the timing and `ready` events.
+int pump_slot(fls_ctx* c, Slot& s, size_t max_bytes) {
+    if (s.next_op >= s.pending_ops.size() && s.timing_idx < 0) return kOk;
+    fls_ctx::CopyTiming& timing = c->copy_ring[s.timing_idx];
+    if (s.next_op == 0) FLS_CUDA(cudaEventRecord(timing.a, c->copy_stream));
+    size_t done = 0;
+    while (s.next_op < s.pending_ops.size() && done < max_bytes) {
+        const Slot::CopyOp& op = s.pending_ops[s.next_op++];
+        FLS_CUDA(cudaMemcpyAsync(op.dst, op.src, op.bytes, cudaMemcpyHostToDevice, c->copy_stream));
+        done += op.bytes;
+    }
+    if (s.next_op >= s.pending_ops.size()) {
+        FLS_CUDA(cudaEventRecord(timing.b, c->copy_stream));
+        timing.pending = true;
+        FLS_CUDA(cudaEventRecord(s.ready, c->copy_stream));
+        s.pending_ops.clear();
+        s.next_op = 0;
+        s.timing_idx = -1;
+    }
+    return kOk;
+}
 }  // namespace
 
 // =============================================================================================
@@ -487,9 +522,11 @@ int fls_prefetch_shard(fls_ctx* c, int slot, const int32_t* layer_ids, int n) {
         }
     }
     for (auto& t : c->copy_ring) harvest_copy_timing(c, t, false);
-    fls_ctx::CopyTiming& timing = c->copy_ring[c->copy_next++ % c->copy_ring.size()];
+    s.timing_idx = static_cast<int>(c->copy_next++ % c->copy_ring.size());
+    fls_ctx::CopyTiming& timing = c->copy_ring[s.timing_idx];
     harvest_copy_timing(c, timing, true);  // only blocks if 64 shard copies are still in flight
-    CTX_CUDA(c, cudaEventRecord(timing.a, c->copy_stream));
+    s.pending_ops.clear();
+    s.next_op = 0;
     size_t off = 0;
     auto put = [&](const HostLayerImage& img, const char* suffix, const __half** dst) -> int {
         const TensorEntry* t = img.find(suffix);
@@ -498,8 +535,7 @@ int fls_prefetch_shard(fls_ctx* c, int slot, const int32_t* layer_ids, int n) {
         // behind a whole shard
         const size_t total = t->numel * 2, piece = size_t(32) << 20;
         for (size_t o = 0; o < total; o += piece)
-            FLS_CUDA(cudaMemcpyAsync(s.dev + off + o, img.pinned + t->host_off + o, std::min(piece, total - o),
-                                     cudaMemcpyHostToDevice, c->copy_stream));
+            s.pending_ops.push_back({s.dev + off + o, img.pinned + t->host_off + o, std::min(piece, total - o)});
         *dst = reinterpret_cast<const __half*>(s.dev + off);
         off += align256(t->numel * 2);
         return kOk;
@@ -530,12 +566,18 @@ int fls_prefetch_shard(fls_ctx* c, int slot, const int32_t* layer_ids, int n) {
         s.pins.push_back(L.img);
         L.img.reset();  // the slot keeps the image alive while its copies fly; afterwards the cache may evict it
     }
-    CTX_CUDA(c, cudaEventRecord(timing.b, c->copy_stream));
     timing.bytes = off;
-    timing.pending = true;
-    CTX_CUDA(c, cudaEventRecord(s.ready, c->copy_stream));
     s.in_use = true;
     s.freed_valid = false;
+    if (!c->paced_stream) CTX_TRY(c, pump_slot(c, s, ~size_t(0)));
+    return kOk;
+}
+
+int fls_prefetch_pump(fls_ctx* c, int slot, size_t max_bytes) {
+    ENTER(c);
+    if (slot < 0 || slot >= static_cast<int>(c->slots.size()))
+        return ctx_fail(c, fail(kErrInvalid, "fls_prefetch_pump: slot %d", slot));
+    CTX_TRY(c, pump_slot(c, c->slots[slot], max_bytes));
     return kOk;
 }
 
@@ -546,6 +588,7 @@ int fls_acquire_shard(fls_ctx* c, int slot, void* stream) {
         return ctx_fail(c, fail(kErrState, "fls_acquire_shard: slot %d has no prefetched shard", slot));
     // a released slot that still holds its layers may be acquired again without a new copy (resident weights)
     c->slots[slot].in_use = true;
+    CTX_TRY(c, pump_slot(c, c->slots[slot], ~size_t(0)));  // paced stream: whatever is still pending goes in now
     CTX_CUDA(c, cudaStreamWaitEvent(as_stream(stream), c->slots[slot].ready, 0));
     return kOk;
 }
@@ -795,6 +838,10 @@ int fls_set_option(fls_ctx* c, const char* name, int value) {
     if (strcmp(name, "gemm_cache_hints") == 0) {
         if (value < 0 || value > 4) return ctx_fail(c, fail(kErrInvalid, "gemm_cache_hints must be 0..4"));
         c->gemm_cache_hints = value;
+        return kOk;
+    }
+    if (strcmp(name, "paced_weight_stream") == 0) {
+        c->paced_stream = value != 0;
         return kOk;
     }
     if (strcmp(name, "gemm_group_m") == 0) {

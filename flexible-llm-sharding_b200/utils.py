@@ -315,26 +315,37 @@ class ShardedLlama:
                                     pinned_pool=self._pinned_pool)
             out = self._alloc_outputs(packed, dev, want_probs, answer_ids)
             live = [s for s in shards if len(s)]
-            if live:
-                self._stage_shard(live, 0)
-            for si, shard in enumerate(live):
-                slot = si % self._n_slots
-                if si + 1 < len(live):
-                    self._stage_shard(live, si + 1)   # H2D of shard si+1 overlaps this shard's compute
-                call("fls_acquire_shard", slot, sp)
-                has_input = shard[0] != 0
-                tokens_in = shard[0] <= n_layers_total - 2      # input is token-stage rows (incl. norm layer)
-                for bi, mb in enumerate(mbs):
-                    if tokens_in:
-                        store.prefetch(bi + 1, has_input)
-                        x = store.fetch(bi, has_input)
-                    else:
-                        x = store.heads_view(bi)
-                    y, still_tokens = self._run_layers(slot, shard, bi, mb, x, store.heads_view(bi), dv, out, sp)
-                    if tokens_in:
-                        store.store(bi, x, keep_tokens=still_tokens)
-                store.end_shard()
-                call("fls_release_shard", slot, sp)
+            # Host/disk activation tiers copy rows host->device on the same copy engine as the weight stream, which
+            # serves requests in arrival order: pace the stream (a slice per micro-batch) so those copies interleave.
+            paced = store.tier != "gpu"
+            call("fls_set_option", b"paced_weight_stream", int(paced))
+            try:
+                if live:
+                    self._stage_shard(live, 0)
+                for si, shard in enumerate(live):
+                    slot = si % self._n_slots
+                    nxt_slot, nxt_slice = None, 0
+                    if si + 1 < len(live):
+                        nxt_slot = self._stage_shard(live, si + 1)   # H2D of shard si+1 overlaps this shard's compute
+                        nxt_slice = sum(self._layer_bytes[i] for i in live[si + 1]) // max(1, len(mbs)) + (1 << 20)
+                    call("fls_acquire_shard", slot, sp)
+                    has_input = shard[0] != 0
+                    tokens_in = shard[0] <= n_layers_total - 2      # input is token-stage rows (incl. norm layer)
+                    for bi, mb in enumerate(mbs):
+                        if tokens_in:
+                            store.prefetch(bi + 1, has_input)
+                            x = store.fetch(bi, has_input)
+                        else:
+                            x = store.heads_view(bi)
+                        if paced and nxt_slot is not None:
+                            call("fls_prefetch_pump", nxt_slot, C.c_size_t(nxt_slice))
+                        y, still_tokens = self._run_layers(slot, shard, bi, mb, x, store.heads_view(bi), dv, out, sp)
+                        if tokens_in:
+                            store.store(bi, x, keep_tokens=still_tokens)
+                    store.end_shard()
+                    call("fls_release_shard", slot, sp)
+            finally:
+                call("fls_set_option", b"paced_weight_stream", 0)
 
             result, out_bytes = None, 0
             if any(n_layers_total - 1 in s for s in live):

@@ -125,6 +125,11 @@ int fls_layer_slot_bytes(fls_ctx* ctx, int layer_idx, size_t* out_bytes);
 /* Enqueue the H2D copies of `n` layers into `slot` on the copy stream.  Waits (on the device) for
  * the slot's previous user to have released it. */
 int fls_prefetch_shard(fls_ctx* ctx, int slot, const int32_t* layer_ids, int n);
+/* Paced weight stream (option "paced_weight_stream" = 1): fls_prefetch_shard only prepares the shard's copies and
+ * fls_prefetch_pump enqueues the next `max_bytes` of them; fls_acquire_shard enqueues whatever is left.  The copy
+ * engine serves requests in arrival order, so a whole shard enqueued at once would make every later host->device
+ * copy of the caller (activation tiers) wait for it; pumping a slice per micro-batch interleaves the two. */
+int fls_prefetch_pump(fls_ctx* ctx, int slot, size_t max_bytes);
 /* Make `stream` wait until the slot's copies have landed (no host blocking).  A slot that was released
  * but not overwritten still holds its layers and may be acquired again without a new prefetch: with one
  * slot per shard the weights stay resident in HBM across passes (the reference re-reads
@@ -249,7 +254,8 @@ int fls_get_profile(fls_ctx* ctx, fls_kernel_profile* out);
 /* Tuning knobs.  "gemm_cta_group": 2 (default; CTA pairs share a 256x256 tile through
  * tcgen05 cta_group::2) or 1 (one CTA per 128x256 tile).  "attention_impl": 1 (default; tcgen05
  * kernel for head_dim 128) or 0 (mma.sync kernel).  "fuse_rope": 1 (default; rotary embedding applied in the
- * QKV GEMM epilogue when head_dim is 128) or 0 (separate kernel). */
+ * QKV GEMM epilogue when head_dim is 128) or 0 (separate kernel).  "paced_weight_stream": see fls_prefetch_pump.
+ * "gemm_group_m", "gemm_cache_hints": raster group / L2 hint experiments (tools/gemm_probe.py), default 0. */
 int fls_set_option(fls_ctx* ctx, const char* name, int value);
 
 int fls_get_stats(fls_ctx* ctx, fls_stats* out);
