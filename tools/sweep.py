@@ -61,12 +61,17 @@ def main():
             model = ShardedLlama(args, DeviceManager(args, [str(dev)]), device=str(dev))
             model(copy.deepcopy(prompts))                              # warm pass (reads layer files, warms allocators)
             torch.cuda.synchronize()
+            model.ctx.call("fls_reset_stats")
+            model.ctx.call("fls_set_profiling", 1)
             s0 = model.ctx.stats()
             t0 = time.perf_counter()
             out = model(copy.deepcopy(prompts))
             torch.cuda.synchronize()
             dt = time.perf_counter() - t0
             s1 = model.ctx.stats()
+            prof = model.ctx.profile()
+            model.ctx.call("fls_set_profiling", 0)
+            kernel_s = sum(v["ms"] for v in prof.values()) / 1e3
             sig = np.stack([o[:, 0] for o in out])
             if first is None:
                 first = sig
@@ -74,7 +79,7 @@ def main():
             lt = model.last_timing
             rows.append({"layer_num_per_shard": k, "storage_location": storage, "tier_used": lt["activation_tier"],
                          "prompts_per_s": a.prompts / dt, "rows_per_s": a.prompts * rows_per_prompt / dt,
-                         "s_per_pass": dt, "activation_h2d_GB": lt["act_h2d_bytes"] / 1e9,
+                         "s_per_pass": dt, "kernel_s": kernel_s, "tokenize_s": lt["tokenize_s"], "activation_h2d_GB": lt["act_h2d_bytes"] / 1e9,
                          "activation_d2h_GB": lt["act_d2h_bytes"] / 1e9,
                          "weight_stream_GBps": ((s1.h2d_bytes - s0.h2d_bytes) / max(s1.h2d_ms - s0.h2d_ms, 1e-9) / 1e6),
                          "scores_identical_to_first": same})
