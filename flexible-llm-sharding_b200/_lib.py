@@ -81,7 +81,7 @@ _SIGNATURES = {
     "fls_register_layer_file": (_I, [_P, _I, _I, C.c_char_p, _I]),
     "fls_layer_slot_bytes": (_I, [_P, _I, C.POINTER(C.c_size_t)]),
     "fls_prefetch_shard": (_I, [_P, _I, C.POINTER(C.c_int32), _I]),
-    "fls_prefetch_pump": (_I, [_P, _I, C.c_size_t]),
+    "fls_prefetch_pump": (_I, [_P, _I, C.c_size_t, _P]),
     "fls_acquire_shard": (_I, [_P, _I, _P]),
     "fls_release_shard": (_I, [_P, _I, _P]),
     "fls_preload_layer_file": (_I, [C.c_char_p]),

@@ -106,6 +106,9 @@ struct fls_ctx {
     unsigned long long peer_enabled_mask = 0;
     int gemm_cg = 2;  // tcgen05 cta_group of the GEMM kernels (2 = CTA pairs, 1 = single CTA)
     int attn_impl = 1;  // 1 = tcgen05 attention (head_dim 128), 0 = mma.sync attention
+    std::vector<cudaEvent_t> pace_events;
+    size_t pace_next = 0;
+    bool pace_always_gate = false;
     int paced_stream = 0;  // 1: fls_prefetch_shard only prepares the copies; fls_prefetch_pump enqueues them
     int gemm_group_m = 0;  // raster group of the GEMM (0 = kernel default)
     int gemm_cache_hints = 0;
@@ -393,6 +396,7 @@ int fls_destroy(fls_ctx* c) {
         cudaEventDestroy(t.a);
         cudaEventDestroy(t.b);
     }
+    for (auto& e : c->pace_events) cudaEventDestroy(e);
     delete c;
     return kOk;
 }
@@ -573,10 +577,21 @@ int fls_prefetch_shard(fls_ctx* c, int slot, const int32_t* layer_ids, int n) {
     return kOk;
 }
 
-int fls_prefetch_pump(fls_ctx* c, int slot, size_t max_bytes) {
+int fls_prefetch_pump(fls_ctx* c, int slot, size_t max_bytes, void* after_stream) {
     ENTER(c);
     if (slot < 0 || slot >= static_cast<int>(c->slots.size()))
         return ctx_fail(c, fail(kErrInvalid, "fls_prefetch_pump: slot %d", slot));
+    if (after_stream != nullptr || c->pace_always_gate) {
+        // hold this slice back until the work enqueued on `after_stream` so far has run: the pacing then follows
+        // the GPU's progress, not the (far ahead) host's
+        if (c->pace_events.empty()) {
+            c->pace_events.resize(64);
+            for (auto& e : c->pace_events) CTX_CUDA(c, cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
+        }
+        cudaEvent_t e = c->pace_events[c->pace_next++ % c->pace_events.size()];
+        CTX_CUDA(c, cudaEventRecord(e, as_stream(after_stream)));
+        CTX_CUDA(c, cudaStreamWaitEvent(c->copy_stream, e, 0));
+    }
     CTX_TRY(c, pump_slot(c, c->slots[slot], max_bytes));
     return kOk;
 }

@@ -338,7 +338,7 @@ class ShardedLlama:
                         else:
                             x = store.heads_view(bi)
                         if paced and nxt_slot is not None:
-                            call("fls_prefetch_pump", nxt_slot, C.c_size_t(nxt_slice))
+                            call("fls_prefetch_pump", nxt_slot, C.c_size_t(nxt_slice), sp)
                         y, still_tokens = self._run_layers(slot, shard, bi, mb, x, store.heads_view(bi), dv, out, sp)
                         if tokens_in:
                             store.store(bi, x, keep_tokens=still_tokens)

@@ -128,8 +128,10 @@ int fls_prefetch_shard(fls_ctx* ctx, int slot, const int32_t* layer_ids, int n);
 /* Paced weight stream (option "paced_weight_stream" = 1): fls_prefetch_shard only prepares the shard's copies and
  * fls_prefetch_pump enqueues the next `max_bytes` of them; fls_acquire_shard enqueues whatever is left.  The copy
  * engine serves requests in arrival order, so a whole shard enqueued at once would make every later host->device
- * copy of the caller (activation tiers) wait for it; pumping a slice per micro-batch interleaves the two. */
-int fls_prefetch_pump(fls_ctx* ctx, int slot, size_t max_bytes);
+ * copy of the caller (activation tiers) wait for it; pumping a slice per micro-batch interleaves the two.  With
+ * `after_stream` non-NULL the slice is additionally held back until everything enqueued on that stream so far has
+ * run, so the pacing follows the GPU's progress rather than the host's. */
+int fls_prefetch_pump(fls_ctx* ctx, int slot, size_t max_bytes, void* after_stream);
 /* Make `stream` wait until the slot's copies have landed (no host blocking).  A slot that was released
  * but not overwritten still holds its layers and may be acquired again without a new prefetch: with one
  * slot per shard the weights stay resident in HBM across passes (the reference re-reads
