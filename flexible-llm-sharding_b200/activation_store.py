@@ -59,6 +59,9 @@ class ActivationStore:
             self.h2d_done = [None] * 3
             self.d2h_done = [None] * 3
             self.loaded = {}     # micro-batch index -> staging slot holding it
+            self.seq = 0         # staging slots rotate over ALL fetches, so a shard's first micro-batch can be
+            #                      brought in while the previous shard's last one still computes
+            self.saved = {}      # micro-batch index -> event: its rows' latest version is in host memory
             if tier == "cpu":
                 self.x_host = self._pinned(pinned_pool, "x_host", packed.total_rows, hidden)
             else:
@@ -78,20 +81,32 @@ class ActivationStore:
         return buf.view(rows, hidden)
 
     # ------------------------------------------------------------------ token-stage rows
-    def _slot(self, i: int) -> int:
-        return i % 3
+    def _take_slot(self) -> int:
+        s = self.seq % 3
+        self.seq += 1
+        return s
 
     def prefetch(self, i: int, has_input: bool):
-        """Start bringing micro-batch i into HBM (no-op for the gpu tier)."""
-        if self.tier == "gpu" or i >= len(self.packed.micro_batches) or i in self.loaded:
+        """Start bringing micro-batch i into HBM (no-op for the gpu tier).  `i == len(micro_batches)` names the
+        first micro-batch of the NEXT shard: the caller passes it only when another token-stage shard follows."""
+        n = len(self.packed.micro_batches)
+        if self.tier == "gpu" or i > n:
+            return
+        if i == n:
+            i = 0
+            if not has_input or n < 2 or i not in self.saved:
+                return                                     # its rows are not in host memory yet
+        if i in self.loaded:
             return
         mb = self.packed.micro_batches[i]
-        s = self._slot(i)
+        s = self._take_slot()
         buf = self.staging[s][:mb.n_rows]
         if has_input:
             with torch.cuda.stream(self.h2d_stream):
                 if self.d2h_done[s] is not None:           # previous tenant fully written back
                     self.h2d_stream.wait_event(self.d2h_done[s])
+                if i in self.saved:                        # and these rows' own write-back has landed
+                    self.h2d_stream.wait_event(self.saved[i])
                 if self.tier == "cpu":
                     buf.copy_(self.x_host[mb.row_lo:mb.row_lo + mb.n_rows], non_blocking=True)
                 else:
@@ -136,10 +151,10 @@ class ActivationStore:
             done = torch.cuda.Event()
             done.record(self.d2h_stream)
             self.d2h_done[s] = done
+            self.saved[i] = done
 
     def end_shard(self):
-        if self.tier != "gpu":
-            self.loaded.clear()
+        """Shard boundary.  Whatever is still in `loaded` was prefetched for the next shard and stays."""
 
     # ------------------------------------------------------------------ scored rows
     def heads_view(self, i: int) -> torch.Tensor:

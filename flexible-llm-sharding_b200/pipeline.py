@@ -95,8 +95,7 @@ def _run(model, dm, inputs, shards, G, rank, serial, want_probs, answer_ids, ret
     call = model.ctx.call
     H = model.hidden
 
-    with torch.cuda.device(dev):
-        stream = torch.cuda.current_stream(dev)
+    with torch.cuda.device(dev), model._on_compute_stream(dev) as stream:
         sp = C.c_void_p(stream.cuda_stream)
         dv = model._device_inputs(packed, dev)
         x_all = torch.empty((packed.total_rows, H), dtype=torch.float16, device=dev)

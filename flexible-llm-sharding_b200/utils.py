@@ -13,6 +13,7 @@ previous shard computes; every layer runs as hand-written sm_100a kernels behind
 """
 from __future__ import annotations
 
+import contextlib
 import ctypes as C
 import json
 import os
@@ -151,6 +152,7 @@ class ShardedLlama:
         self._set_pinned_limit(getattr(args, "pinned_limit_bytes", os.environ.get("FLS_PINNED_LIMIT_BYTES", "auto")))
         self._configured = None
         self._pinned_pool = {}
+        self._stream = None
         self.last_timing = {}
 
     def _set_pinned_limit(self, limit):
@@ -196,6 +198,22 @@ class ShardedLlama:
             self._configured = key
             self._slot_holds = {}            # slot -> shard currently held there
         self._n_slots = n_slots
+
+    @contextlib.contextmanager
+    def _on_compute_stream(self, dev):
+        """Run a pass on this model's own (non-blocking) CUDA stream, ordered after the caller's current stream
+        at entry and before it at exit.  The legacy default stream is avoided on purpose: with the host activation
+        tier the weight stream only made progress at shard boundaries when compute sat on stream 0
+        (tools/trace_tier.py)."""
+        caller = torch.cuda.current_stream(dev)
+        if self._stream is None:
+            self._stream = torch.cuda.Stream(dev)
+        self._stream.wait_stream(caller)
+        try:
+            with torch.cuda.stream(self._stream):
+                yield self._stream
+        finally:
+            caller.wait_stream(self._stream)
 
     def _stage_shard(self, live, si):
         """Start the H2D stream of shard `si` unless its slot already holds it (resident weights)."""
@@ -303,8 +321,7 @@ class ShardedLlama:
         dev = self.torch_device
         n_layers_total = len(self.layer_names)
         call = self.ctx.call
-        with torch.cuda.device(dev):
-            stream = torch.cuda.current_stream(dev)
+        with torch.cuda.device(dev), self._on_compute_stream(dev) as stream:
             sp = C.c_void_p(stream.cuda_stream)
             dv = self._device_inputs(packed, dev)
             mbs = packed.micro_batches
@@ -331,9 +348,13 @@ class ShardedLlama:
                     call("fls_acquire_shard", slot, sp)
                     has_input = shard[0] != 0
                     tokens_in = shard[0] <= n_layers_total - 2      # input is token-stage rows (incl. norm layer)
+                    nxt_tokens_in = si + 1 < len(live) and live[si + 1][0] <= n_layers_total - 2
                     for bi, mb in enumerate(mbs):
                         if tokens_in:
-                            store.prefetch(bi + 1, has_input)
+                            if bi + 1 < len(mbs):
+                                store.prefetch(bi + 1, has_input)
+                            elif nxt_tokens_in:
+                                store.prefetch(len(mbs), True)       # next shard's first micro-batch
                             x = store.fetch(bi, has_input)
                         else:
                             x = store.heads_view(bi)

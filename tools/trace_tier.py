@@ -23,6 +23,7 @@ ap.add_argument("--workload", default="70b")
 ap.add_argument("--prompts", type=int, default=32)
 ap.add_argument("--k", type=int, default=10)
 ap.add_argument("--storage", default="cpu")
+ap.add_argument("--own_stream", type=int, default=0, help="1: run the pass on a non-default torch stream")
 a = ap.parse_args()
 
 import __graft_entry__ as ge
@@ -36,14 +37,18 @@ prompts = synthetic.make_prompts(a.prompts, shape.vocab_size, 1792, 4, 64, seed=
 args = bench.make_args(md, layer_num_per_shard=a.k, storage_location=a.storage, force_storage_tier=True,
                        disk_folder=tempfile.mkdtemp(), max_rows=16384)
 model = ShardedLlama(args, DeviceManager(args, [str(dev)]), device=str(dev))
-model(copy.deepcopy(prompts))
-torch.cuda.synchronize()
-with profile(activities=[ProfilerActivity.CUDA]) as prof:
+side = torch.cuda.Stream(dev) if a.own_stream else torch.cuda.current_stream(dev)
+with torch.cuda.stream(side):
     model(copy.deepcopy(prompts))
     torch.cuda.synchronize()
+    with profile(activities=[ProfilerActivity.CUDA, ProfilerActivity.CPU]) as prof:
+        model(copy.deepcopy(prompts))
+        torch.cuda.synchronize()
 path = os.path.join(tempfile.mkdtemp(), "trace.json")
 prof.export_chrome_trace(path)
-ev = [e for e in json.load(open(path))["traceEvents"] if e.get("ph") == "X" and e.get("cat") in ("kernel", "gpu_memcpy")]
+allev = [e for e in json.load(open(path))["traceEvents"] if e.get("ph") == "X"]
+ev = [e for e in allev if e.get("cat") in ("kernel", "gpu_memcpy")]
+rt = sorted([e for e in allev if e.get("cat") in ("cuda_runtime", "cuda_driver")], key=lambda e: e["ts"])
 kern = sorted([e for e in ev if e["cat"] == "kernel"], key=lambda e: e["ts"])
 cpy = sorted([e for e in ev if e["cat"] == "gpu_memcpy"], key=lambda e: e["ts"])
 t0 = kern[0]["ts"]
@@ -68,3 +73,25 @@ for c in cpy:
     b[0] += 1; b[1] += c["dur"] / 1e3; b[2] += c.get("args", {}).get("bytes", 0)
 for k, (n, ms, byts) in by.items():
     print("memcpy", k, "n", n, "ms", round(ms), "GB", round(byts / 1e9, 1), "GB/s", round(byts / max(ms, 1e-9) / 1e6, 1))
+
+# host side: which runtime calls blocked, and when the weight chunks of each shard were ENQUEUED vs EXECUTED
+print("host runtime calls > 5 ms:")
+for e in sorted(rt, key=lambda e: -e["dur"])[:12]:
+    if e["dur"] > 5000:
+        print(f"  {e['name'][:40]:40s} {e['dur'] / 1e3:8.1f} ms at {(e['ts'] - t0) / 1e6:7.3f}s")
+wstream = max(by, key=lambda k: by[k][2])[1]
+w = [c for c in cpy if c.get("args", {}).get("stream") == wstream and c["name"].startswith("Memcpy HtoD")]
+corr = {e.get("args", {}).get("correlation"): e for e in rt}
+groups, cur = [], []
+for c in w:
+    if cur and c["ts"] - (cur[-1]["ts"] + cur[-1]["dur"]) > 20000:
+        groups.append(cur); cur = []
+    cur.append(c)
+if cur:
+    groups.append(cur)
+print("weight-copy bursts (device time) and when their first/last chunk was enqueued on the host:")
+for g in groups:
+    f, l = g[0], g[-1]
+    ef, el = corr.get(f.get("args", {}).get("correlation")), corr.get(l.get("args", {}).get("correlation"))
+    print(f"  n {len(g):4d} dev {(f['ts'] - t0) / 1e6:7.3f}..{(l['ts'] + l['dur'] - t0) / 1e6:7.3f}s  "
+          f"host enqueue {((ef['ts'] - t0) / 1e6) if ef else -1:7.3f}..{((el['ts'] - t0) / 1e6) if el else -1:7.3f}s")
