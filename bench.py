@@ -49,6 +49,13 @@ WORKLOADS = {
 }
 
 
+# DRAM bytes (read + write) of one launch of each decoder GEMM at 16384 rows, 7B shapes, from the `ncu --set full`
+# capture summarised in profiles/r01_ncu_full_prof_gemm2.csv (dram__bytes_read.sum + dram__bytes_write.sum).
+# Static evidence, not measured by this run: quoted only for the workload the capture was taken on.
+NCU_GEMM_TRAFFIC = {"7b": {"gemm_qkv": 0.716098e9 + 4.211310e6, "gemm_o": 0.465435e9 + 3.910457e6,
+                           "gemm_gate_up": 1.080926e9 + 2.213196e6, "gemm_down": 2.097680e9 + 1.500891e6}}
+
+
 def peaks():
     p = os.path.join(ROOT, "MEASURED_PEAKS.json")
     if os.path.exists(p):
@@ -380,8 +387,14 @@ def main():
             per_class[c] = {"ms_per_step": v["ms"] / a.steps, "launches_per_step": v["launches"] / a.steps,
                             "share_of_step": v["ms"] * 1e-3 / dt,
                             ("tflops" if c.startswith("gemm") else "gbs"): rate / (1e12 if c.startswith("gemm") else 1e9)}
+    traffic, traffic_source = None, None
+    ncu = NCU_GEMM_TRAFFIC.get(shape_name)
+    if ncu and a.max_rows == 16384 and g_n:
+        # launch-weighted mean over the four GEMM classes, like `achieved` / `avg_launch_ms`
+        traffic = sum(ncu[c] * prof[c]["launches"] for c in gemm_cls) / g_n
+        traffic_source = "profiles/r01_ncu_full_prof_gemm2.csv (ncu --set full, one launch per class, bytes/launch)"
     roofline = {"bound": "tensor", "achieved": achieved, "peak": peak, "unit": "TFLOP/s",
-                "frac": achieved / peak if peak else None, "traffic": None,
+                "frac": achieved / peak if peak else None, "traffic": traffic, "traffic_source": traffic_source,
                 "kernel": "gemm_tcgen05_kernel (qkv, o+residual, gate/up+SwiGLU, down+residual)",
                 "avg_launch_ms": g_ms / max(g_n, 1), "flops_per_launch": g_fl / max(g_n, 1),
                 "peak_source": pk["source"] + ", sustained figure (kernel timed inside a long step)",

@@ -11,6 +11,9 @@ rows of all prompts form one `[total_rows, H]` fp16 matrix and a tier decides wh
         one computes and copied back on a D2H stream (three rotating HBM staging buffers).
   disk  per-prompt `.npy` files with the reference's names and shapes
         (`prefix{rank}-{idx:05d}.npy` [1,len_p,H], `suffix…` [S,len_s,H]; utils.py:171-177).
+        Files are written and read by a small thread pool straight from / into pinned host buffers
+        (three for each direction), a micro-batch ahead of the GPU, so the file system works while
+        the GPU computes.
 
 `storage_location` names the tier the user allows; unless `force_tier` is set the store upgrades
 `cpu`/`disk` to `gpu` when the matrix fits the HBM budget ("HBM-resident where capacity allows").
@@ -19,9 +22,12 @@ The scored rows after `model.norm` (S per prompt) are small and always stay in H
 from __future__ import annotations
 
 import os
+from concurrent.futures import ThreadPoolExecutor
 
 import numpy as np
 import torch
+
+DISK_IO_THREADS = 8      # per-prompt file reads / writes in flight
 
 
 class ActivationStore:
@@ -66,7 +72,13 @@ class ActivationStore:
                 self.x_host = self._pinned(pinned_pool, "x_host", packed.total_rows, hidden)
             else:
                 os.makedirs(disk_folder, exist_ok=True)
-                self.host_stage = self._pinned(pinned_pool, "host_stage", cap, hidden)
+                self.host_w = [self._pinned(pinned_pool, f"disk_w{j}", cap, hidden) for j in range(3)]
+                self.host_r = [self._pinned(pinned_pool, f"disk_r{j}", cap, hidden) for j in range(3)]
+                self.jobs = ThreadPoolExecutor(max_workers=4, thread_name_prefix="fls-disk-job")
+                self.io = ThreadPoolExecutor(max_workers=DISK_IO_THREADS, thread_name_prefix="fls-disk-io")
+                self.w_job = [None] * 3   # writer job that last used host_w[j]
+                self.r_job = {}           # micro-batch index -> reader job filling its staging slot
+                self.written = {}         # micro-batch index -> writer job of its latest files
 
     @staticmethod
     def _pinned(pool, name, rows, hidden):
@@ -101,16 +113,19 @@ class ActivationStore:
         mb = self.packed.micro_batches[i]
         s = self._take_slot()
         buf = self.staging[s][:mb.n_rows]
-        if has_input:
+        if has_input and self.tier == "disk":
+            ev = torch.cuda.Event()
+            self.r_job[i] = self.jobs.submit(self._disk_load, mb, s, self.d2h_done[s], self.written.get(i),
+                                             self.h2d_done[s], ev)
+            self.h2d_done[s] = ev                          # recorded by the job; fetch() waits for the job first
+            self.h2d_bytes += mb.n_rows * self.H * 2
+        elif has_input:
             with torch.cuda.stream(self.h2d_stream):
                 if self.d2h_done[s] is not None:           # previous tenant fully written back
                     self.h2d_stream.wait_event(self.d2h_done[s])
                 if i in self.saved:                        # and these rows' own write-back has landed
                     self.h2d_stream.wait_event(self.saved[i])
-                if self.tier == "cpu":
-                    buf.copy_(self.x_host[mb.row_lo:mb.row_lo + mb.n_rows], non_blocking=True)
-                else:
-                    self._disk_load(mb, buf)
+                buf.copy_(self.x_host[mb.row_lo:mb.row_lo + mb.n_rows], non_blocking=True)
                 ev = torch.cuda.Event()
                 ev.record(self.h2d_stream)
                 self.h2d_done[s] = ev
@@ -128,6 +143,8 @@ class ActivationStore:
             return self.x_all[mb.row_lo:mb.row_lo + mb.n_rows]
         self.prefetch(i, has_input)
         s = self.loaded[i]
+        if self.tier == "disk" and i in self.r_job:
+            self.r_job.pop(i).result()                     # files read and the H2D enqueued (event recorded)
         if self.h2d_done[s] is not None:
             self.compute_stream.wait_event(self.h2d_done[s])
         return self.staging[s][:mb.n_rows]
@@ -140,18 +157,22 @@ class ActivationStore:
         mb = self.packed.micro_batches[i]
         ev = torch.cuda.Event()
         ev.record(self.compute_stream)
+        if keep_tokens and self.tier == "disk" and self.w_job[s] is not None:
+            self.w_job[s].result()                         # host_w[s] is free again (bounds the host's run-ahead)
         with torch.cuda.stream(self.d2h_stream):
             self.d2h_stream.wait_event(ev)
             if keep_tokens:
                 if self.tier == "cpu":
                     self.x_host[mb.row_lo:mb.row_lo + mb.n_rows].copy_(x, non_blocking=True)
                 else:
-                    self._disk_save(mb, x)
+                    self.host_w[s][:mb.n_rows].copy_(x, non_blocking=True)
                 self.d2h_bytes += mb.n_rows * self.H * 2
             done = torch.cuda.Event()
             done.record(self.d2h_stream)
             self.d2h_done[s] = done
             self.saved[i] = done
+        if keep_tokens and self.tier == "disk":
+            self.w_job[s] = self.written[i] = self.jobs.submit(self._disk_save, mb, s, done)
 
     def end_shard(self):
         """Shard boundary.  Whatever is still in `loaded` was prefetched for the next shard and stays."""
@@ -166,35 +187,89 @@ class ActivationStore:
         f = self.disk_folder
         return (f"{f}/prefix{self.rank_tag}-{prompt_idx:05d}.npy", f"{f}/suffix{self.rank_tag}-{prompt_idx:05d}.npy")
 
-    def _disk_save(self, mb, x: torch.Tensor):
-        host = self.host_stage[:mb.n_rows]
-        host.copy_(x, non_blocking=True)
-        self.d2h_stream.synchronize()
-        arr = host.numpy()
+    def _prompt_slices(self, mb):
+        """(prefix file, suffix file, first row in the micro-batch, len_p, S, len_s) per prompt."""
         for p in range(mb.prompt_lo, mb.prompt_hi):
             len_p, S, len_s = self.packed.shapes[p]
-            b = int(self.packed.prompt_row[p]) - mb.row_lo
             pf, sf = self._names(p)
+            yield pf, sf, int(self.packed.prompt_row[p]) - mb.row_lo, len_p, S, len_s
+
+    def _disk_save(self, mb, s: int, d2h_done):
+        """Writer job: once the rows are in host_w[s], write the reference's two files per prompt."""
+        d2h_done.synchronize()
+        arr = self.host_w[s][:mb.n_rows].numpy()
+
+        def save_one(item):
+            pf, sf, b, len_p, S, len_s = item
             np.save(pf, arr[b:b + len_p].reshape(1, len_p, self.H))
             np.save(sf, arr[b + len_p:b + len_p + S * len_s].reshape(S, len_s, self.H))
 
-    def _disk_load(self, mb, buf: torch.Tensor):
-        host = self.host_stage[:mb.n_rows]
-        self.h2d_stream.synchronize()
-        self.d2h_stream.synchronize()
-        arr = host.numpy()
-        for p in range(mb.prompt_lo, mb.prompt_hi):
-            len_p, S, len_s = self.packed.shapes[p]
-            b = int(self.packed.prompt_row[p]) - mb.row_lo
-            pf, sf = self._names(p)
-            arr[b:b + len_p] = np.load(pf).reshape(len_p, self.H)
-            arr[b + len_p:b + len_p + S * len_s] = np.load(sf).reshape(S * len_s, self.H)
-        buf.copy_(host, non_blocking=True)
-        self.h2d_stream.synchronize()
+        list(self.io.map(save_one, self._prompt_slices(mb)))
 
-    def cleanup(self):
-        if self.tier == "disk":
-            for p in range(len(self.packed.shapes)):
-                for fn in self._names(p):
-                    if os.path.exists(fn):
-                        os.remove(fn)
+    @staticmethod
+    def _read_npy_into(path: str, dest: np.ndarray, shape: tuple):
+        """Read a `.npy` file's payload straight into `dest` (rows of a pinned buffer), checking its header."""
+        with open(path, "rb", buffering=0) as fp:
+            major, _ = np.lib.format.read_magic(fp)
+            hdr = (np.lib.format.read_array_header_1_0 if major == 1 else np.lib.format.read_array_header_2_0)(fp)
+            if tuple(hdr[0]) != tuple(shape) or hdr[1] or hdr[2] != np.float16:
+                raise ValueError(f"{path}: expected float16 C-order {shape}, found {hdr}")
+            view = memoryview(dest.reshape(-1).view(np.uint8))
+            got = 0
+            while got < len(view):
+                n = fp.readinto(view[got:])
+                if not n:
+                    raise IOError(f"{path}: truncated ({got} of {len(view)} bytes)")
+                got += n
+
+    def _disk_load(self, mb, s: int, slot_written_back, files_written, host_free, h2d_ev):
+        """Reader job: files -> host_r[s] -> staging[s] on the H2D stream; records `h2d_ev` when enqueued."""
+        torch.cuda.set_device(self.device)
+        if files_written is not None:
+            files_written.result()
+        if host_free is not None:
+            host_free.synchronize()                        # the previous copy out of host_r[s] has finished
+        host = self.host_r[s][:mb.n_rows]
+        arr = host.numpy()
+
+        def load_one(item):
+            pf, sf, b, len_p, S, len_s = item
+            self._read_npy_into(pf, arr[b:b + len_p], (1, len_p, self.H))
+            self._read_npy_into(sf, arr[b + len_p:b + len_p + S * len_s], (S, len_s, self.H))
+
+        list(self.io.map(load_one, self._prompt_slices(mb)))
+        with torch.cuda.stream(self.h2d_stream):
+            if slot_written_back is not None:              # staging[s]'s previous tenant has left
+                self.h2d_stream.wait_event(slot_written_back)
+            self.staging[s][:mb.n_rows].copy_(host, non_blocking=True)
+            h2d_ev.record(self.h2d_stream)
+
+    keep_disk_files = False      # tests set this to look at the files a pass leaves behind
+
+    def cleanup(self, abort: bool = False):
+        """End of the pass: wait for the disk tier's jobs, stop its threads, remove its files.  `abort` (the pass
+        failed) drops queued jobs and swallows their errors so the original exception surfaces."""
+        if self.tier != "disk" or self.jobs is None:
+            return
+        pending = list(self.r_job.values()) + list(self.written.values())
+        self.r_job.clear()
+        self.written.clear()
+        try:
+            for f in pending:
+                if abort:
+                    f.cancel()
+                    try:
+                        f.result()
+                    except BaseException:
+                        pass
+                else:
+                    f.result()
+        finally:
+            self.jobs.shutdown(wait=True, cancel_futures=abort)
+            self.io.shutdown(wait=True, cancel_futures=abort)
+            self.jobs = self.io = None
+            if not self.keep_disk_files:
+                for p in range(len(self.packed.shapes)):
+                    for fn in self._names(p):
+                        if os.path.exists(fn):
+                            os.remove(fn)

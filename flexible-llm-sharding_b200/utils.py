@@ -365,6 +365,9 @@ class ShardedLlama:
                             store.store(bi, x, keep_tokens=still_tokens)
                     store.end_shard()
                     call("fls_release_shard", slot, sp)
+            except BaseException:
+                store.cleanup(abort=True)
+                raise
             finally:
                 call("fls_set_option", b"paced_weight_stream", 0)
 

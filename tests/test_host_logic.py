@@ -149,3 +149,29 @@ def test_safetensors_header_parse_rejects_garbage(tmp_path):
     bad.write_bytes(b"\x10\x00\x00\x00\x00\x00\x00\x00{not json.......")
     lib = _lib.load()
     assert lib.fls_preload_layer_file(str(bad).encode()) == -3
+
+
+def test_disk_tier_reads_reference_npy_files_in_place(tmp_path):
+    """The disk tier reads `.npy` payloads straight into rows of a (pinned) buffer: files written by plain
+    `np.save` (what the reference writes, utils.py:171-177) must land bit-exactly, and a wrong shape must raise."""
+    from flexible_llm_sharding_b200.activation_store import ActivationStore
+    rng = np.random.default_rng(0)
+    H = 64
+    pre = rng.standard_normal((1, 37, H)).astype(np.float16)
+    suf = rng.standard_normal((3, 5, H)).astype(np.float16)
+    np.save(tmp_path / "prefix-00000.npy", pre)
+    np.save(tmp_path / "suffix-00000.npy", suf)
+    rows = np.zeros((60, H), np.float16)
+    ActivationStore._read_npy_into(str(tmp_path / "prefix-00000.npy"), rows[2:39], (1, 37, H))
+    ActivationStore._read_npy_into(str(tmp_path / "suffix-00000.npy"), rows[39:54], (3, 5, H))
+    assert np.array_equal(rows[2:39], pre[0]) and np.array_equal(rows[39:54], suf.reshape(15, H))
+    assert not rows[:2].any() and not rows[54:].any()
+    with pytest.raises(ValueError):
+        ActivationStore._read_npy_into(str(tmp_path / "suffix-00000.npy"), rows[39:54], (5, 3, H))
+    np.save(tmp_path / "f32.npy", suf.astype(np.float32))
+    with pytest.raises(ValueError):
+        ActivationStore._read_npy_into(str(tmp_path / "f32.npy"), rows[39:54], (3, 5, H))
+    with open(tmp_path / "short.npy", "wb") as f:
+        f.write(open(tmp_path / "suffix-00000.npy", "rb").read()[:-10])
+    with pytest.raises(IOError):
+        ActivationStore._read_npy_into(str(tmp_path / "short.npy"), rows[39:54], (3, 5, H))

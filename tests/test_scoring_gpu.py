@@ -102,6 +102,33 @@ def test_schedule_does_not_change_scores(tiny, k, storage, num_batch, max_rows, 
         assert not [f for f in os.listdir(tmp_path / "act") if f.endswith(".npy")]      # cleaned up
 
 
+def test_disk_tier_writes_the_reference_file_layout(tiny, tmp_path, monkeypatch):
+    """`storage_location=disk` keeps the reference's files (utils.py:171-177): `prefix{rank}-{idx:05d}.npy`
+    [1, len_p, H] and `suffix…` [S, len_s, H], float16, one pair per prompt, loadable with plain np.load."""
+    from flexible_llm_sharding_b200.activation_store import ActivationStore
+    from flexible_llm_sharding_b200.main import run_sharded_llama
+    from flexible_llm_sharding_b200.utils import DeviceManager
+    monkeypatch.setattr(ActivationStore, "keep_disk_files", True)
+    folder = tmp_path / "act"
+    args = make_args(tiny["layer_dir"], layer_num_per_shard=2, storage_location="disk", max_rows=250,
+                     force_storage_tier=True, disk_folder=str(folder), data_parallel=True)
+    dm = DeviceManager(args, ["cuda:0"])
+    prompts = copy.deepcopy(tiny["prompts"])
+    out = run_sharded_llama("cuda:0", copy.deepcopy(prompts), dm, args)
+    _, base = run_model(tiny)
+    for a, b in zip(out, base):
+        assert np.array_equal(a, b)
+    files = sorted(os.listdir(folder))
+    assert files == sorted([f"prefix0-{i:05d}.npy" for i in range(len(prompts))] +
+                           [f"suffix0-{i:05d}.npy" for i in range(len(prompts))])
+    for i, (_, options) in enumerate(prompts):
+        pre = np.load(folder / f"prefix0-{i:05d}.npy")
+        suf = np.load(folder / f"suffix0-{i:05d}.npy")
+        assert pre.dtype == np.float16 and suf.dtype == np.float16
+        assert pre.ndim == 3 and pre.shape[0] == 1 and suf.ndim == 3 and suf.shape[0] == len(options)
+        assert pre.shape[2] == suf.shape[2] and np.isfinite(pre.astype(np.float32)).all()
+
+
 def test_kernel_variants_give_identical_scores(tiny_gqa):
     """RoPE in the QKV epilogue vs the stand-alone kernel, and cta_group 1 vs 2 GEMMs, are the same
     arithmetic: bit-identical scores.  tcgen05 vs mma.sync attention differ only in summation order."""
