@@ -66,6 +66,7 @@ PROF_CLASSES = ["gemm_qkv", "gemm_o", "gemm_gate_up", "gemm_down", "gemm_head", 
                 "embed", "other"]
 LAYER_EMBED, LAYER_DECODER, LAYER_NORM, LAYER_HEAD = 0, 1, 2, 3
 EPI_STORE, EPI_RESIDUAL, EPI_SWIGLU = 0, 1, 2
+KV_NONE, KV_SAVE, KV_LOAD = 0, 1, 2
 ATTN_TILE_INTS = 8  # sizeof(fls_attn_tile) / 4
 
 _P = C.c_void_p
@@ -90,6 +91,7 @@ _SIGNATURES = {
     "fls_peer_copy": (_I, [_P, _P, _I, _P, C.c_size_t, _P]),
     "fls_embed": (_I, [_P, _I, _I, _P, _I, _P, _P]),
     "fls_decoder_layer": (_I, [_P, _I, _I, _P, _I, _P, _P, _I, _P]),
+    "fls_decoder_layer_kv": (_I, [_P, _I, _I, _P, _I, _P, _P, _I, _I, _P, _I, _P, _P]),
     "fls_final_norm": (_I, [_P, _I, _I, _P, _P, _I, _P, _P]),
     "fls_lm_head": (_I, [_P, _I, _I, _P, _I, _P, _P, _I, _P, _P, _P]),
     "fls_op_gemm": (_I, [_P, _I, _P, _I, _P, _I, _I, _I, _I, _I, _P, _I, _P, _I, _I, _P]),

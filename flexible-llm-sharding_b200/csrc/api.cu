@@ -650,12 +650,27 @@ int fls_embed(fls_ctx* c, int slot, int layer_idx, const int32_t* ids, int n_row
 
 int fls_decoder_layer(fls_ctx* c, int slot, int layer_idx, uint16_t* x_dev, int n_rows, const int32_t* row_pos,
                       const fls_attn_tile* tiles, int n_tiles, void* stream) {
+    return fls_decoder_layer_kv(c, slot, layer_idx, x_dev, n_rows, row_pos, tiles, n_tiles, FLS_KV_NONE, nullptr, 0,
+                                nullptr, stream);
+}
+
+int fls_decoder_layer_kv(fls_ctx* c, int slot, int layer_idx, uint16_t* x_dev, int n_rows, const int32_t* row_pos,
+                         const fls_attn_tile* tiles, int n_tiles, int kv_mode, const int32_t* kv_rows, int n_kv_rows,
+                         uint16_t* kv_cache, void* stream) {
     ENTER(c);
     const ResidentLayer* r = find_resident(c, slot, layer_idx, FLS_LAYER_DECODER);
     if (!r) return ctx_fail(c, kErrState);
-    if (n_rows > c->max_rows)
-        return ctx_fail(c, fail(kErrCapacity, "decoder_layer: %d rows exceed the configured max_rows %d", n_rows,
-                                c->max_rows));
+    if (kv_mode != FLS_KV_NONE && kv_mode != FLS_KV_SAVE && kv_mode != FLS_KV_LOAD)
+        return ctx_fail(c, fail(kErrInvalid, "decoder_layer: kv_mode %d", kv_mode));
+    if (kv_mode == FLS_KV_NONE) n_kv_rows = 0;
+    if (n_kv_rows < 0 || (n_kv_rows > 0 && (!kv_cache || (kv_mode == FLS_KV_SAVE && !kv_rows))))
+        return ctx_fail(c, fail(kErrInvalid, "decoder_layer: %d cached rows need a cache%s", n_kv_rows,
+                                kv_mode == FLS_KV_SAVE ? " and their row indices" : ""));
+    // rows of the cache ahead of x's rows in the attention workspace (FLS_KV_LOAD only)
+    const int row0 = kv_mode == FLS_KV_LOAD ? n_kv_rows : 0;
+    if (row0 + n_rows > c->max_rows)
+        return ctx_fail(c, fail(kErrCapacity, "decoder_layer: %d rows (%d of them cached) exceed the configured "
+                                "max_rows %d", row0 + n_rows, row0, c->max_rows));
     if (!c->rope_cos) return ctx_fail(c, fail(kErrState, "decoder_layer: call fls_set_rope_table first"));
     if (n_rows <= 0) return kOk;
     const auto& m = c->m;
@@ -673,7 +688,8 @@ int fls_decoder_layer(fls_ctx* c, int slot, int layer_idx, uint16_t* x_dev, int 
     }
     GemmArgs a{};
     a.A = c->xn, a.lda = Hd, a.B = r->dec.wqkv, a.ldb = Hd, a.b_rows = c->qkv_dim;
-    a.M = n_rows, a.N = c->qkv_dim, a.K = Hd, a.C = c->qkv, a.ldc = c->qkv_dim;
+    __half* qkv_new = c->qkv + static_cast<size_t>(row0) * c->qkv_dim;     // where this call's rows go
+    a.M = n_rows, a.N = c->qkv_dim, a.K = Hd, a.C = qkv_new, a.ldc = c->qkv_dim;
     const bool fused_rope = c->fuse_rope && m.head_dim == 128;
     {
         ProfScope ps(c, FLS_PROF_GEMM_QKV, 2.0 * R * c->qkv_dim * Hd, st);
@@ -687,17 +703,25 @@ int fls_decoder_layer(fls_ctx* c, int slot, int layer_idx, uint16_t* x_dev, int 
     }
     if (!fused_rope) {
         ProfScope ps(c, FLS_PROF_ROPE, R * (c->q_dim + c->kv_dim) * 4.0, st);
-        CTX_TRY(c, rope_launch(c->qkv, c->qkv_dim, n_rows, m.num_attention_heads, m.num_key_value_heads, m.head_dim,
+        CTX_TRY(c, rope_launch(qkv_new, c->qkv_dim, n_rows, m.num_attention_heads, m.num_key_value_heads, m.head_dim,
                                row_pos, c->rope_cos, c->rope_sin, c->rope_n_pos, st));
+    }
+    if (n_kv_rows > 0) {
+        ProfScope ps(c, FLS_PROF_OTHER, static_cast<double>(n_kv_rows) * c->kv_dim * 8.0, st);
+        CTX_TRY(c, kv_rows_copy_launch(c->qkv, c->qkv_dim, c->q_dim, 2 * c->kv_dim,
+                                       kv_mode == FLS_KV_SAVE ? kv_rows : nullptr, n_kv_rows, H(kv_cache),
+                                       kv_mode == FLS_KV_SAVE, st));
+        c->stats.kernel_launches += 1;
     }
     {
         ProfScope ps(c, FLS_PROF_ATTENTION, 0, st);
-        CTX_TRY(c, attention_dispatch(c, c->qkv, c->qkv_dim, n_rows, m.num_attention_heads, m.num_key_value_heads,
-                                      m.head_dim, reinterpret_cast<const AttnTile*>(tiles), n_tiles, c->attn,
-                                      c->q_dim, st));
+        CTX_TRY(c, attention_dispatch(c, c->qkv, c->qkv_dim, row0 + n_rows, m.num_attention_heads,
+                                      m.num_key_value_heads, m.head_dim, reinterpret_cast<const AttnTile*>(tiles),
+                                      n_tiles, c->attn, c->q_dim, st));
     }
     a = GemmArgs{};
-    a.A = c->attn, a.lda = c->q_dim, a.B = r->dec.wo, a.ldb = c->q_dim, a.b_rows = Hd;
+    a.A = c->attn + static_cast<size_t>(row0) * c->q_dim, a.lda = c->q_dim, a.B = r->dec.wo, a.ldb = c->q_dim;
+    a.b_rows = Hd;
     a.M = n_rows, a.N = Hd, a.K = c->q_dim, a.C = x, a.ldc = Hd, a.R = x, a.ldr = Hd;
     {
         ProfScope ps(c, FLS_PROF_GEMM_O, 2.0 * R * Hd * c->q_dim, st);

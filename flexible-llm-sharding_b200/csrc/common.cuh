@@ -74,6 +74,9 @@ int gemm_lse_blocks(int N);
 
 // ---- element-wise / reductions (elementwise.cu) ---------------------------------------------
 int embed_launch(const __half* table, const int32_t* ids, int n_rows, int H, __half* out, cudaStream_t s);
+// Copies `width` columns from `col0` of qkv rows (rows[r], or r when rows == nullptr) to dense cache rows, or back.
+int kv_rows_copy_launch(__half* qkv, int ld, int col0, int width, const int32_t* rows, int n, __half* cache,
+                        bool to_cache, cudaStream_t s);
 // out_norm[r] = w * fp16(x32 * rsqrt(mean(x32^2) + eps)), x = x_in[gather ? gather[r] : r] (+ delta[r]);
 // when delta != nullptr the sum is also written back to x_sum (may alias x_in).
 int rmsnorm_launch(const __half* x_in, const __half* delta, const int32_t* gather, const __half* w, float eps,

@@ -33,6 +33,28 @@ __global__ void embed_kernel(const __half* __restrict__ table, const int32_t* __
     }
 }
 
+// ---------------------------------------------------------------------------------- K|V row copy
+// Prefix K/V cache (no counterpart in the reference, which recomputes the prefix for every generated token,
+// main.py:65): `width` columns starting at `col0` of selected rows of the qkv workspace <-> dense cache rows.
+//   to_cache:  cache[r, :] = qkv[rows ? rows[r] : r, col0 : col0 + width]
+//   !to_cache: qkv[rows ? rows[r] : r, col0 : col0 + width] = cache[r, :]
+__global__ void kv_rows_copy_kernel(__half* __restrict__ qkv, int ld, int col0, int width,
+                                    const int32_t* __restrict__ rows, int n, __half* __restrict__ cache,
+                                    int to_cache) {
+    const int vec_per_row = width / 8;
+    const long long total = static_cast<long long>(n) * vec_per_row;
+    for (long long i = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; i < total;
+         i += static_cast<long long>(gridDim.x) * blockDim.x) {
+        const int r = static_cast<int>(i / vec_per_row);
+        const int v = static_cast<int>(i - static_cast<long long>(r) * vec_per_row);
+        const int row = rows ? rows[r] : r;
+        uint4* q = reinterpret_cast<uint4*>(qkv + static_cast<size_t>(row) * ld + col0 + v * 8);
+        uint4* k = reinterpret_cast<uint4*>(cache + static_cast<size_t>(r) * width + v * 8);
+        if (to_cache) *k = *q;
+        else *q = *k;
+    }
+}
+
 // ---------------------------------------------------------------------------------- RMSNorm
 // HF LlamaRMSNorm: x32 = x.float(); y = (x32 * rsqrt(mean(x32^2) + eps)).half(); out = w * y.
 // Optional fused residual (x = x_in + delta, rounded to fp16 first, written back to x_sum) and
@@ -234,6 +256,17 @@ int embed_launch(const __half* table, const int32_t* ids, int n_rows, int H, __h
     if (H % 8) return fail(kErrInvalid, "embed: hidden size %d not a multiple of 8", H);
     if (n_rows <= 0) return kOk;
     embed_kernel<<<grid_for(static_cast<long long>(n_rows) * (H / 8), 256), 256, 0, s>>>(table, ids, n_rows, H, out);
+    FLS_CUDA(cudaGetLastError());
+    return kOk;
+}
+
+int kv_rows_copy_launch(__half* qkv, int ld, int col0, int width, const int32_t* rows, int n, __half* cache,
+                        bool to_cache, cudaStream_t s) {
+    if (width % 8 || col0 % 8 || ld % 8)
+        return fail(kErrInvalid, "kv_rows_copy: ld %d, col0 %d, width %d must be multiples of 8", ld, col0, width);
+    if (n <= 0) return kOk;
+    kv_rows_copy_kernel<<<grid_for(static_cast<long long>(n) * (width / 8), 256), 256, 0, s>>>(
+        qkv, ld, col0, width, rows, n, cache, to_cache ? 1 : 0);
     FLS_CUDA(cudaGetLastError());
     return kOk;
 }

@@ -142,7 +142,14 @@ def main(argv=None):
     else:
         device_manager = DeviceManager(args, devices)          # created once, like main.py:61
     output_scores, tokenizer = [], None
+    # Prefix K/V cache: the reference recomputes everything for every new token (main.py:65); the
+    # prefixes do not change between tokens, so every pass but the last keeps their per-layer K/V in HBM when they
+    # fit and later passes run the option rows only.  Same scores bit for bit; FLS_PREFIX_KV_CACHE=off disables it.
+    kv_user = getattr(args, "prefix_kv_cache", os.environ.get("FLS_PREFIX_KV_CACHE", "auto"))
+    use_kv = kv_user != "off" and args.num_gen_token > 1
     for i_new in range(args.num_gen_token):
+        if use_kv:
+            args.prefix_kv_cache = "last" if i_new == args.num_gen_token - 1 else "on"
         prompts_now = list(input_prompts)
         outputs = (score_all_distributed(args, prompts_now, device_manager) if distributed
                    else score_all(args, prompts_now, devices, device_manager))
@@ -164,6 +171,9 @@ def main(argv=None):
             box = [input_prompts if is_root else None]
             dist.broadcast_object_list(box, src=0)
             input_prompts = box[0]
+    args.prefix_kv_cache = kv_user
+    for model in getattr(device_manager, "models", {}).values():
+        model.drop_prefix_kv_cache()
     if is_root:
         with open(args.prompt_pickle.replace(".pkl", "_updated.pkl"), "wb") as f:
             pickle.dump(input_prompts, f)

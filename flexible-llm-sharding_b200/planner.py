@@ -125,6 +125,9 @@ class MicroBatch:
     n_head: int
     tiles: np.ndarray        # [n_tiles, 8] int32, rows relative to row_lo
     gather: np.ndarray       # [n_head] int32 rows (relative to row_lo) of each option's last real token
+    kv_lo: int = 0           # first prefix row of its prompts in the pass-wide prefix K/V cache (prompt order)
+    n_kv: int = 0            # prefix rows of its prompts
+    kv_rows: np.ndarray | None = None   # [n_kv] int32: those rows relative to row_lo (None when the prefix is cached)
 
 
 @dataclass
@@ -133,8 +136,10 @@ class PackedPrompts:
     row_pos: np.ndarray      # [total_rows] int32 rotary positions
     prompt_row: np.ndarray   # [n_prompts + 1] first row of each prompt
     head_row: np.ndarray     # [n_prompts + 1] first scored row of each prompt
-    shapes: list[tuple[int, int, int]]   # (len_p, S, len_s)
+    shapes: list[tuple[int, int, int]]   # (len_p, S, len_s) of the packed ROWS: len_p is 0 when the prefix is cached
     micro_batches: list[MicroBatch] = field(default_factory=list)
+    cached_prefix: bool = False          # rows hold the options only; prefix K/V come from a cache (prefix_len rows)
+    prefix_len: list[int] = field(default_factory=list)     # real prefix length of every prompt
 
     @property
     def total_rows(self): return int(self.prompt_row[-1])
@@ -145,17 +150,23 @@ class PackedPrompts:
 ATTN_PREFIX, ATTN_PREFIX_CAUSAL, ATTN_SUFFIX = 0, 1, 2
 
 
-def prompt_tiles(base: int, len_p: int, S: int, len_s: int, prefix_causal: bool) -> list[list[int]]:
+def prompt_tiles(base: int, len_p: int, S: int, len_s: int, prefix_causal: bool,
+                 option_base: int | None = None) -> list[list[int]]:
     """Attention tiles of one prompt whose rows start at `base` (include/fls_b200.h: fls_attn_tile).
     Prefix rows: tiles of <= 128 queries over the prefix keys.  Option rows: as many whole options
     as fit 128 rows share one tile (their common prefix keys are then read once); an option longer
-    than 128 rows is cut into 128-row tiles that see the option's rows up to their own last query."""
+    than 128 rows is cut into 128-row tiles that see the option's rows up to their own last query.
+    With `option_base` the prefix is cached: its keys sit at `base`, the option rows start at
+    `option_base`, and there are no prefix queries."""
     Q = ATTN_TILE_Q
     t = []
-    mode = ATTN_PREFIX_CAUSAL if prefix_causal else ATTN_PREFIX
-    for q0 in range(0, len_p, Q):
-        t.append([base + q0, min(Q, len_p - q0), q0, mode, base, len_p, 0, 0])
-    first = base + len_p
+    if option_base is None:
+        mode = ATTN_PREFIX_CAUSAL if prefix_causal else ATTN_PREFIX
+        for q0 in range(0, len_p, Q):
+            t.append([base + q0, min(Q, len_p - q0), q0, mode, base, len_p, 0, 0])
+        first = base + len_p
+    else:
+        first = option_base
     if len_s <= Q:
         per_tile = max(1, Q // len_s)
         for s0 in range(0, S, per_tile):
@@ -172,10 +183,15 @@ def prompt_tiles(base: int, len_p: int, S: int, len_s: int, prefix_causal: bool)
 
 
 def pack_prompts(tok: list[TokenizedPrompt], max_rows: int, max_head_rows: int,
-                 prefix_causal: bool = False) -> PackedPrompts:
+                 prefix_causal: bool = False, cached_prefix: bool = False) -> PackedPrompts:
+    """Packs the prompts' token rows and cuts them into micro-batches of <= max_rows rows.
+    `cached_prefix`: only the option rows are packed (the prefix K/V of every layer come from a cache filled by
+    an earlier pass over the same prefixes); a micro-batch's attention then works in the row space
+    [its prompts' cached prefix rows | its option rows], which is what max_rows bounds."""
     n = len(tok)
     prompt_row = np.zeros(n + 1, dtype=np.int64)
     head_row = np.zeros(n + 1, dtype=np.int64)
+    kv_row = np.zeros(n + 1, dtype=np.int64)
     for i, t in enumerate(tok):
         if t.len_p + t.len_s > MAX_TOKEN_LEN:
             # the reference would fail slicing its 4096^2 mask (utils.py:276)
@@ -184,44 +200,57 @@ def pack_prompts(tok: list[TokenizedPrompt], max_rows: int, max_head_rows: int,
             raise ValueError(f"prompt {i} has {t.rows} token rows; raise max_rows (currently {max_rows})")
         if t.len_s == 0:
             raise ValueError(f"prompt {i}: every option is empty")
-        prompt_row[i + 1] = prompt_row[i] + t.rows
+        prompt_row[i + 1] = prompt_row[i] + (t.rows - t.len_p if cached_prefix else t.rows)
         head_row[i + 1] = head_row[i] + t.n_options
+        kv_row[i + 1] = kv_row[i] + t.len_p
     total = int(prompt_row[-1])
     ids = np.empty(total, dtype=np.int32)
     row_pos = np.empty(total, dtype=np.int32)
     shapes = []
     for i, t in enumerate(tok):
-        b = int(prompt_row[i])
-        ids[b:b + t.len_p] = t.prefix_ids
-        row_pos[b:b + t.len_p] = np.arange(t.len_p)
-        so = b + t.len_p
+        so = int(prompt_row[i])
+        if not cached_prefix:
+            ids[so:so + t.len_p] = t.prefix_ids
+            row_pos[so:so + t.len_p] = np.arange(t.len_p)
+            so += t.len_p
         ids[so:so + t.n_options * t.len_s] = t.suffix_ids.reshape(-1)
         row_pos[so:so + t.n_options * t.len_s] = np.tile(np.arange(t.len_p, t.len_p + t.len_s), t.n_options)
-        shapes.append((t.len_p, t.n_options, t.len_s))
-    packed = PackedPrompts(ids, row_pos, prompt_row, head_row, shapes)
+        shapes.append((0 if cached_prefix else t.len_p, t.n_options, t.len_s))
+    packed = PackedPrompts(ids, row_pos, prompt_row, head_row, shapes, cached_prefix=cached_prefix,
+                           prefix_len=[t.len_p for t in tok])
+
+    def space(lo, hi):      # rows of the attention workspace prompts [lo, hi) need
+        return int(prompt_row[hi] - prompt_row[lo]) + (int(kv_row[hi] - kv_row[lo]) if cached_prefix else 0)
 
     lo = 0
     while lo < n:
         hi = lo
-        while hi < n and (prompt_row[hi + 1] - prompt_row[lo] <= max_rows
-                          and head_row[hi + 1] - head_row[lo] <= max_head_rows):
+        while hi < n and space(lo, hi + 1) <= max_rows and head_row[hi + 1] - head_row[lo] <= max_head_rows:
             hi += 1
         if hi == lo:
             raise ValueError(f"prompt {lo} does not fit a micro-batch (max_rows {max_rows}, max_head_rows {max_head_rows})")
         row_lo = int(prompt_row[lo])
-        tiles, gather = [], []
+        kv_lo, n_kv = int(kv_row[lo]), int(kv_row[hi] - kv_row[lo])
+        tiles, gather, kv_rows = [], [], []
         for i in range(lo, hi):
-            len_p, S, len_s = shapes[i]
+            len_p, S, len_s = tok[i].len_p, tok[i].n_options, tok[i].len_s
             base = int(prompt_row[i]) - row_lo
-            tiles += prompt_tiles(base, len_p, S, len_s, prefix_causal)
+            if cached_prefix:
+                first = base                                        # x rows: options only
+                tiles += prompt_tiles(int(kv_row[i]) - kv_lo, len_p, S, len_s, prefix_causal, option_base=n_kv + base)
+            else:
+                first = base + len_p
+                tiles += prompt_tiles(base, len_p, S, len_s, prefix_causal)
+                kv_rows.append(np.arange(base, base + len_p, dtype=np.int32))
             for s in range(S):
                 e = int(tok[i].suffix_eos[s])
                 if e < 0:
                     e += len_s          # torch negative indexing at utils.py:286
-                gather.append(base + len_p + s * len_s + e)
+                gather.append(first + s * len_s + e)
         packed.micro_batches.append(MicroBatch(
             lo, hi, row_lo, int(prompt_row[hi]) - row_lo, int(head_row[lo]), int(head_row[hi] - head_row[lo]),
-            np.asarray(tiles, dtype=np.int32).reshape(-1, 8), np.asarray(gather, dtype=np.int32)))
+            np.asarray(tiles, dtype=np.int32).reshape(-1, 8), np.asarray(gather, dtype=np.int32), kv_lo, n_kv,
+            None if cached_prefix else (np.concatenate(kv_rows) if kv_rows else np.zeros(0, np.int32))))
         lo = hi
     return packed
 

@@ -15,6 +15,7 @@ from __future__ import annotations
 
 import contextlib
 import ctypes as C
+import hashlib
 import json
 import os
 import threading
@@ -153,6 +154,8 @@ class ShardedLlama:
         self._configured = None
         self._pinned_pool = {}
         self._stream = None
+        self._kv = {}            # prefix signature -> per-layer prefix K/V of an earlier pass (see _kv_plan)
+        self.kv_dim = cfg.get("num_key_value_heads", nh) * self.head_dim
         self.last_timing = {}
 
     def _set_pinned_limit(self, limit):
@@ -246,16 +249,55 @@ class ShardedLlama:
         return [lp[int(packed.head_row[i]):int(packed.head_row[i + 1])] for i in range(len(packed.shapes))]
 
     # ------------------------------------------------------------------ engine
-    def _device_inputs(self, packed, dev):
+    def _device_inputs(self, packed, dev, kv_mode=_lib.KV_NONE):
         """Token ids, rotary positions, attention tiles and gather lists on the device (pinned -> async H2D)."""
         up = lambda a: torch.from_numpy(a).pin_memory().to(dev, non_blocking=True)
         mbs = packed.micro_batches
         d = dict(ids=up(packed.ids), pos=up(packed.row_pos), tiles=[up(mb.tiles) for mb in mbs],
                  gather=[up(mb.gather) for mb in mbs])
         d["bytes"] = packed.ids.nbytes + packed.row_pos.nbytes + sum(mb.tiles.nbytes + mb.gather.nbytes for mb in mbs)
+        if kv_mode == _lib.KV_SAVE:
+            d["kv_rows"] = [up(mb.kv_rows) for mb in mbs]
+            d["bytes"] += sum(mb.kv_rows.nbytes for mb in mbs)
         return d
 
-    def _run_layers(self, slot, shard, bi, mb, x, heads, dv, out, sp):
+    # ------------------------------------------------------------------ prefix K/V cache (SURVEY.md 8f-1)
+    def _kv_plan(self, tok):
+        """Decide what this pass does with the prefix K/V cache.  The reference recomputes prefix and options for
+        every generated token (main.py:65-90) although a prompt's prefix rows never change; with
+        `args.prefix_kv_cache` = "on" the first pass over a set of prefixes keeps every decoder layer's post-RoPE
+        K|V of the prefix rows in HBM (if they fit) and later passes over the same prefixes push only the option
+        rows through the layers.  "last" = use a cache if there is one, then drop it, and never start one.
+        Returns (kv_mode, cache tensor [decoder layers, prefix rows, 2 * kv_dim] or None, note, signature); a cache
+        being filled is registered under its signature by `run` only once the pass has succeeded."""
+        policy = str(getattr(self.args, "prefix_kv_cache", "off"))
+        if policy not in ("on", "last"):
+            return _lib.KV_NONE, None, "off", None
+        h = hashlib.blake2b(digest_size=16)
+        h.update(np.asarray([t.len_p for t in tok], dtype=np.int64).tobytes())
+        for t in tok:
+            h.update(t.prefix_ids.tobytes())
+        sig = h.digest()
+        if sig in self._kv:
+            cache = self._kv[sig] if policy == "on" else self._kv.pop(sig)
+            return _lib.KV_LOAD, cache, "load", sig
+        if policy == "last":
+            return _lib.KV_NONE, None, "off (last pass)", sig
+        n_dec = self.layer_kinds.count(_lib.LAYER_DECODER)
+        rows = sum(t.len_p for t in tok)
+        need = n_dec * rows * 2 * self.kv_dim * 2
+        free = torch.cuda.mem_get_info(self.torch_device)[0]
+        act = sum(t.rows for t in tok) * self.hidden * 2 if self.args.storage_location == "gpu" else 0
+        out = sum(t.n_options for t in tok) * self.vocab * 2
+        if need > 0.8 * (free - act - out):
+            return _lib.KV_NONE, None, f"skipped: {need / 1e9:.1f} GB of prefix K/V do not fit", sig
+        cache = torch.empty((n_dec, rows, 2 * self.kv_dim), dtype=torch.float16, device=self.torch_device)
+        return _lib.KV_SAVE, cache, "save", sig
+
+    def drop_prefix_kv_cache(self):
+        self._kv.clear()
+
+    def _run_layers(self, slot, shard, bi, mb, x, heads, dv, out, sp, kv_mode=_lib.KV_NONE, kv_cache=None):
         """Runs the layers of `shard` on micro-batch `bi`.  `x` = token-stage rows (or scored rows when
         the shard starts after model.norm).  Returns (tensor holding the shard's output, is_token_stage)."""
         call = self.ctx.call
@@ -265,6 +307,11 @@ class ShardedLlama:
             kind = self.layer_kinds[li]
             if kind == _lib.LAYER_EMBED:
                 call("fls_embed", slot, li, dv["ids"][mb.row_lo:].data_ptr(), mb.n_rows, x.data_ptr(), sp)
+            elif kind == _lib.LAYER_DECODER and kv_mode != _lib.KV_NONE:
+                rows = dv["kv_rows"][bi].data_ptr() if kv_mode == _lib.KV_SAVE else None
+                call("fls_decoder_layer_kv", slot, li, x.data_ptr(), mb.n_rows, dv["pos"][mb.row_lo:].data_ptr(),
+                     dv["tiles"][bi].data_ptr(), int(mb.tiles.shape[0]), kv_mode, rows, mb.n_kv,
+                     kv_cache[li - 1, mb.kv_lo:].data_ptr(), sp)       # decoder layer li is the (li-1)-th one
             elif kind == _lib.LAYER_DECODER:
                 call("fls_decoder_layer", slot, li, x.data_ptr(), mb.n_rows, dv["pos"][mb.row_lo:].data_ptr(),
                      dv["tiles"][bi].data_ptr(), int(mb.tiles.shape[0]), sp)
@@ -315,7 +362,14 @@ class ShardedLlama:
                 inputs[i] = None                                  # utils.py:259
             if not tok:
                 return None, None
-            packed = planner.pack_prompts(tok, self.max_rows, self.max_head_rows, self.prefix_causal)
+            self._configure(shards)
+            kv_mode, kv_cache, kv_note, kv_sig = self._kv_plan(tok)
+            packed = planner.pack_prompts(tok, self.max_rows, self.max_head_rows, self.prefix_causal,
+                                          cached_prefix=kv_mode == _lib.KV_LOAD)
+        elif packed.cached_prefix:
+            raise ValueError("a pre-packed pass cannot use the prefix K/V cache")
+        else:
+            kv_mode, kv_cache, kv_note, kv_sig = _lib.KV_NONE, None, "off", None
         t_tok = perf_counter() - t0
         self._configure(shards)
         dev = self.torch_device
@@ -323,7 +377,7 @@ class ShardedLlama:
         call = self.ctx.call
         with torch.cuda.device(dev), self._on_compute_stream(dev) as stream:
             sp = C.c_void_p(stream.cuda_stream)
-            dv = self._device_inputs(packed, dev)
+            dv = self._device_inputs(packed, dev, kv_mode)
             mbs = packed.micro_batches
             rank_tag = str(rank) if self.args.data_parallel else ""
             store = ActivationStore(self.args.storage_location, packed, self.hidden, dev, stream,
@@ -360,7 +414,8 @@ class ShardedLlama:
                             x = store.heads_view(bi)
                         if paced and nxt_slot is not None:
                             call("fls_prefetch_pump", nxt_slot, C.c_size_t(nxt_slice), sp)
-                        y, still_tokens = self._run_layers(slot, shard, bi, mb, x, store.heads_view(bi), dv, out, sp)
+                        y, still_tokens = self._run_layers(slot, shard, bi, mb, x, store.heads_view(bi), dv, out, sp,
+                                                           kv_mode, kv_cache)
                         if tokens_in:
                             store.store(bi, x, keep_tokens=still_tokens)
                     store.end_shard()
@@ -377,8 +432,11 @@ class ShardedLlama:
             else:
                 stream.synchronize()
             store.cleanup()
+            if kv_mode == _lib.KV_SAVE:
+                self._kv[kv_sig] = kv_cache              # filled by a pass that ran to its end
             self.last_timing = dict(tokenize_s=t_tok, total_s=perf_counter() - t0, h2d_input_bytes=dv["bytes"],
                                     d2h_output_bytes=out_bytes, activation_tier=store.tier,
-                                    act_h2d_bytes=store.h2d_bytes, act_d2h_bytes=store.d2h_bytes)
+                                    act_h2d_bytes=store.h2d_bytes, act_d2h_bytes=store.d2h_bytes,
+                                    prefix_kv=kv_note, rows=packed.total_rows)
             self._keepalive = (dv, out, store)
         return result, packed

@@ -164,6 +164,25 @@ int fls_embed(fls_ctx* ctx, int slot, int layer_idx, const int32_t* ids_dev, int
  * (0..len_p-1 for prefix rows, len_p.. for option rows, utils.py:221,275). */
 int fls_decoder_layer(fls_ctx* ctx, int slot, int layer_idx, uint16_t* x_dev, int n_rows, const int32_t* row_pos_dev,
                       const fls_attn_tile* tiles_dev, int n_tiles, void* stream);
+/* The same layer with a prefix K/V cache.  No counterpart in the reference: its generation loop (main.py:65-90)
+ * re-runs prefix and options from scratch for every new token, although the prefix rows never change
+ * (utils.py:272: the prefix attends only to itself).  The cache is caller-owned fp16 memory
+ * [n_kv_rows, 2 * kv_heads * head_dim] per layer: post-RoPE keys, then values.
+ *   FLS_KV_SAVE  a normal pass over x_dev[n_rows]; afterwards row kv_rows_dev[j] (an index into the rows of this
+ *                call, normally the prefix rows in prompt order) has its K|V copied to cache row j.
+ *   FLS_KV_LOAD  x_dev holds only the n_rows NEW rows (the options).  The layer works in a row space of
+ *                n_kv_rows + n_rows rows: rows [0, n_kv_rows) are the cached rows, whose K|V are restored from
+ *                the cache (kv_rows_dev is ignored), rows n_kv_rows.. are x_dev's rows.  Tile descriptors index
+ *                that space, and every query tile must start at or after n_kv_rows; row_pos_dev has n_rows
+ *                entries.  n_kv_rows + n_rows must not exceed the configured max_rows.
+ *   FLS_KV_NONE  identical to fls_decoder_layer.
+ * Results are bit-identical to recomputing the cached rows (every kernel treats rows independently). */
+#define FLS_KV_NONE 0
+#define FLS_KV_SAVE 1
+#define FLS_KV_LOAD 2
+int fls_decoder_layer_kv(fls_ctx* ctx, int slot, int layer_idx, uint16_t* x_dev, int n_rows,
+                         const int32_t* row_pos_dev, const fls_attn_tile* tiles_dev, int n_tiles, int kv_mode,
+                         const int32_t* kv_rows_dev, int n_kv_rows, uint16_t* kv_cache_dev, void* stream);
 /* utils.py:281-286  out[j] = norm(x[gather_dev[j]]) - the last real token of every option. */
 int fls_final_norm(fls_ctx* ctx, int slot, int layer_idx, const uint16_t* x_dev, const int32_t* gather_dev, int n_out,
                    uint16_t* out_dev, void* stream);

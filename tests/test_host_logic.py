@@ -88,6 +88,45 @@ def test_pack_prompts_layout_and_tiles():
         planner.pack_prompts(_tok([(4000, 1, 200)]), max_rows=10000, max_head_rows=6)     # > 4096 (utils.py:276)
 
 
+def test_cached_prefix_packing_is_the_normal_packing_remapped():
+    """Prefix K/V cache: a pass over the option rows only must use the same micro-batches, rotary positions,
+    gathers and option tiles as the full pass, with rows renumbered to [cached prefix rows | option rows]."""
+    shapes = [(70, 3, 9), (1, 2, 5), (129, 4, 33), (64, 1, 64), (200, 2, 70), (30, 2, 150)]
+    tok = _tok(shapes)
+    full = planner.pack_prompts(tok, max_rows=400, max_head_rows=6)
+    opt = planner.pack_prompts(tok, max_rows=400, max_head_rows=6, cached_prefix=True)
+    assert opt.cached_prefix and not full.cached_prefix
+    assert opt.prefix_len == [lp for lp, _, _ in shapes] and opt.shapes == [(0, S, ls) for _, S, ls in shapes]
+    assert opt.total_rows == sum(S * ls for _, S, ls in shapes) and len(opt.micro_batches) == len(full.micro_batches)
+    kv_seen = 0
+    for f, o in zip(full.micro_batches, opt.micro_batches):
+        assert (f.prompt_lo, f.prompt_hi, f.head_lo, f.n_head) == (o.prompt_lo, o.prompt_hi, o.head_lo, o.n_head)
+        assert (f.kv_lo, f.n_kv) == (o.kv_lo, o.n_kv) == (kv_seen, sum(lp for lp, _, _ in shapes[f.prompt_lo:f.prompt_hi]))
+        kv_seen += f.n_kv
+        assert o.kv_rows is None and o.n_kv + o.n_rows == f.n_rows <= 400
+        # row map of the full micro-batch -> workspace rows of the option-only pass
+        remap = np.full(f.n_rows, -1)
+        kv, x = 0, 0
+        for i in range(f.prompt_lo, f.prompt_hi):
+            lp, S, ls = shapes[i]
+            b = int(full.prompt_row[i]) - f.row_lo
+            remap[b:b + lp] = kv + np.arange(lp)
+            remap[b + lp:b + lp + S * ls] = o.n_kv + x + np.arange(S * ls)
+            assert np.array_equal(f.kv_rows[kv:kv + lp], b + np.arange(lp))
+            assert np.array_equal(opt.ids[o.row_lo + x:o.row_lo + x + S * ls], full.ids[f.row_lo + b + lp:f.row_lo + b + lp + S * ls])
+            assert np.array_equal(opt.row_pos[o.row_lo + x:o.row_lo + x + S * ls],
+                                  full.row_pos[f.row_lo + b + lp:f.row_lo + b + lp + S * ls])
+            kv, x = kv + lp, x + S * ls
+        assert len(f.kv_rows) == f.n_kv
+        want = []
+        for q_row, n_q, q_seq0, mode, s0r, s0l, s1r, s1l in f.tiles:
+            if mode == planner.ATTN_SUFFIX:
+                want.append([remap[q_row], n_q, q_seq0, mode, remap[s0r], s0l, remap[s1r], s1l])
+        assert np.array_equal(o.tiles, np.asarray(want, dtype=np.int32))
+        assert (o.tiles[:, 0] >= o.n_kv).all()                     # queries are never cached rows
+        assert np.array_equal(o.gather, remap[f.gather] - o.n_kv)  # gathers index the option-only rows
+
+
 def test_rope_table_matches_oracle():
     import torch
     cos, sin = planner.rope_tables(300, 128)

@@ -229,6 +229,70 @@ def test_long_prompts_many_key_tiles(tiny_gqa, causal):
         check_against_reference([o], w[None])
 
 
+def _extend_options(prompts, words):
+    """What the generation loop does (main.py:84-90): append a decoded token to every option."""
+    return [(pre, tuple(o + " " + words[(i + j) % len(words)] for j, o in enumerate(opts)))
+            for i, (pre, opts) in enumerate(prompts)]
+
+
+@pytest.mark.parametrize("which,storage,max_rows,k", [("tiny", "gpu", 16384, 1), ("tiny_gqa", "gpu", 300, 2),
+                                                      ("tiny_gqa", "cpu", 300, 3), ("tiny", "disk", 250, 2)])
+def test_prefix_kv_cache_gives_identical_scores(which, storage, max_rows, k, request, tmp_path):
+    """later passes over the same prefixes (the generation loop) reuse the prefix K/V of every
+    layer and push only the option rows through; the scores must be bit-identical to recomputing everything."""
+    from flexible_llm_sharding_b200.utils import DeviceManager, ShardedLlama
+    case = request.getfixturevalue(which)
+    kw = dict(layer_num_per_shard=k, storage_location=storage, max_rows=max_rows, force_storage_tier=True,
+              disk_folder=str(tmp_path / "act"))
+    p1 = copy.deepcopy(case["prompts"])
+    p2 = _extend_options(p1, ["w7", "w11", "w5"])
+    p3 = _extend_options(p2, ["w9", "w4"])
+    plain = ShardedLlama(make_args(case["layer_dir"], **kw), DeviceManager(make_args(case["layer_dir"]), ["cuda:0"]))
+    want = [plain(copy.deepcopy(p)) for p in (p1, p2, p3)]
+    assert plain.last_timing["prefix_kv"] == "off"
+    args = make_args(case["layer_dir"], prefix_kv_cache="on", **kw)
+    model = ShardedLlama(args, DeviceManager(args, ["cuda:0"]))
+    notes, rows = [], []
+    for step, p in enumerate((p1, p2, p3)):
+        if step == 2:
+            args.prefix_kv_cache = "last"
+        got = model(copy.deepcopy(p))
+        notes.append(model.last_timing["prefix_kv"])
+        rows.append(model.last_timing["rows"])
+        for a, b in zip(got, want[step]):
+            assert np.array_equal(a, b), (step, notes)
+    assert notes == ["save", "load", "load"] and rows[1] < rows[0] and not model._kv
+    # a different set of prefixes never hits the cache
+    args.prefix_kv_cache = "on"
+    model(copy.deepcopy(p1))
+    other = [(pre + " w3", opts) for pre, opts in p1]
+    model(copy.deepcopy(other))
+    assert model.last_timing["prefix_kv"] == "save" and len(model._kv) == 2
+    model.drop_prefix_kv_cache()
+    assert not model._kv
+
+
+def test_cli_generation_with_and_without_prefix_kv_cache(tiny, tmp_path, monkeypatch):
+    """main.py --num_gen_token 3: the prefix K/V cache is on by default and must not change a single bit."""
+    from flexible_llm_sharding_b200.main import main
+    res = {}
+    for mode in ("off", "auto"):
+        monkeypatch.setenv("FLS_PREFIX_KV_CACHE", mode)
+        pp = tmp_path / f"prompts_{mode}.pkl"
+        with open(pp, "wb") as f:
+            pickle.dump(tiny["prompts"][:5], f)
+        outp = tmp_path / f"scores_{mode}.pkl"
+        main(["--model_path", tiny["layer_dir"], "--prompt_pickle", str(pp), "--output_file", str(outp),
+              "--storage_location", "gpu", "--layer_num_per_shard", "3", "--num_gen_token", "3", "--num_batch", "2"])
+        with open(outp, "rb") as f:
+            scores = pickle.load(f)
+        with open(str(pp).replace(".pkl", "_updated.pkl"), "rb") as f:
+            res[mode] = (scores, pickle.load(f))
+    assert res["off"][1] == res["auto"][1]
+    for a, b in zip(res["off"][0], res["auto"][0]):
+        assert a.shape[1] == 3 and np.array_equal(a, b)
+
+
 def test_prompt_larger_than_a_micro_batch_is_rejected(tiny):
     from flexible_llm_sharding_b200.utils import DeviceManager, ShardedLlama
     args = make_args(tiny["layer_dir"], max_rows=64)
