@@ -21,7 +21,7 @@ from time import perf_counter
 
 import torch
 
-from . import planner
+from . import _lib, planner
 
 _WAIT_S = 600.0
 
@@ -72,12 +72,46 @@ def run_model_parallel(model, inputs, shards, G, rank, want_probs, answer_ids, r
 
 def _run(model, dm, inputs, shards, G, rank, serial, want_probs, answer_ids, return_device):
     t0 = perf_counter()
+    my_layers = [li for sh in shards for li in sh]
     if rank == 0:
         tok = planner.tokenize_prompts(model.tokenizer, inputs)
         for i in range(len(inputs)):
             inputs[i] = None
-        packed = planner.pack_prompts(tok, model.max_rows, model.max_head_rows, model.prefix_causal) if tok else None
         dm.suffix_eos = [t.suffix_eos for t in tok]                  # utils.py:157,258 (kept for inspection)
+        ask = None
+        if tok and model._kv_policy() != "off":
+            ask = dict(sig=model._kv_signature(tok), policy=model._kv_policy(), prefix_rows=sum(t.len_p for t in tok),
+                       act_rows=sum(t.rows for t in tok), head_rows=sum(t.n_options for t in tok))
+        _board_post(dm, ("kv_ask", serial), ask)
+    else:
+        tok = None
+        ask = _board_wait(dm, ("kv_ask", serial))
+    # Prefix K/V cache (utils.py:_kv_plan): every rank caches the layers it owns; the pass loads only if every
+    # rank holds the prefixes and saves only if every rank has room, so all ranks pack the same rows.
+    kv_mode, kv_cache, kv_note = _lib.KV_NONE, None, "off"
+    if ask is not None:
+        model._configure(shards)
+        if ask["sig"] in model._kv:
+            mine_says = "load"
+        elif ask["policy"] == "on" and model._kv_need(my_layers, ask["prefix_rows"], ask["act_rows"], ask["head_rows"])[1]:
+            mine_says = "save"
+        else:
+            mine_says = "no"
+        _board_post(dm, ("kv_say", serial, rank), mine_says)
+        says = [_board_wait(dm, ("kv_say", serial, r)) for r in range(G)]
+        if all(v == "load" for v in says):
+            kv_mode, kv_note = _lib.KV_LOAD, "load"
+            kv_cache = model._kv[ask["sig"]] if ask["policy"] == "on" else model._kv.pop(ask["sig"])
+        else:
+            model._kv.pop(ask["sig"], None)                          # a partial set of ranks is of no use
+            if all(v == "save" for v in says):
+                kv_mode, kv_note = _lib.KV_SAVE, "save"
+                kv_cache = model._kv_alloc(my_layers, ask["prefix_rows"])
+            else:
+                kv_note = "off (last pass)" if ask["policy"] == "last" else "skipped: no room on every rank"
+    if rank == 0:
+        packed = planner.pack_prompts(tok, model.max_rows, model.max_head_rows, model.prefix_causal,
+                                      cached_prefix=kv_mode == _lib.KV_LOAD) if tok else None
         _board_post(dm, ("packed", serial), packed)
     else:
         packed = _board_wait(dm, ("packed", serial))
@@ -97,7 +131,7 @@ def _run(model, dm, inputs, shards, G, rank, serial, want_probs, answer_ids, ret
 
     with torch.cuda.device(dev), model._on_compute_stream(dev) as stream:
         sp = C.c_void_p(stream.cuda_stream)
-        dv = model._device_inputs(packed, dev)
+        dv = model._device_inputs(packed, dev, kv_mode)
         x_all = torch.empty((packed.total_rows, H), dtype=torch.float16, device=dev)
         heads = torch.empty((packed.total_head_rows, H), dtype=torch.float16, device=dev)
         out = model._alloc_outputs(packed, dev, want_probs and owns_head, answer_ids if owns_head else None)
@@ -120,7 +154,7 @@ def _run(model, dm, inputs, shards, G, rank, serial, want_probs, answer_ids, ret
                 if g > 0:
                     ev = _board_wait(dm, ("ev", serial, g - 1, bi))      # producer has enqueued its copy
                     stream.wait_event(ev)                                 # device-side wait, no host sync
-                y, still_tokens = model._run_layers(slot, shard, bi, mb, x, hv, dv, out, sp)
+                y, still_tokens = model._run_layers(slot, shard, bi, mb, x, hv, dv, out, sp, kv_mode, kv_cache)
                 if g != last_g:
                     if nxt is None:
                         nxt = _board_wait(dm, ("buffers", serial, (rank + 1) % G))
@@ -140,8 +174,11 @@ def _run(model, dm, inputs, shards, G, rank, serial, want_probs, answer_ids, ret
             result, out_bytes = model._fetch_result(out, want_probs, stream, return_device)
         stream.synchronize()
         _barrier(dm, serial, rank, G)          # peers may still be writing into / reading from our buffers
+        if kv_mode == _lib.KV_SAVE:
+            model._kv[ask["sig"]] = kv_cache               # every rank has passed the barrier: the pass succeeded
         model.last_timing = dict(tokenize_s=t_tok, total_s=perf_counter() - t0, h2d_input_bytes=dv["bytes"],
-                                 d2h_output_bytes=out_bytes, activation_tier="gpu", p2p_bytes=p2p_bytes)
+                                 d2h_output_bytes=out_bytes, activation_tier="gpu", p2p_bytes=p2p_bytes,
+                                 prefix_kv=kv_note, rows=packed.total_rows)
         if rank == 0:
             # Entries of call serial-2 and older can go: whoever posted done(serial-1) has left barrier(serial-2).
             with dm.condition:

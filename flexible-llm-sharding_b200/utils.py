@@ -262,37 +262,56 @@ class ShardedLlama:
         return d
 
     # ------------------------------------------------------------------ prefix K/V cache
-    def _kv_plan(self, tok):
+    def _kv_policy(self) -> str:
+        p = str(getattr(self.args, "prefix_kv_cache", "off"))
+        return p if p in ("on", "last") else "off"
+
+    @staticmethod
+    def _kv_signature(tok) -> bytes:
+        """Identifies a list of prefixes (token ids and lengths, in order)."""
+        h = hashlib.blake2b(digest_size=16)
+        h.update(np.asarray([t.len_p for t in tok], dtype=np.int64).tobytes())
+        for t in tok:
+            h.update(t.prefix_ids.tobytes())
+        return h.digest()
+
+    def _kv_need(self, layers, prefix_rows: int, act_rows: int, head_rows: int):
+        """(bytes the prefix K/V of `layers` would take, whether they fit 80 % of the free HBM once the
+        HBM-resident activations and the scores are accounted for)."""
+        n_dec = sum(1 for li in layers if self.layer_kinds[li] == _lib.LAYER_DECODER)
+        need = n_dec * prefix_rows * 2 * self.kv_dim * 2
+        free = torch.cuda.mem_get_info(self.torch_device)[0]
+        act = act_rows * self.hidden * 2 if self.args.storage_location == "gpu" else 0
+        return need, need <= 0.8 * (free - act - head_rows * self.vocab * 2)
+
+    def _kv_alloc(self, layers, prefix_rows: int):
+        """{layer index: [prefix_rows, 2 * kv_dim] fp16} for the decoder layers among `layers` (one allocation)."""
+        dec = [li for li in layers if self.layer_kinds[li] == _lib.LAYER_DECODER]
+        big = torch.empty((len(dec), prefix_rows, 2 * self.kv_dim), dtype=torch.float16, device=self.torch_device)
+        return {li: big[j] for j, li in enumerate(dec)}
+
+    def _kv_plan(self, tok, layers):
         """Decide what this pass does with the prefix K/V cache.  The reference recomputes prefix and options for
         every generated token (main.py:65-90) although a prompt's prefix rows never change; with
         `args.prefix_kv_cache` = "on" the first pass over a set of prefixes keeps every decoder layer's post-RoPE
         K|V of the prefix rows in HBM (if they fit) and later passes over the same prefixes push only the option
         rows through the layers.  "last" = use a cache if there is one, then drop it, and never start one.
-        Returns (kv_mode, cache tensor [decoder layers, prefix rows, 2 * kv_dim] or None, note, signature); a cache
-        being filled is registered under its signature by `run` only once the pass has succeeded."""
-        policy = str(getattr(self.args, "prefix_kv_cache", "off"))
-        if policy not in ("on", "last"):
+        Returns (kv_mode, {layer: cache rows} or None, note, signature); a cache being filled is registered
+        under its signature by `run` only once the pass has succeeded."""
+        policy = self._kv_policy()
+        if policy == "off":
             return _lib.KV_NONE, None, "off", None
-        h = hashlib.blake2b(digest_size=16)
-        h.update(np.asarray([t.len_p for t in tok], dtype=np.int64).tobytes())
-        for t in tok:
-            h.update(t.prefix_ids.tobytes())
-        sig = h.digest()
+        sig = self._kv_signature(tok)
         if sig in self._kv:
             cache = self._kv[sig] if policy == "on" else self._kv.pop(sig)
             return _lib.KV_LOAD, cache, "load", sig
         if policy == "last":
             return _lib.KV_NONE, None, "off (last pass)", sig
-        n_dec = self.layer_kinds.count(_lib.LAYER_DECODER)
         rows = sum(t.len_p for t in tok)
-        need = n_dec * rows * 2 * self.kv_dim * 2
-        free = torch.cuda.mem_get_info(self.torch_device)[0]
-        act = sum(t.rows for t in tok) * self.hidden * 2 if self.args.storage_location == "gpu" else 0
-        out = sum(t.n_options for t in tok) * self.vocab * 2
-        if need > 0.8 * (free - act - out):
+        need, fits = self._kv_need(layers, rows, sum(t.rows for t in tok), sum(t.n_options for t in tok))
+        if not fits:
             return _lib.KV_NONE, None, f"skipped: {need / 1e9:.1f} GB of prefix K/V do not fit", sig
-        cache = torch.empty((n_dec, rows, 2 * self.kv_dim), dtype=torch.float16, device=self.torch_device)
-        return _lib.KV_SAVE, cache, "save", sig
+        return _lib.KV_SAVE, self._kv_alloc(layers, rows), "save", sig
 
     def drop_prefix_kv_cache(self):
         self._kv.clear()
@@ -311,7 +330,7 @@ class ShardedLlama:
                 rows = dv["kv_rows"][bi].data_ptr() if kv_mode == _lib.KV_SAVE else None
                 call("fls_decoder_layer_kv", slot, li, x.data_ptr(), mb.n_rows, dv["pos"][mb.row_lo:].data_ptr(),
                      dv["tiles"][bi].data_ptr(), int(mb.tiles.shape[0]), kv_mode, rows, mb.n_kv,
-                     kv_cache[li - 1, mb.kv_lo:].data_ptr(), sp)       # decoder layer li is the (li-1)-th one
+                     kv_cache[li][mb.kv_lo:].data_ptr(), sp)
             elif kind == _lib.LAYER_DECODER:
                 call("fls_decoder_layer", slot, li, x.data_ptr(), mb.n_rows, dv["pos"][mb.row_lo:].data_ptr(),
                      dv["tiles"][bi].data_ptr(), int(mb.tiles.shape[0]), sp)
@@ -363,7 +382,7 @@ class ShardedLlama:
             if not tok:
                 return None, None
             self._configure(shards)
-            kv_mode, kv_cache, kv_note, kv_sig = self._kv_plan(tok)
+            kv_mode, kv_cache, kv_note, kv_sig = self._kv_plan(tok, range(len(self.layer_names)))
             packed = planner.pack_prompts(tok, self.max_rows, self.max_head_rows, self.prefix_causal,
                                           cached_prefix=kv_mode == _lib.KV_LOAD)
         elif packed.cached_prefix:
