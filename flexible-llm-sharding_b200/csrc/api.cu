@@ -108,7 +108,6 @@ struct fls_ctx {
     int attn_impl = 1;  // 1 = tcgen05 attention (head_dim 128), 0 = mma.sync attention
     std::vector<cudaEvent_t> pace_events;
     size_t pace_next = 0;
-    bool pace_always_gate = false;
     int paced_stream = 0;  // 1: fls_prefetch_shard only prepares the copies; fls_prefetch_pump enqueues them
     int gemm_group_m = 0;  // raster group of the GEMM (0 = kernel default)
     int gemm_cache_hints = 0;
@@ -581,7 +580,7 @@ int fls_prefetch_pump(fls_ctx* c, int slot, size_t max_bytes, void* after_stream
     ENTER(c);
     if (slot < 0 || slot >= static_cast<int>(c->slots.size()))
         return ctx_fail(c, fail(kErrInvalid, "fls_prefetch_pump: slot %d", slot));
-    if (after_stream != nullptr || c->pace_always_gate) {
+    if (after_stream != nullptr) {
         // hold this slice back until the work enqueued on `after_stream` so far has run: the pacing then follows
         // the GPU's progress, not the (far ahead) host's
         if (c->pace_events.empty()) {

@@ -9,9 +9,12 @@
 // with M <= a few hundred rows, one prompt at a time.  Here M = all packed rows of a micro-batch.
 //
 // Structure: persistent CTAs (one per SM), 256 threads, warp-specialised:
-//   warp 0      TMA producer: A tile 128x64 and B tile 256x64 per stage (128B swizzle), 4 stages
-//   warp 1      MMA issuer: one elected thread, tcgen05.mma cta_group::1 kind::f16, M=128 N=256 K=16,
-//               fp32 accumulators in TMEM, two accumulator stages (2 x 256 columns = all 512)
+//   warp 0      TMA producer (128B swizzle).  Default cta_group::2: a cluster of two CTAs shares one 256x256
+//               tile, each CTA stages its own 128 A rows and half of the B rows per stage, 6 stages of 32 KiB;
+//               cta_group::1 (option / test comparator): A 128x64 + B 256x64 per stage, 4 stages of 48 KiB
+//   warp 1      MMA issuer: one elected thread (of the leader CTA with cta_group::2), tcgen05.mma kind::f16,
+//               M=128 per CTA, N=256, K=16, fp32 accumulators in TMEM, two accumulator stages
+//               (2 x 256 columns = all 512); tcgen05.commit (multicast to the peer) frees the smem stage
 //   warp 2      TMEM allocator
 //   warps 4-7   epilogue: tcgen05.ld (32 lanes x 32 columns per warp) -> registers -> fused op ->
 //               global.  Overlaps the next tile's main loop through the second accumulator stage.

@@ -189,6 +189,39 @@ def test_bounded_pinned_cache_rereads_layers(tiny):
         _lib.load().fls_set_host_cache_limit(0)
 
 
+def _recast_layer_dir(src, dst, cast):
+    """Copy a layer directory, passing every tensor through `cast` (non-weight files are copied as they are)."""
+    import shutil
+    from safetensors.torch import load_file, save_file
+    os.makedirs(dst, exist_ok=True)
+    for name in os.listdir(src):
+        if name.endswith(".safetensors"):
+            save_file({k: cast(v).contiguous() for k, v in load_file(os.path.join(src, name)).items()},
+                      os.path.join(dst, name))
+        else:
+            shutil.copy(os.path.join(src, name), os.path.join(dst, name))
+    return str(dst)
+
+
+def test_fp32_and_bf16_layer_files_are_converted_to_fp16_on_load(tiny, tmp_path):
+    """The reference casts whatever dtype the layer files hold to fp16 when it loads them
+    (`set_module_tensor_to_device(..., dtype=self.dtype)`, utils.py:130); the pinned-host loader does the same.
+    fp32 copies of fp16 weights must score bit-identically; bf16 files must score like fp16 files holding the
+    bf16-rounded values (bf16 -> fp16 is exact for weights of this magnitude)."""
+    _, base = run_model(tiny)
+    d32 = _recast_layer_dir(tiny["layer_dir"], tmp_path / "f32", lambda t: t.float())
+    _, out32 = run_model(dict(tiny, layer_dir=d32))
+    for a, b in zip(out32, base):
+        assert np.array_equal(a, b)
+    dbf = _recast_layer_dir(tiny["layer_dir"], tmp_path / "bf16", lambda t: t.bfloat16())
+    dbf_as_f16 = _recast_layer_dir(tiny["layer_dir"], tmp_path / "bf16_f16", lambda t: t.bfloat16().half())
+    _, out_bf = run_model(dict(tiny, layer_dir=dbf))
+    _, out_ref = run_model(dict(tiny, layer_dir=dbf_as_f16))
+    for a, b in zip(out_bf, out_ref):
+        assert np.array_equal(a, b)
+    assert any(not np.array_equal(a, b) for a, b in zip(out_bf, base))      # the rounding was really applied
+
+
 def test_fused_answer_token_logprobs(tiny):
     """lm_head + log-softmax + gather without the full-vocabulary output."""
     model, out = run_model(tiny)
