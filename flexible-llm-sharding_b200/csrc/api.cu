@@ -111,6 +111,7 @@ struct fls_ctx {
     int paced_stream = 0;  // 1: fls_prefetch_shard only prepares the copies; fls_prefetch_pump enqueues them
     int gemm_group_m = 0;  // raster group of the GEMM (0 = kernel default)
     int gemm_cache_hints = 0;
+    int rmsnorm_variant = 0;
     int fuse_rope = 1;  // 1 = rotary embedding in the QKV GEMM epilogue (head_dim 128), 0 = separate kernel
 };
 
@@ -683,7 +684,8 @@ int fls_decoder_layer_kv(fls_ctx* c, int slot, int layer_idx, uint16_t* x_dev, i
     // hidden = x + o_proj(attn(rope(qkv(norm(x)))))
     {
         ProfScope ps(c, FLS_PROF_RMSNORM, norm_bytes, st);
-        CTX_TRY(c, rmsnorm_launch(x, nullptr, nullptr, r->dec.ln1, m.rms_norm_eps, n_rows, Hd, nullptr, c->xn, st));
+        CTX_TRY(c, rmsnorm_launch(x, nullptr, nullptr, r->dec.ln1, m.rms_norm_eps, n_rows, Hd, nullptr, c->xn, st,
+                                  c->rmsnorm_variant));
     }
     GemmArgs a{};
     a.A = c->xn, a.lda = Hd, a.B = r->dec.wqkv, a.ldb = Hd, a.b_rows = c->qkv_dim;
@@ -730,7 +732,8 @@ int fls_decoder_layer_kv(fls_ctx* c, int slot, int layer_idx, uint16_t* x_dev, i
     // hidden = hidden + down_proj(silu(gate_proj(norm(hidden))) * up_proj(norm(hidden)))
     {
         ProfScope ps(c, FLS_PROF_RMSNORM, norm_bytes, st);
-        CTX_TRY(c, rmsnorm_launch(x, nullptr, nullptr, r->dec.ln2, m.rms_norm_eps, n_rows, Hd, nullptr, c->xn, st));
+        CTX_TRY(c, rmsnorm_launch(x, nullptr, nullptr, r->dec.ln2, m.rms_norm_eps, n_rows, Hd, nullptr, c->xn, st,
+                                  c->rmsnorm_variant));
     }
     a = GemmArgs{};
     a.A = c->xn, a.lda = Hd, a.B = r->dec.wgu, a.ldb = Hd, a.b_rows = 2 * I;
@@ -815,7 +818,8 @@ int fls_op_gemm(fls_ctx* c, int epilogue, const uint16_t* a_dev, int lda, const 
 int fls_op_rmsnorm(fls_ctx* c, const uint16_t* x, const uint16_t* delta, const int32_t* gather, const uint16_t* w,
                    float eps, int n_rows, int hidden, uint16_t* x_sum, uint16_t* out, void* stream) {
     ENTER(c);
-    CTX_TRY(c, rmsnorm_launch(H(x), H(delta), gather, H(w), eps, n_rows, hidden, H(x_sum), H(out), as_stream(stream)));
+    CTX_TRY(c, rmsnorm_launch(H(x), H(delta), gather, H(w), eps, n_rows, hidden, H(x_sum), H(out), as_stream(stream),
+                              c->rmsnorm_variant));
     c->stats.kernel_launches += 1;
     return kOk;
 }
@@ -871,6 +875,11 @@ int fls_set_option(fls_ctx* c, const char* name, int value) {
     if (strcmp(name, "gemm_cta_group") == 0) {
         if (value != 1 && value != 2) return ctx_fail(c, fail(kErrInvalid, "gemm_cta_group must be 1 or 2"));
         c->gemm_cg = value;
+        return kOk;
+    }
+    if (strcmp(name, "rmsnorm_variant") == 0) {
+        if (value < 0 || value > 2) return ctx_fail(c, fail(kErrInvalid, "rmsnorm_variant must be 0..2"));
+        c->rmsnorm_variant = value;
         return kOk;
     }
     if (strcmp(name, "gemm_cache_hints") == 0) {

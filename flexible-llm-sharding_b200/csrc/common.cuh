@@ -80,7 +80,7 @@ int kv_rows_copy_launch(__half* qkv, int ld, int col0, int width, const int32_t*
 // out_norm[r] = w * fp16(x32 * rsqrt(mean(x32^2) + eps)), x = x_in[gather ? gather[r] : r] (+ delta[r]);
 // when delta != nullptr the sum is also written back to x_sum (may alias x_in).
 int rmsnorm_launch(const __half* x_in, const __half* delta, const int32_t* gather, const __half* w, float eps,
-                   int n_rows, int H, __half* x_sum, __half* out_norm, cudaStream_t s);
+                   int n_rows, int H, __half* x_sum, __half* out_norm, cudaStream_t s, int variant = 0);
 // In-place rotary embedding on the q and k column blocks of a packed qkv buffer.
 int rope_launch(__half* qkv, int ld, int n_rows, int n_q_heads, int n_kv_heads, int head_dim,
                 const int32_t* row_pos, const __half* cos_tab, const __half* sin_tab, int n_pos, cudaStream_t s);

@@ -272,23 +272,28 @@ int kv_rows_copy_launch(__half* qkv, int ld, int col0, int width, const int32_t*
 }
 
 int rmsnorm_launch(const __half* x_in, const __half* delta, const int32_t* gather, const __half* w, float eps,
-                   int n_rows, int H, __half* x_sum, __half* out_norm, cudaStream_t s) {
+                   int n_rows, int H, __half* x_sum, __half* out_norm, cudaStream_t s, int variant) {
     if (H % 8) return fail(kErrInvalid, "rmsnorm: hidden size %d not a multiple of 8", H);
     if (delta && !x_sum) return fail(kErrInvalid, "rmsnorm: residual input needs an x_sum output");
     if (n_rows <= 0) return kOk;
     const int nvec = H / 8;
-    if (nvec <= 128)
-        rmsnorm_kernel<128, 1><<<n_rows, 128, 0, s>>>(x_in, delta, gather, w, eps, n_rows, H, x_sum, out_norm);
-    else if (nvec <= 256)
-        rmsnorm_kernel<256, 1><<<n_rows, 256, 0, s>>>(x_in, delta, gather, w, eps, n_rows, H, x_sum, out_norm);
-    else if (nvec <= 512)
-        rmsnorm_kernel<256, 2><<<n_rows, 256, 0, s>>>(x_in, delta, gather, w, eps, n_rows, H, x_sum, out_norm);
-    else if (nvec <= 1024)
-        rmsnorm_kernel<256, 4><<<n_rows, 256, 0, s>>>(x_in, delta, gather, w, eps, n_rows, H, x_sum, out_norm);
-    else if (nvec <= 2048)
-        rmsnorm_kernel<512, 4><<<n_rows, 512, 0, s>>>(x_in, delta, gather, w, eps, n_rows, H, x_sum, out_norm);
-    else
+#define FLS_NORM(T, V) rmsnorm_kernel<T, V><<<n_rows, T, 0, s>>>(x_in, delta, gather, w, eps, n_rows, H, x_sum, out_norm)
+    // variant 0: the default shapes; 1: half the threads, twice the vectors per thread (more CTAs and more
+    // loads in flight per SM); 2: twice the threads (tools/norm_probe.py compares them)
+    if (nvec <= 128) {
+        if (variant == 1) FLS_NORM(64, 2); else FLS_NORM(128, 1);
+    } else if (nvec <= 256) {
+        if (variant == 1) FLS_NORM(128, 2); else FLS_NORM(256, 1);
+    } else if (nvec <= 512) {
+        if (variant == 1) FLS_NORM(128, 4); else if (variant == 2) FLS_NORM(512, 1); else FLS_NORM(256, 2);
+    } else if (nvec <= 1024) {
+        if (variant == 1) FLS_NORM(128, 8); else if (variant == 2) FLS_NORM(512, 2); else FLS_NORM(256, 4);
+    } else if (nvec <= 2048) {
+        if (variant == 1) FLS_NORM(256, 8); else FLS_NORM(512, 4);
+    } else {
         return fail(kErrInvalid, "rmsnorm: hidden size %d above the supported 16384", H);
+    }
+#undef FLS_NORM
     FLS_CUDA(cudaGetLastError());
     return kOk;
 }
