@@ -45,7 +45,8 @@ class ActivationStore:
         tier = location
         if tier != "gpu" and not force_tier:
             if hbm_budget_bytes is None:
-                free, _ = torch.cuda.mem_get_info(device)
+                free, _ = torch.cuda.mem_get_info(device)     # plus what torch's allocator holds but is not using
+                free += torch.cuda.memory_reserved(device) - torch.cuda.memory_allocated(device)
                 hbm_budget_bytes = int(free * 0.8)
             if total_bytes <= hbm_budget_bytes:
                 tier = "gpu"

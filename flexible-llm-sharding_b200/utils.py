@@ -280,7 +280,9 @@ class ShardedLlama:
         HBM-resident activations and the scores are accounted for)."""
         n_dec = sum(1 for li in layers if self.layer_kinds[li] == _lib.LAYER_DECODER)
         need = n_dec * prefix_rows * 2 * self.kv_dim * 2
-        free = torch.cuda.mem_get_info(self.torch_device)[0]
+        # what the driver reports free plus what torch's allocator holds but has handed back to us
+        free = torch.cuda.mem_get_info(self.torch_device)[0] + (torch.cuda.memory_reserved(self.torch_device)
+                                                                 - torch.cuda.memory_allocated(self.torch_device))
         act = act_rows * self.hidden * 2 if self.args.storage_location == "gpu" else 0
         return need, need <= 0.8 * (free - act - head_rows * self.vocab * 2)
 
@@ -308,7 +310,11 @@ class ShardedLlama:
         if policy == "last":
             return _lib.KV_NONE, None, "off (last pass)", sig
         rows = sum(t.len_p for t in tok)
-        need, fits = self._kv_need(layers, rows, sum(t.rows for t in tok), sum(t.n_options for t in tok))
+        sizes = (sum(t.rows for t in tok), sum(t.n_options for t in tok))
+        need, fits = self._kv_need(layers, rows, *sizes)
+        while not fits and self._kv:                      # make room: the least recently started cache goes first
+            self._kv.pop(next(iter(self._kv)))
+            need, fits = self._kv_need(layers, rows, *sizes)
         if not fits:
             return _lib.KV_NONE, None, f"skipped: {need / 1e9:.1f} GB of prefix K/V do not fit", sig
         return _lib.KV_SAVE, self._kv_alloc(layers, rows), "save", sig
