@@ -6,6 +6,8 @@
 #include <string>
 #include <vector>
 
+#include <nvtx3/nvToolsExt.h>   // header-only; ranges cost a pointer test unless a profiler is attached
+
 #include "../../include/fls_b200.h"
 #include "common.cuh"
 #include "host_cache.h"
@@ -232,6 +234,10 @@ struct ProfScope {
     fls_ctx::ProfSlot* slot = nullptr;
     cudaStream_t st;
     ProfScope(fls_ctx* ctx, int cls, double work, cudaStream_t stream) : c(ctx), st(stream) {
+        static const char* const kNames[FLS_PROF_CLASSES] = {"fls:gemm_qkv", "fls:gemm_o", "fls:gemm_gate_up",
+                                                             "fls:gemm_down", "fls:gemm_head", "fls:attention",
+                                                             "fls:rmsnorm", "fls:rope", "fls:embed", "fls:other"};
+        nvtxRangePushA(kNames[cls]);     // the reference's only trace is one wall-clock print (utils.py:304)
         if (!c->profiling) return;
         if (c->prof_ring.empty()) {
             c->prof_ring.resize(4096);
@@ -252,7 +258,13 @@ struct ProfScope {
             cudaEventRecord(slot->b, st);
             slot->pending = true;
         }
+        nvtxRangePop();
     }
+};
+
+struct NvtxRange {
+    explicit NvtxRange(const char* name) { nvtxRangePushA(name); }
+    ~NvtxRange() { nvtxRangePop(); }
 };
 
 inline cudaStream_t as_stream(void* s) { return reinterpret_cast<cudaStream_t>(s); }
@@ -501,6 +513,7 @@ int fls_prefetch_shard(fls_ctx* c, int slot, const int32_t* layer_ids, int n) {
         return ctx_fail(c, fail(kErrInvalid, "fls_prefetch_shard: slot %d, n %d", slot, n));
     Slot& s = c->slots[slot];
     if (s.in_use) return ctx_fail(c, fail(kErrState, "slot %d is still in use: release it before prefetching", slot));
+    NvtxRange prefetch_range("fls:prefetch_shard");
     size_t need = 0;
     for (int i = 0; i < n; ++i) {
         const int li = layer_ids[i];
@@ -673,6 +686,7 @@ int fls_decoder_layer_kv(fls_ctx* c, int slot, int layer_idx, uint16_t* x_dev, i
                                 "max_rows %d", row0 + n_rows, row0, c->max_rows));
     if (!c->rope_cos) return ctx_fail(c, fail(kErrState, "decoder_layer: call fls_set_rope_table first"));
     if (n_rows <= 0) return kOk;
+    NvtxRange layer_range(kv_mode == FLS_KV_LOAD ? "fls:decoder_layer(kv load)" : "fls:decoder_layer");
     const auto& m = c->m;
     const int Hd = m.hidden_size, I = m.intermediate_size;
     cudaStream_t st = as_stream(stream);
