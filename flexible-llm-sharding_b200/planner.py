@@ -97,9 +97,20 @@ def tokenize_prompts(tokenizer, prompts) -> list[TokenizedPrompt]:
     if not prompts:
         return []
     pad = tokenizer.pad_token_id
-    kw = dict(return_attention_mask=False, truncation=True, max_length=MAX_TOKEN_LEN)
-    pre = tokenizer([p for p, _ in prompts], **kw)["input_ids"]
-    flat = tokenizer([s for _, ss in prompts for s in ss], **kw)["input_ids"]
+    pre_txt, flat_txt = [p for p, _ in prompts], [s for _, ss in prompts for s in ss]
+    backend = getattr(tokenizer, "backend_tokenizer", None) if getattr(tokenizer, "is_fast", False) else None
+    if backend is not None:
+        # what `tokenizer(texts, truncation=True, max_length=...)` does underneath, minus the per-item Python
+        # wrapping of the results (a fifth of the tokenisation time at 1024 prompts)
+        backend.enable_truncation(max_length=MAX_TOKEN_LEN, stride=0, strategy="longest_first",
+                                  direction=getattr(tokenizer, "truncation_side", "right"))
+        backend.no_padding()
+        pre = [e.ids for e in backend.encode_batch(pre_txt, add_special_tokens=True)]
+        flat = [e.ids for e in backend.encode_batch(flat_txt, add_special_tokens=True)]
+    else:
+        kw = dict(return_attention_mask=False, truncation=True, max_length=MAX_TOKEN_LEN)
+        pre = tokenizer(pre_txt, **kw)["input_ids"]
+        flat = tokenizer(flat_txt, **kw)["input_ids"]
     out, k = [], 0
     for i, (_, ss) in enumerate(prompts):
         S = len(ss)
