@@ -189,17 +189,28 @@ def bench_model_parallel(a, shape_name, shape, n_prompts, prefix_tokens, n_optio
     md = model_dir_for(shape_name, 0, 1, torch.device("cuda:0"), alias)
     prompts = synthetic.make_prompts(n_prompts, shape.vocab_size, prefix_tokens, n_options, option_tokens, seed=1234)
     args = make_args(md, layer_num_per_shard=a.layer_num_per_shard, storage_location="gpu", max_rows=a.max_rows)
-    for _ in range(a.warmup):
-        out = score_all(args, copy.deepcopy(prompts), devices)
+    from flexible_llm_sharding_b200.utils import DeviceManager
+    dm = DeviceManager(args, devices)        # created once per process, as main.py:61 does; models live on it
+    for _ in range(max(1, a.warmup)):
+        out = score_all(args, copy.deepcopy(prompts), devices, dm)
     for d in devices:
         torch.cuda.synchronize(d)
+    for d in devices:                       # per-launch CUDA events: how busy each rank's GPU really is
+        dm.models[d].ctx.call("fls_reset_stats")
+        dm.models[d].ctx.call("fls_set_profiling", 1)
     with ClockSampler(0) as clocks:
         t0 = time.perf_counter()
         for _ in range(a.steps):
-            out = score_all(args, copy.deepcopy(prompts), devices)
+            out = score_all(args, copy.deepcopy(prompts), devices, dm)
         for d in devices:
             torch.cuda.synchronize(d)
         dt = time.perf_counter() - t0
+    per_rank = {d: {k: round(v, 3) if isinstance(v, float) else v for k, v in dm.models[d].last_timing.items()}
+                for d in devices}
+    for d in devices:
+        prof = dm.models[d].ctx.profile()
+        dm.models[d].ctx.call("fls_set_profiling", 0)
+        per_rank[d]["kernel_s_per_pass"] = round(sum(v["ms"] for v in prof.values()) / 1e3 / a.steps, 3)
     assert len(out) == n_prompts
     v = n_prompts * a.steps / dt
     rows_per_prompt = prefix_tokens + n_options * option_tokens
@@ -209,8 +220,10 @@ def bench_model_parallel(a, shape_name, shape, n_prompts, prefix_tokens, n_optio
         "scaling": "strong", "vs_baseline": None, "dtype": "f16 (fp32 accumulate)", "data": "synthetic",
         "config": {"workload": workload_name + (f" [{alias} distinct decoder layers, others aliased]" if alias else ""),
                    "parallelism": f"mp{G}: layer pipeline, shard j on GPU j mod {G}, NVLink peer hand-off",
-                   "timing": "host wall clock around main.score_all (includes ShardedLlama construction per pass, "
-                             "tokenisation, D2H of the scores)"},
+                   "timing": "host wall clock around main.score_all (strings in / numpy out: tokenisation, all "
+                             "ranks' passes, D2H of the scores; the DeviceManager and its per-GPU models are "
+                             "created once before the warm-up pass, as in main.py)",
+                   "last_pass_per_rank": per_rank},
         "prefill_tok_per_s": v * rows_per_prompt, "clocks": clocks.summary(),
         "e2e": {"value": v, "unit": "prompts/s"},
     }))

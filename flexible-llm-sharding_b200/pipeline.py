@@ -131,6 +131,10 @@ def _run(model, dm, inputs, shards, G, rank, serial, want_probs, answer_ids, ret
 
     with torch.cuda.device(dev), model._on_compute_stream(dev) as stream:
         sp = C.c_void_p(stream.cuda_stream)
+        if getattr(model, "_p2p_stream", None) is None:
+            model._p2p_stream = torch.cuda.Stream(dev)
+        p2p = model._p2p_stream
+        p2p_sp = C.c_void_p(p2p.cuda_stream)
         dv = model._device_inputs(packed, dev, kv_mode)
         x_all = torch.empty((packed.total_rows, H), dtype=torch.float16, device=dev)
         heads = torch.empty((packed.total_head_rows, H), dtype=torch.float16, device=dev)
@@ -162,16 +166,22 @@ def _run(model, dm, inputs, shards, G, rank, serial, want_probs, answer_ids, ret
                     dst = (nx_all[mb.row_lo:mb.row_lo + mb.n_rows] if still_tokens
                            else nheads[mb.head_lo:mb.head_lo + mb.n_head])
                     nbytes = y.numel() * 2
-                    call("fls_peer_copy", dst.data_ptr(), ndev, y.data_ptr(), C.c_size_t(nbytes), sp)
+                    # the hand-off rides its own stream: the next micro-batch's kernels start while the rows
+                    # cross NVLink (nobody writes these rows again before the consumer has used them)
+                    computed = torch.cuda.Event()
+                    computed.record(stream)
+                    p2p.wait_event(computed)
+                    call("fls_peer_copy", dst.data_ptr(), ndev, y.data_ptr(), C.c_size_t(nbytes), p2p_sp)
                     p2p_bytes += nbytes
                     done = torch.cuda.Event()
-                    done.record(stream)
+                    done.record(p2p)
                     _board_post(dm, ("ev", serial, g, bi), done)
             call("fls_release_shard", slot, sp)
 
         result, out_bytes = None, 0
         if owns_head:
             result, out_bytes = model._fetch_result(out, want_probs, stream, return_device)
+        stream.wait_stream(p2p)
         stream.synchronize()
         _barrier(dm, serial, rank, G)          # peers may still be writing into / reading from our buffers
         if kv_mode == _lib.KV_SAVE:
