@@ -50,10 +50,12 @@ def run_sharded_llama(device, prompt_list, device_manager, args):
     # stdout stays free for callers that print results there
     dt, s1 = perf_counter() - t0, model.ctx.stats()
     gb, ms = (s1.h2d_bytes - s0.h2d_bytes) / 1e9, s1.h2d_ms - s0.h2d_ms
-    print(f"{device} scored {len(outputs)} prompts in {dt:.2f}s ({len(outputs) / max(dt, 1e-9):.1f} prompts/s); "
-          f"streamed {gb:.1f} GB of weights" + (f" at {gb / (ms * 1e-3):.1f} GB/s" if ms > 0 else "")
-          + f"; activations: {model.last_timing.get('activation_tier', '-')}, prefix K/V: "
-          f"{model.last_timing.get('prefix_kv', '-')}", file=sys.stderr)
+    what = (f"scored {len(outputs)} prompts in {dt:.2f}s ({len(outputs) / max(dt, 1e-9):.1f} prompts/s)" if outputs
+            else f"ran its pipeline stages in {dt:.2f}s")
+    sys.stderr.write(f"{device} {what}; streamed {gb:.1f} GB of weights"
+                     + (f" at {gb / (ms * 1e-3):.1f} GB/s" if ms > 0 else "")
+                     + f"; activations: {model.last_timing.get('activation_tier', '-')}, prefix K/V: "
+                     f"{model.last_timing.get('prefix_kv', '-')}\n")        # one write: threads do not interleave
     return outputs
 
 
