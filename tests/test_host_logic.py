@@ -127,6 +127,27 @@ def test_cached_prefix_packing_is_the_normal_packing_remapped():
         assert np.array_equal(o.gather, remap[f.gather] - o.n_kv)  # gathers index the option-only rows
 
 
+def test_prefix_signature_depends_on_the_prefixes_only():
+    """The prefix K/V cache is keyed by the prefixes' token ids in order: growing options (the generation loop)
+    keep the key, any change to a prefix, to the order or to the number of prompts changes it."""
+    from flexible_llm_sharding_b200.utils import ShardedLlama
+    sig = ShardedLlama._kv_signature
+    shapes = [(70, 3, 9), (12, 2, 5), (129, 4, 33)]
+    a = _tok(shapes, seed=1)
+    b = _tok([(lp, S, ls + 1) for lp, S, ls in shapes], seed=2)       # other options ...
+    for x, y in zip(a, b):
+        y.prefix_ids = x.prefix_ids.copy()                             # ... same prefixes
+    assert sig(a) == sig(b)
+    c = _tok(shapes, seed=1)
+    c[1].prefix_ids[3] += 1
+    assert sig(c) != sig(a)
+    assert sig(a[::-1]) != sig(a) and sig(a[:2]) != sig(a)
+    # lengths are part of the key: moving a token from one prefix to the next must not collide
+    d = _tok(shapes, seed=1)
+    d[0].prefix_ids, d[1].prefix_ids = (np.concatenate([a[0].prefix_ids, a[1].prefix_ids[:1]]), a[1].prefix_ids[1:])
+    assert sig(d) != sig(a)
+
+
 def test_rope_table_matches_oracle():
     import torch
     cos, sin = planner.rope_tables(300, 128)
