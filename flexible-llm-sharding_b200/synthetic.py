@@ -225,3 +225,21 @@ def make_prompts(n_prompts: int, vocab_size: int, prefix_tokens: int, n_options:
             opts[0] = " ".join(f"w{i}" for i in rng.integers(3, vocab_size, option_tokens))
         out.append((pre, tuple(opts)))
     return out
+
+
+def make_edge_prompts(vocab_size: int, seed=4321) -> list[tuple[str, tuple[str, ...]]]:
+    """Prompt shapes the reference's loop accepts (utils.py:246-258,284-286) that `make_prompts` never produces."""
+    rng = np.random.default_rng(seed)
+
+    def words(n):
+        return " ".join(f"w{i}" for i in rng.integers(3, vocab_size, n))
+
+    return [
+        (words(20), (words(6), "", words(3))),        # an empty option: all pad, suffix_eos = -1 wraps to the last pad
+        (words(15), (words(9),)),                     # a single option
+        ("", (words(5), words(2))),                   # an empty prefix: BOS only
+        (words(33), (words(1), words(24), words(12), words(24), words(2))),      # five very ragged options
+        (words(40), tuple(words(7) for _ in range(3))),                          # equal lengths: no padding at all
+        (words(25), (words(150), words(131))),        # options longer than one 128-row attention tile
+        (words(140), (words(4), words(4))),           # a prefix longer than one query tile
+    ]

@@ -67,8 +67,10 @@ def _build(case_name, tmp_path_factory):
                                      case["n_options"], case["option_tokens"], seed=mg.PROMPT_SEED,
                                      ragged=True)
     golden = dict(np.load(os.path.join(GOLDEN_DIR, f"{case_name}.npz")))
+    edge_golden = dict(np.load(os.path.join(GOLDEN_DIR, f"{case_name}-edge.npz")))
     return dict(name=case_name, shape=shape, bin_dir=bin_dir, layer_dir=layer_dir, prompts=prompts,
-                golden=golden, digest=layer_dir_digest(layer_dir))
+                golden=golden, digest=layer_dir_digest(layer_dir),
+                edge_prompts=synthetic.make_edge_prompts(shape.vocab_size), edge_golden=edge_golden)
 
 
 @pytest.fixture(scope="session")

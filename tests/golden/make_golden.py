@@ -94,6 +94,19 @@ def main():
                     out[f"h{li}_suffix_{tag}"] = s.numpy().astype(np.float32)
             np.savez_compressed(os.path.join(GOLDEN_DIR, f"{name}.npz"), **out)
             print(name, {k: v.shape for k, v in out.items()})
+            # edge shapes (empty option / empty prefix / one option / very ragged / longer than a tile): the number
+            # of options differs per prompt, so the probabilities are stored per prompt
+            edge = synthetic.make_edge_prompts(shape.vocab_size)
+            eout = {"digest": out["digest"]}
+            for causal in (False, True):
+                tag = "causal" if causal else "ref"
+                s32, _ = hf_reference_scores(layer_dir, edge, tok, torch.float32, causal)
+                s16, _ = hf_reference_scores(layer_dir, edge, tok, torch.float16, causal)
+                for i, (a, b) in enumerate(zip(s32, s16)):
+                    eout[f"probs32_{tag}_{i}"] = a[:, 0].astype(np.float32)
+                    eout[f"probs16_{tag}_{i}"] = b[:, 0].astype(np.float16)
+            np.savez_compressed(os.path.join(GOLDEN_DIR, f"{name}-edge.npz"), **eout)
+            print(name + "-edge", len(edge), "prompts")
 
 
 if __name__ == "__main__":

@@ -160,11 +160,15 @@ def test_tokenize_matches_oracle(tiny):
     tok = AutoTokenizer.from_pretrained(tiny["layer_dir"])
     tok.pad_token = tok.eos_token
     tok.padding_side = "right"
-    got = planner.tokenize_prompts(tok, tiny["prompts"])
-    for g, (pre, suf) in zip(got, tiny["prompts"]):
+    prompts = tiny["prompts"] + tiny["edge_prompts"]          # incl. empty option, empty prefix, one option
+    got = planner.tokenize_prompts(tok, prompts)
+    for g, (pre, suf) in zip(got, prompts):
         p, s, e = O.tokenize_prompt(tok, pre, suf)
         assert g.prefix_ids.tolist() == p[0].tolist() and g.suffix_ids.tolist() == s.tolist()
         assert g.suffix_eos.tolist() == e.tolist()
+    # the edge prompts pack: a 150-token option spans two attention tiles, a 140-token prefix two query tiles
+    packed = planner.pack_prompts(got[len(tiny["prompts"]):], max_rows=400, max_head_rows=64)
+    assert packed.total_head_rows == sum(len(o) for _, o in tiny["edge_prompts"])
 
 
 def test_batched_tokenisation_equals_per_prompt_tokenisation(tiny):

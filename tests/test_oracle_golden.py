@@ -58,6 +58,26 @@ def test_oracle_fp16_matches_hf_modules_fp16(tiny):
     np.testing.assert_allclose(got, want, rtol=2e-2, atol=2e-6)
 
 
+@pytest.mark.parametrize("causal", [False, True])
+@pytest.mark.parametrize("which", ["tiny", "tiny_gqa"])
+def test_oracle_matches_hf_modules_on_edge_shapes(which, causal, request):
+    """Empty option (all pad: `suffix_eos = -1` wraps to the last pad position, utils.py:258,286), empty prefix
+    (BOS only), a single option, five very ragged options, options and a prefix longer than 128 rows."""
+    case = request.getfixturevalue(which)
+    tag = "causal" if causal else "ref"
+    prompts = case["edge_prompts"]
+    assert str(case["edge_golden"]["digest"]) == case["digest"]
+    orc = O.OracleShardedLlama(case["layer_dir"], dtype=torch.float32, layer_num_per_shard=3, prefix_causal=causal)
+    scores = orc(copy.deepcopy(prompts))
+    assert len(scores) == len(prompts)
+    for i, ((_, options), s) in enumerate(zip(prompts, scores)):
+        want = case["edge_golden"][f"probs32_{tag}_{i}"]
+        assert s.shape == (len(options), 1, want.shape[-1])
+        np.testing.assert_allclose(s[:, 0], want, rtol=FP32_PROB_RTOL, atol=1e-9, err_msg=f"prompt {i}")
+    # the empty option really has no token: index -1, i.e. the last (pad) position, is what gets scored
+    assert int(orc.suffix_eos[0][1]) == -1
+
+
 def test_prefix_mask_fork_matters(tiny):
     """The unmasked-prefix semantics (utils.py:272) is not a detail: it moves the scores."""
     g = tiny["golden"]

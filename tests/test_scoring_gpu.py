@@ -83,6 +83,31 @@ def test_scores_match_golden(which, causal, request):
     print(f"{which}/{tag}: max |dlogp| vs fp32 reference = {worst:.4f}")
 
 
+@pytest.mark.parametrize("which", ["tiny", "tiny_gqa"])
+@pytest.mark.parametrize("causal", [False, True])
+def test_edge_shapes_match_golden(which, causal, request):
+    """The CUDA path on the shapes of tests/golden/*-edge.npz (real HF modules through the reference's call
+    convention): an empty option scored at its wrapped-around last pad position, an empty prefix, one option,
+    five very ragged options, options / a prefix longer than one 128-row attention tile."""
+    case = request.getfixturevalue(which)
+    tag = "causal" if causal else "ref"
+    prompts = case["edge_prompts"]
+    _, out = run_model(case, prompts=prompts, prefix_causal=causal, layer_num_per_shard=2, max_rows=400)
+    assert len(out) == len(prompts)
+    worst = 0.0
+    for i, ((_, options), o) in enumerate(zip(prompts, out)):
+        assert o.shape == (len(options), 1, case["shape"].vocab_size) and o.dtype == np.float16
+        for suffix, ref in (("32", 1.0), ("16", 1.0)):
+            w = case["edge_golden"][f"probs{suffix}_{tag}_{i}"].astype(np.float64)
+            g = o[:, 0].astype(np.float64)
+            m = w >= P_MIN
+            d = np.abs(np.log(np.maximum(g[m], 1e-30)) - np.log(w[m])).max()
+            assert d <= LOGP_TOL, (i, suffix, d)
+            worst = max(worst, d)
+        assert np.abs(o[:, 0].astype(np.float64).sum(-1) - 1).max() <= 5e-3
+    print(f"{which}/{tag} edge shapes: max |dlogp| = {worst:.4f}")
+
+
 @pytest.mark.parametrize("k,storage,num_batch,max_rows", [
     (2, "gpu", 1, 16384), (3, "cpu", 2, 16384), (7, "gpu", 1, 200), (1, "cpu", 1, 160), (2, "disk", 1, 250)])
 def test_schedule_does_not_change_scores(tiny, k, storage, num_batch, max_rows, tmp_path):
