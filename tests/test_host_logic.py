@@ -239,3 +239,30 @@ def test_disk_tier_reads_reference_npy_files_in_place(tmp_path):
         f.write(open(tmp_path / "suffix-00000.npy", "rb").read()[:-10])
     with pytest.raises(IOError):
         ActivationStore._read_npy_into(str(tmp_path / "short.npy"), rows[39:54], (3, 5, H))
+
+
+def test_product_path_fails_loudly_without_its_cuda_library(tiny, monkeypatch, tmp_path):
+    """No CPU fallback anywhere in the product: a missing shared object, a missing CUDA device and an import of
+    the test-only oracle from the package are all errors."""
+    import torch
+    from flexible_llm_sharding_b200 import _lib
+    from flexible_llm_sharding_b200.utils import DeviceManager, ShardedLlama
+    monkeypatch.setattr(_lib, "_lib", None)
+    monkeypatch.setattr(_lib, "LIB_PATH", str(tmp_path / "libfls_b200.so"))
+    with pytest.raises(FileNotFoundError, match="no non-CUDA fallback"):
+        _lib.load()
+    monkeypatch.undo()
+    if not torch.cuda.is_available():
+        import types
+        args = types.SimpleNamespace(model_path=tiny["layer_dir"], layer_num_per_shard=1, storage_location="gpu",
+                                     data_parallel=False, num_batch=1, max_activation_in_cpu=100, disk_folder="./temp",
+                                     num_gen_token=1)
+        with pytest.raises(RuntimeError, match="no CPU fallback"):
+            ShardedLlama(args, DeviceManager(args, ["cuda:0"]), device="cuda:0")
+    # nothing under the package imports the oracle (test infrastructure only)
+    pkg = os.path.dirname(_lib.__file__)
+    for root, _, files in os.walk(pkg):
+        for fn in files:
+            if fn.endswith(".py"):
+                src = open(os.path.join(root, fn)).read()
+                assert not re.search(r"^\s*(from|import)\s+oracle\b", src, re.M), fn
