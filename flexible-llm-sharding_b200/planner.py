@@ -271,6 +271,16 @@ def rope_tables(n_pos: int, head_dim: int, theta: float = 10000.0):
     (transformers 4.3x `_set_cos_sin_cache` in fp32, cast to fp16 by utils.py:117-119)."""
     import torch
     inv_freq = 1.0 / (theta ** (torch.arange(0, head_dim, 2, dtype=torch.int64).to(torch.float32) / head_dim))
-    freqs = torch.arange(n_pos, dtype=torch.int64).to(torch.float32)[:, None] * inv_freq[None, :]
-    emb = torch.cat((freqs, freqs), dim=-1)
-    return emb.cos().to(torch.float16).contiguous(), emb.sin().to(torch.float16).contiguous()
+    cos = torch.empty((n_pos, head_dim), dtype=torch.float16)
+    sin = torch.empty((n_pos, head_dim), dtype=torch.float16)
+    # Evaluated in row blocks small enough for torch to stay on one thread: the vectorised fp32 cos/sin pick their
+    # range-reduction path per SIMD vector, so a table cut into per-thread chunks at non-row boundaries can differ
+    # from a row-aligned evaluation by one fp32 ulp (and, rarely, one fp16 ulp) depending on the host's core count.
+    block = max(1, 16384 // head_dim)
+    for lo in range(0, n_pos, block):
+        pos = torch.arange(lo, min(lo + block, n_pos), dtype=torch.int64).to(torch.float32)
+        freqs = pos[:, None] * inv_freq[None, :]
+        emb = torch.cat((freqs, freqs), dim=-1)
+        cos[lo:lo + emb.shape[0]] = emb.cos().to(torch.float16)
+        sin[lo:lo + emb.shape[0]] = emb.sin().to(torch.float16)
+    return cos, sin
