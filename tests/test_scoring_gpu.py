@@ -333,6 +333,24 @@ def test_prefix_kv_cache_gives_identical_scores(which, storage, max_rows, k, req
     assert not model._kv
 
 
+def test_prefix_kv_cache_with_the_mma_sync_attention_kernel(tiny_gqa):
+    """The comparison attention kernel (the one head_dim 64 models use) takes the same tile descriptors: the
+    [cached prefix rows | option rows] layout must give it the same bits as recomputing."""
+    from flexible_llm_sharding_b200.utils import DeviceManager, ShardedLlama
+    p1 = copy.deepcopy(tiny_gqa["prompts"])
+    p2 = _extend_options(p1, ["w7", "w11", "w5"])
+    outs = {}
+    for policy in ("off", "on"):
+        args = make_args(tiny_gqa["layer_dir"], prefix_kv_cache=policy, layer_num_per_shard=2, max_rows=300)
+        model = ShardedLlama(args, DeviceManager(args, ["cuda:0"]))
+        model.ctx.call("fls_set_option", b"attention_impl", 0)
+        outs[policy] = [model(copy.deepcopy(p)) for p in (p1, p2)]
+        assert model.last_timing["prefix_kv"] == ("load" if policy == "on" else "off")
+    for step in range(2):
+        for a, b in zip(outs["off"][step], outs["on"][step]):
+            assert np.array_equal(a, b), step
+
+
 def test_cli_generation_with_and_without_prefix_kv_cache(tiny, tmp_path, monkeypatch):
     """main.py --num_gen_token 3: the prefix K/V cache is on by default and must not change a single bit."""
     from flexible_llm_sharding_b200.main import main
