@@ -305,7 +305,7 @@ int head_impl(fls_ctx* c, const __half* x, const __half* W, int n_rows, int V, i
     }
     if (logprob && n_ids > 0) {
         ProfScope ps(c, FLS_PROF_OTHER, 0, st);
-        FLS_TRY(gather_logprob_launch(x, K, W, K, K, answer_ids, n_ids, c->lse, n_rows, logprob, st));
+        FLS_TRY(gather_logprob_launch(x, K, W, K, K, answer_ids, n_ids, c->lse, n_rows, V, logprob, st));
         c->stats.kernel_launches += 1;
     }
     if (lse_out) FLS_CUDA(cudaMemcpyAsync(lse_out, c->lse, sizeof(float) * n_rows, cudaMemcpyDeviceToDevice, st));
@@ -493,6 +493,31 @@ int fls_register_layer_file(fls_ctx* c, int layer_idx, int kind, const char* pat
         CTX_TRY(c, expect_shape(L, "mlp.down_proj.weight", m.hidden_size, m.intermediate_size, &bytes));
         CTX_TRY(c, expect_shape(L, ".input_layernorm.weight", m.hidden_size, -1, &bytes));
         CTX_TRY(c, expect_shape(L, "post_attention_layernorm.weight", m.hidden_size, -1, &bytes));
+    }
+    // Every tensor of the file must be one this architecture uses: a bias or an adapter tensor that the kernels
+    // would silently ignore (the reference, which builds the model from the config, would not) is refused.
+    {
+        static const char* const kDecoder[] = {"self_attn.q_proj.weight", "self_attn.k_proj.weight",
+                                               "self_attn.v_proj.weight", "self_attn.o_proj.weight",
+                                               "mlp.gate_proj.weight", "mlp.up_proj.weight", "mlp.down_proj.weight",
+                                               ".input_layernorm.weight", "post_attention_layernorm.weight",
+                                               "rotary_emb.inv_freq"};   // old checkpoints carry this buffer; unused
+        static const char* const kEmbed[] = {"embed_tokens.weight"};
+        static const char* const kNorm[] = {"norm.weight"};
+        static const char* const kHead[] = {"lm_head.weight"};
+        const char* const* names = kind == FLS_LAYER_EMBED ? kEmbed : kind == FLS_LAYER_NORM ? kNorm
+                                   : kind == FLS_LAYER_HEAD ? kHead : kDecoder;
+        const int n_names = kind == FLS_LAYER_DECODER ? 10 : 1;
+        for (auto& t : L.header) {
+            bool known = false;
+            for (int i = 0; i < n_names && !known; ++i) {
+                const size_t n = strlen(names[i]);
+                known = t.name.size() >= n && t.name.compare(t.name.size() - n, n, names[i]) == 0;
+            }
+            if (!known)
+                return ctx_fail(c, fail(kErrInvalid, "%s: unexpected tensor %s (biases and non-Llama-2 tensors are not "
+                                        "supported)", path, t.name.c_str()));
+        }
     }
     L.slot_bytes = bytes;
     if (load_now) CTX_TRY(c, acquire_host_image(L.path, &L.img));

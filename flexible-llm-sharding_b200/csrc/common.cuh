@@ -87,9 +87,9 @@ int rope_launch(__half* qkv, int ld, int n_rows, int n_q_heads, int n_kv_heads, 
 int swiglu_launch(const __half* gate, const __half* up, int ld_in, int n_rows, int I, __half* out, int ld_out,
                   cudaStream_t s);
 int lse_reduce_launch(const float2* partial, int n_rows, int n_blocks, float* lse, cudaStream_t s);
-// out[r, j] = float(fp16(dot(x[r], W[ids[r*n_ids + j]]))) - lse[r]
+// out[r, j] = float(fp16(dot(x[r], W[ids[r*n_ids + j]]))) - lse[r]; NaN where the id is outside [0, n_vocab)
 int gather_logprob_launch(const __half* x, int ldx, const __half* W, int ldw, int H, const int32_t* ids, int n_ids,
-                          const float* lse, int n_rows, float* out, cudaStream_t s);
+                          const float* lse, int n_rows, int n_vocab, float* out, cudaStream_t s);
 
 // ---- attention (attention.cu) ------------------------------------------------------------------
 // One descriptor per query tile; see include/fls_b200.h fls_attn_tile.

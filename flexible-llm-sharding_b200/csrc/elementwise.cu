@@ -219,12 +219,17 @@ __global__ void lse_reduce_kernel(const float2* __restrict__ partial, int n_rows
 // hold), out = logit - lse[r].
 __global__ void gather_logprob_kernel(const __half* __restrict__ x, int ldx, const __half* __restrict__ W, int ldw,
                                       int H, const int32_t* __restrict__ ids, int n_ids,
-                                      const float* __restrict__ lse, int n_rows, float* __restrict__ out) {
+                                      const float* __restrict__ lse, int n_rows, int n_vocab,
+                                      float* __restrict__ out) {
     const long long wid = blockIdx.x * static_cast<long long>(blockDim.x >> 5) + (threadIdx.x >> 5);
     if (wid >= static_cast<long long>(n_rows) * n_ids) return;
     const int r = static_cast<int>(wid / n_ids);
     const int lane = threadIdx.x & 31;
     const int id = ids[wid];
+    if (id < 0 || id >= n_vocab) {  // ids live on the device: an id outside W's rows must not become a wild read
+        if (lane == 0) out[wid] = __int_as_float(0x7fc00000);  // NaN marks the entry
+        return;
+    }
     const __half* xr = x + static_cast<size_t>(r) * ldx;
     const __half* wr = W + static_cast<size_t>(id) * ldw;
     float acc = 0.f;
@@ -329,12 +334,12 @@ int lse_reduce_launch(const float2* partial, int n_rows, int n_blocks, float* ls
 }
 
 int gather_logprob_launch(const __half* x, int ldx, const __half* W, int ldw, int H, const int32_t* ids, int n_ids,
-                          const float* lse, int n_rows, float* out, cudaStream_t s) {
+                          const float* lse, int n_rows, int n_vocab, float* out, cudaStream_t s) {
     if (H % 8 || ldx % 8 || ldw % 8) return fail(kErrInvalid, "gather_logprob: sizes must be multiples of 8");
     const long long warps = static_cast<long long>(n_rows) * n_ids;
     if (warps <= 0) return kOk;
     gather_logprob_kernel<<<static_cast<int>((warps + 7) / 8), 256, 0, s>>>(x, ldx, W, ldw, H, ids, n_ids, lse, n_rows,
-                                                                            out);
+                                                                            n_vocab, out);
     FLS_CUDA(cudaGetLastError());
     return kOk;
 }

@@ -22,6 +22,7 @@
 #include <cuda.h>
 
 #include <algorithm>
+#include <mutex>
 
 #include "common.cuh"
 #include "ptx.cuh"
@@ -502,6 +503,10 @@ int encode_tmap_2d(::CUtensorMap_st* tm, const __half* base, int rows, int cols,
 }
 
 int gemm_init() {
+    // contexts are created from one host thread per GPU and fls_op_head_noalloc sets itself up on first use: the
+    // entry-point lookup and the per-device function attributes are serialised here, not by the callers
+    static std::mutex mu;
+    std::lock_guard<std::mutex> lock(mu);
     if (!g_encode) {
         void* fn = nullptr;
         cudaDriverEntryPointQueryResult qres;

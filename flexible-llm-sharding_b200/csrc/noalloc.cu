@@ -85,6 +85,10 @@ extern "C" int fls_op_head_noalloc(const uint16_t* x_dev, const uint16_t* w_dev,
                     n_rows, n, kMaxRows, FLS_NOALLOC_MAX_VOCAB);
     if (n_ids > 0 && (!answer_ids_dev || !logprob_dev))
         return fail(kErrInvalid, "fls_op_head_noalloc: n_ids > 0 needs answer_ids_dev and logprob_dev");
+    if (n % 8 || k % 8 || ((reinterpret_cast<uintptr_t>(x_dev) | reinterpret_cast<uintptr_t>(w_dev) |
+                            reinterpret_cast<uintptr_t>(probs_dev)) & 15))
+        return fail(kErrInvalid, "fls_op_head_noalloc: n and k must be multiples of 8 and x, w, probs 16-byte aligned "
+                    "(n=%d k=%d)", n, k);
     int dev = 0;
     FLS_CUDA(cudaGetDevice(&dev));
     if (dev < 0 || dev >= kMaxDevices) return fail(kErrInvalid, "fls_op_head_noalloc: device ordinal %d not supported", dev);
@@ -107,7 +111,7 @@ extern "C" int fls_op_head_noalloc(const uint16_t* x_dev, const uint16_t* w_dev,
         FLS_TRY(gemm_launch(kEpiProbs, a, num_sms, st));
     }
     if (n_ids > 0)
-        FLS_TRY(gather_logprob_launch(a.A, k, a.B, k, k, answer_ids_dev, n_ids, lse, n_rows, logprob_dev, st));
+        FLS_TRY(gather_logprob_launch(a.A, k, a.B, k, k, answer_ids_dev, n_ids, lse, n_rows, n, logprob_dev, st));
     if (lse_dev) FLS_CUDA(cudaMemcpyAsync(lse_dev, lse, sizeof(float) * n_rows, cudaMemcpyDeviceToDevice, st));
     return kOk;
 }

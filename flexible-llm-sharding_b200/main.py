@@ -75,6 +75,10 @@ def build_parser() -> argparse.ArgumentParser:
     parser.add_argument("--disk_folder", type=str, default="./temp",
                         help="folder path for writing files of intermediate activations in 'disk' mode")
     parser.add_argument("--num_gen_token", type=int, default=1, help="how many new tokens to be generated")
+    # not a reference flag: rows per micro-batch (a prompt's prefix + all its option rows must fit one);
+    # also settable through the FLS_MAX_ROWS environment variable
+    parser.add_argument("--max_rows", type=int, default=None,
+                        help="token rows per micro-batch (default 16384); raise it for prompts with more rows")
     return parser
 
 

@@ -109,6 +109,7 @@ class ShardedLlama:
 
         with open(os.path.join(args.model_path, "config.json")) as f:
             self.config = json.load(f)
+        self._check_config(self.config)
         self.tokenizer = load_tokenizer(args.model_path)
         self.tokenizer.pad_token = self.tokenizer.eos_token      # utils.py:103
         self.tokenizer.padding_side = "right"                    # utils.py:104
@@ -119,7 +120,7 @@ class ShardedLlama:
 
         # extras with reference-compatible defaults (not CLI flags in the reference)
         self.prefix_causal = bool(getattr(args, "prefix_causal", False))     # False = reference (utils.py:272)
-        self.max_rows = int(getattr(args, "max_rows", 16384))
+        self.max_rows = int(getattr(args, "max_rows", None) or os.environ.get("FLS_MAX_ROWS", 16384))
         self.max_head_rows = int(getattr(args, "max_head_rows", 4096))
         self.force_tier = bool(getattr(args, "force_storage_tier", False) or os.environ.get("FLS_FORCE_STORAGE"))
         self.hbm_activation_budget = getattr(args, "hbm_activation_budget", None)
@@ -157,6 +158,35 @@ class ShardedLlama:
         self._kv = {}            # prefix signature -> per-layer prefix K/V of an earlier pass (see _kv_plan)
         self.kv_dim = cfg.get("num_key_value_heads", nh) * self.head_dim
         self.last_timing = {}
+
+    @staticmethod
+    def _check_config(cfg):
+        """The reference builds whatever `AutoModelForCausalLM.from_config` returns (utils.py:112) and so honours
+        every config field; the kernels here implement the Llama-2 architecture only.  Anything that would change
+        the arithmetic is refused up front instead of giving silently different scores."""
+        bad = []
+        if cfg.get("model_type", "llama") != "llama":
+            bad.append(f"model_type={cfg['model_type']!r} (only 'llama')")
+        if cfg.get("hidden_act", "silu") != "silu":
+            bad.append(f"hidden_act={cfg['hidden_act']!r} (only 'silu')")
+        scaling = cfg.get("rope_scaling")
+        if scaling and (scaling.get("rope_type", scaling.get("type")) not in (None, "default")):
+            bad.append(f"rope_scaling={scaling!r} (not implemented)")
+        for key in ("attention_bias", "mlp_bias", "tie_word_embeddings"):
+            if cfg.get(key):
+                bad.append(f"{key}=true (not implemented)")
+        if cfg.get("pretraining_tp", 1) not in (None, 1):
+            bad.append(f"pretraining_tp={cfg['pretraining_tp']} (sliced projections are not implemented)")
+        if bad:
+            raise ValueError("unsupported model configuration: " + "; ".join(bad))
+
+    def _rank_tag(self, rank: int) -> str:
+        """Suffix of the disk tier's file names (utils.py:172,176: the GPU rank with --data_parallel, else none).
+        With one process per GPU (torchrun) the index within this process's device list is always 0, so the
+        global rank is what keeps the processes' files apart in a shared --disk_folder."""
+        if int(os.environ.get("WORLD_SIZE", "1")) > 1:
+            return os.environ.get("RANK", str(rank))
+        return str(rank) if self.args.data_parallel else ""
 
     def _set_pinned_limit(self, limit):
         """Bound the pinned host copies of the layer files (the reference's `max_layer_num`, utils.py:31, in bytes).
@@ -404,7 +434,7 @@ class ShardedLlama:
             sp = C.c_void_p(stream.cuda_stream)
             dv = self._device_inputs(packed, dev, kv_mode)
             mbs = packed.micro_batches
-            rank_tag = str(rank) if self.args.data_parallel else ""
+            rank_tag = self._rank_tag(rank)
             store = ActivationStore(self.args.storage_location, packed, self.hidden, dev, stream,
                                     disk_folder=getattr(self.args, "disk_folder", "./temp"), rank_tag=rank_tag,
                                     hbm_budget_bytes=self.hbm_activation_budget, force_tier=self.force_tier,

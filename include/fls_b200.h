@@ -190,7 +190,8 @@ int fls_final_norm(fls_ctx* ctx, int slot, int layer_idx, const uint16_t* x_dev,
  * (max, sum-exp) epilogue + reduction -> log-sum-exp per row; then, as requested,
  *   probs_dev   [n_rows, vocab] fp16 probabilities (the reference's output format), GEMM pass 2 with
  *               an exp(logit - lse) epilogue; may be NULL;
- *   logprob_dev [n_rows, n_ids] fp32 log-probabilities of `answer_ids_dev[n_rows, n_ids]`; may be NULL;
+ *   logprob_dev [n_rows, n_ids] fp32 log-probabilities of `answer_ids_dev[n_rows, n_ids]` (an id outside
+ *               [0, vocab) gives NaN in its entry, never a read outside the weight); may be NULL;
  *   lse_dev     [n_rows] fp32; may be NULL. */
 int fls_lm_head(fls_ctx* ctx, int slot, int layer_idx, const uint16_t* x_dev, int n_rows, uint16_t* probs_dev,
                 const int32_t* answer_ids_dev, int n_ids, float* logprob_dev, float* lse_dev, void* stream);
@@ -243,7 +244,10 @@ int fls_op_head(fls_ctx* ctx, const uint16_t* x_dev, const uint16_t* w_dev, int 
  *  - all calls on a device share that array: calls whose kernels overlap on the GPU race, so keep
  *    them on one stream or order them.  Nothing in the array needs clearing between calls (each
  *    call writes every entry it reads).
- * Inputs/outputs are the caller's buffers, as in fls_op_head; errors via fls_last_error(NULL). */
+ * Inputs/outputs are the caller's buffers, as in fls_op_head: x [n_rows, k] and w [n, k] fp16 row-major and
+ * probs [n_rows, n] fp16, each 16-byte aligned, n and k multiples of 8 (FLS_ERR_INVALID otherwise);
+ * answer_ids [n_rows, n_ids] int32 on the device - an id outside [0, n) yields NaN in its logprob entry
+ * instead of a read outside w.  Errors via fls_last_error(NULL). */
 #define FLS_NOALLOC_MAX_ROWS 1024
 #define FLS_NOALLOC_MAX_VOCAB 32768
 int fls_op_head_noalloc(const uint16_t* x_dev, const uint16_t* w_dev, int n_rows, int n, int k, uint16_t* probs_dev,

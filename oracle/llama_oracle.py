@@ -92,9 +92,11 @@ def rmsnorm(x: torch.Tensor, w: torch.Tensor, eps: float) -> torch.Tensor:
 def rope_cos_sin(positions: torch.Tensor, head_dim: int, theta: float, dtype) -> tuple[torch.Tensor, torch.Tensor]:
     """positions [L] int64 -> cos, sin [L, head_dim] in `dtype` (fp32 math, then cast)."""
     inv_freq = 1.0 / (theta ** (torch.arange(0, head_dim, 2, dtype=torch.int64).to(torch.float32) / head_dim))
-    freqs = positions.to(torch.float32)[:, None] * inv_freq[None, :]
+    # evaluated on the host like the reference's rotary buffers (built at module construction on the CPU, then
+    # moved and cast by utils.py:117-119), whatever device the run is on
+    freqs = positions.cpu().to(torch.float32)[:, None] * inv_freq[None, :]
     emb = torch.cat((freqs, freqs), dim=-1)
-    return emb.cos().to(dtype), emb.sin().to(dtype)
+    return emb.cos().to(dtype).to(positions.device), emb.sin().to(dtype).to(positions.device)
 
 
 def rotate_half(x: torch.Tensor) -> torch.Tensor:
@@ -162,20 +164,24 @@ def decoder_layer(x: torch.Tensor, W: dict, prefix: str, cfg: dict, positions: t
 # --------------------------------------------------------------------------------------
 # the scoring loop (utils.py:133-305 restated)
 # --------------------------------------------------------------------------------------
-def load_layer(model_path: str, layer_name: str, dtype) -> dict:
-    """utils.py:121-131 (weights cast to the run dtype, as set_module_tensor_to_device does)."""
+def load_layer(model_path: str, layer_name: str, dtype, device="cpu") -> dict:
+    """utils.py:121-131 (weights moved to the device and cast to the run dtype, as set_module_tensor_to_device does)."""
     from safetensors.torch import load_file
     sd = load_file(os.path.join(model_path, f"{layer_name}.safetensors"))
-    return {k: v.to(dtype) for k, v in sd.items()}
+    return {k: v.to(device).to(dtype) for k, v in sd.items()}
 
 
 class OracleShardedLlama:
-    """Restated `ShardedLlama` (single device, `storage_location='cpu'`)."""
+    """Restated `ShardedLlama` (single device, `storage_location='cpu'`).  `device="cuda:0"` with
+    `dtype=torch.float16` is the reference's own arithmetic path on this box (torch eager + cuBLAS, one prompt
+    at a time, utils.py:228-297): the like-for-like comparator of the GPU tests and bench.py's
+    `gpu_eager_baseline`."""
 
     def __init__(self, model_path: str, tokenizer=None, dtype=torch.float32,
                  layer_num_per_shard: int = 1, prefix_causal: bool = False,
-                 max_decoder_layers: int | None = None):
+                 max_decoder_layers: int | None = None, device="cpu"):
         self.model_path = model_path
+        self.device = torch.device(device)
         with open(os.path.join(model_path, "config.json")) as f:
             self.cfg = json.load(f)
         if tokenizer is None:
@@ -205,20 +211,22 @@ class OracleShardedLlama:
         trace = {li: [] for li in trace_layers}
 
         # utils.py:219-221
+        dev = self.device
         mask_full = torch.finfo(dt).min * torch.ones((MAX_TOKEN_LEN, MAX_TOKEN_LEN), dtype=dt)
-        mask_full = mask_full.triu(diagonal=1)[None, None]
-        position_ids = torch.arange(MAX_TOKEN_LEN, dtype=torch.long)
+        mask_full = mask_full.triu(diagonal=1)[None, None].to(dev)
+        position_ids = torch.arange(MAX_TOKEN_LEN, dtype=torch.long, device=dev)
 
         with torch.inference_mode():
             for shard in shards:
                 W = {}
                 for li in shard:
-                    W.update(load_layer(self.model_path, self.layer_names[li], dt))
+                    W.update(load_layer(self.model_path, self.layer_names[li], dt, dev))
                 for pi in range(n):
                     for li in shard:
                         name = self.layer_names[li]
                         if li == 0:
                             prefix, suffix, eos = tokenize_prompt(self.tokenizer, inputs[pi][0], inputs[pi][1])
+                            prefix, suffix = prefix.to(dev), suffix.to(dev)
                             suffix_eos.append(eos)
                         elif li == shard[0]:
                             assert prompt2layer[pi] == li - 1
@@ -239,7 +247,7 @@ class OracleShardedLlama:
                         elif name == "model.norm":
                             prefix = None
                             pos = suffix_eos[pi]
-                            suffix = rmsnorm(suffix[torch.arange(suffix.shape[0]), pos][:, None],
+                            suffix = rmsnorm(suffix[torch.arange(suffix.shape[0], device=dev), pos.to(dev)][:, None],
                                              W["model.norm.weight"], self.cfg["rms_norm_eps"])
                         else:
                             logits = torch.nn.functional.linear(suffix, W["lm_head.weight"])[:, 0]

@@ -272,3 +272,32 @@ def test_product_path_fails_loudly_without_its_cuda_library(tiny, monkeypatch, t
             if fn.endswith(".py"):
                 src = open(os.path.join(root, fn)).read()
                 assert not re.search(r"^\s*(from|import)\s+oracle\b", src, re.M), fn
+
+
+def test_config_fields_that_change_the_arithmetic_are_refused():
+    """ADVICE r1: the reference honours every config field through AutoModelForCausalLM.from_config (utils.py:112);
+    this build implements Llama-2 only and must say so instead of scoring wrongly."""
+    from flexible_llm_sharding_b200 import synthetic
+    from flexible_llm_sharding_b200.utils import ShardedLlama
+    ok = synthetic.LlamaShape.named("tiny").hf_config()
+    ShardedLlama._check_config(ok)
+    ShardedLlama._check_config(dict(ok, rope_scaling=None))
+    for bad in (dict(rope_scaling={"rope_type": "llama3", "factor": 8.0}), dict(hidden_act="gelu"),
+                dict(attention_bias=True), dict(mlp_bias=True), dict(model_type="mistral"),
+                dict(tie_word_embeddings=True), dict(pretraining_tp=2)):
+        with pytest.raises(ValueError, match="unsupported model configuration"):
+            ShardedLlama._check_config(dict(ok, **bad))
+
+
+def test_disk_tier_file_tag_is_the_global_rank_under_torchrun(monkeypatch):
+    """with one process per GPU every process has device index 0; the files of the disk tier must
+    still be kept apart in a shared --disk_folder (reference names: utils.py:172,176)."""
+    import types
+    from flexible_llm_sharding_b200.utils import ShardedLlama
+    dp = types.SimpleNamespace(args=types.SimpleNamespace(data_parallel=True))
+    mp = types.SimpleNamespace(args=types.SimpleNamespace(data_parallel=False))
+    monkeypatch.delenv("WORLD_SIZE", raising=False)
+    assert ShardedLlama._rank_tag(dp, 3) == "3" and ShardedLlama._rank_tag(mp, 3) == ""
+    monkeypatch.setenv("WORLD_SIZE", "4")
+    monkeypatch.setenv("RANK", "2")
+    assert ShardedLlama._rank_tag(dp, 0) == "2" and ShardedLlama._rank_tag(mp, 0) == "2"

@@ -19,17 +19,7 @@ import torch
 
 pytestmark = pytest.mark.gpu
 
-LOGP_TOL = 5e-2
-P_MIN = 1e-4
-ANSWER_TOKEN = 5
-
-
-def make_args(model_path, **kw):
-    d = dict(model_path=model_path, num_batch=1, layer_num_per_shard=1, storage_location="gpu",
-             max_activation_in_cpu=100, data_parallel=False, disk_folder="./temp", num_gen_token=1,
-             resident_weights="never")
-    d.update(kw)
-    return types.SimpleNamespace(**d)
+from _parity import ANSWER_TOKEN, LOGP_TOL, P_MIN, check_against_reference, make_args  # noqa: E402,F401
 
 
 def run_model(case, prompts=None, **kw):
@@ -41,28 +31,6 @@ def run_model(case, prompts=None, **kw):
     out = model(prompts)
     assert all(p is None for p in prompts)                    # reference utils.py:259
     return model, out
-
-
-def check_against_reference(out, want32):
-    got = np.stack([o[:, 0] for o in out])
-    assert got.dtype == np.float16 and got.shape == want32.shape
-    g, w = got.astype(np.float64), want32.astype(np.float64)
-    m = w >= P_MIN
-    dlog = np.abs(np.log(np.maximum(g[m], 1e-30)) - np.log(w[m]))
-    assert dlog.max() <= LOGP_TOL, dlog.max()
-    assert np.abs(g.sum(-1) - 1).max() <= 5e-3
-    # top-1 token: identical wherever the reference's top-2 margin is rankable
-    srt = np.sort(np.log(w), axis=-1)
-    rankable = (srt[..., -1] - srt[..., -2]) > 2 * LOGP_TOL
-    assert (g.argmax(-1)[rankable] == w.argmax(-1)[rankable]).all()
-    # option ranking on the answer token
-    gl, wl = np.log(np.maximum(g[..., ANSWER_TOKEN], 1e-30)), np.log(w[..., ANSWER_TOKEN])
-    for p in range(w.shape[0]):
-        order = np.argsort(-wl[p])
-        gaps = -np.diff(wl[p][order])
-        if (gaps > 2 * LOGP_TOL).all():
-            assert (np.argsort(-gl[p]) == order).all()
-    return dlog.max()
 
 
 @pytest.mark.parametrize("which", ["tiny", "tiny_gqa"])
@@ -401,3 +369,25 @@ def test_cli_round_trip(tiny, tmp_path):
     assert np.abs(np.log(got0[m]) - np.log(want[m].astype(np.float64))).max() <= LOGP_TOL
     for (pre, suf), (pre0, suf0) in zip(updated, tiny["prompts"][:3]):
         assert pre == pre0 and all(s.startswith(s0) and len(s) > len(s0) for s, s0 in zip(suf, suf0))
+
+
+def test_unexpected_tensors_and_max_rows_env(tiny, tmp_path, monkeypatch):
+    """A layer file with a tensor the kernels would ignore (a bias) is refused at registration; FLS_MAX_ROWS
+    raises the micro-batch limit for CLI users."""
+    from safetensors.torch import load_file, save_file
+    from flexible_llm_sharding_b200 import _lib
+    from flexible_llm_sharding_b200.utils import DeviceManager, ShardedLlama
+    d = tmp_path / "with_bias"
+    shutil_copy = __import__("shutil").copytree
+    shutil_copy(tiny["layer_dir"], d)
+    sd = load_file(str(d / "model.layers.1.safetensors"))
+    sd["model.layers.1.self_attn.q_proj.bias"] = torch.zeros(sd["model.layers.1.self_attn.q_proj.weight"].shape[0],
+                                                             dtype=torch.float16)
+    save_file(sd, str(d / "model.layers.1.safetensors"))
+    args = make_args(str(d))
+    with pytest.raises(_lib.FlsError, match="unexpected tensor"):
+        ShardedLlama(args, DeviceManager(args, ["cuda:0"]), device="cuda:0")
+    monkeypatch.setenv("FLS_MAX_ROWS", "96")
+    args = make_args(tiny["layer_dir"])
+    model = ShardedLlama(args, DeviceManager(args, ["cuda:0"]), device="cuda:0")
+    assert model.max_rows == 96
