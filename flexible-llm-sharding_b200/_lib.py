@@ -89,6 +89,13 @@ _SIGNATURES = {
     "fls_set_host_cache_limit": (_I, [C.c_size_t]),
     "fls_trim_host_cache": (_I, [C.c_size_t]),
     "fls_peer_copy": (_I, [_P, _P, _I, _P, C.c_size_t, _P]),
+    "fls_ipc_alloc": (_I, [_P, C.c_size_t, C.POINTER(_P), _P]),
+    "fls_ipc_free": (_I, [_P, _P]),
+    "fls_ipc_open": (_I, [_P, _P, C.POINTER(_P)]),
+    "fls_ipc_close": (_I, [_P, _P]),
+    "fls_flag_signal": (_I, [_P, _P, C.c_uint32, _P]),
+    "fls_flag_wait": (_I, [_P, _P, C.c_uint32, C.c_uint32, _P]),
+    "fls_flag_timeouts": (_I, [_P, C.POINTER(C.c_uint32)]),
     "fls_embed": (_I, [_P, _I, _I, _P, _I, _P, _P]),
     "fls_decoder_layer": (_I, [_P, _I, _I, _P, _I, _P, _P, _I, _P]),
     "fls_decoder_layer_kv": (_I, [_P, _I, _I, _P, _I, _P, _P, _I, _I, _P, _I, _P, _P]),

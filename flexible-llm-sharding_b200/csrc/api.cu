@@ -115,6 +115,9 @@ struct fls_ctx {
     int gemm_cache_hints = 0;
     int rmsnorm_variant = 0;
     int fuse_rope = 1;  // 1 = rotary embedding in the QKV GEMM epilogue (head_dim 128), 0 = separate kernel
+    // cross-process hand-off: buffers this context exported (fls_ipc_alloc) and peers' buffers it mapped (fls_ipc_open)
+    std::vector<void*> ipc_owned, ipc_mapped;
+    uint32_t* flag_timeouts = nullptr;  // device counter bumped by a flag wait that gave up
 };
 
 namespace {
@@ -400,6 +403,9 @@ int fls_destroy(fls_ctx* c) {
     if (c->rope_cos) cudaFree(c->rope_cos);
     if (c->rope_sin) cudaFree(c->rope_sin);
     if (c->copy_stream) cudaStreamDestroy(c->copy_stream);
+    for (void* p : c->ipc_mapped) cudaIpcCloseMemHandle(p);
+    for (void* p : c->ipc_owned) cudaFree(p);
+    if (c->flag_timeouts) cudaFree(c->flag_timeouts);
     for (auto& p : c->prof_ring) {
         cudaEventDestroy(p.a);
         cudaEventDestroy(p.b);
@@ -821,6 +827,12 @@ int fls_peer_copy(fls_ctx* c, void* dst_dev, int dst_device, const void* src_dev
     ENTER(c);
     if (!dst_dev || !src_dev) return ctx_fail(c, fail(kErrInvalid, "fls_peer_copy: null pointer"));
     if (bytes == 0) return kOk;
+    if (dst_device < 0) {
+        // `dst_dev` is a mapping made by fls_ipc_open: unified addressing knows which GPU it lives on
+        CTX_CUDA(c, cudaMemcpyAsync(dst_dev, src_dev, bytes, cudaMemcpyDefault, as_stream(stream)));
+        c->stats.p2p_bytes += bytes;
+        return kOk;
+    }
     if (dst_device != c->device && !(c->peer_enabled_mask & (1ull << (dst_device & 63)))) {
         int can = 0;
         CTX_CUDA(c, cudaDeviceCanAccessPeer(&can, c->device, dst_device));
@@ -834,6 +846,89 @@ int fls_peer_copy(fls_ctx* c, void* dst_dev, int dst_device, const void* src_dev
     }
     CTX_CUDA(c, cudaMemcpyPeerAsync(dst_dev, dst_device, src_dev, c->device, bytes, as_stream(stream)));
     c->stats.p2p_bytes += bytes;
+    return kOk;
+}
+
+// --------------------------------------------------------------------------------- hand-off across processes
+int fls_ipc_alloc(fls_ctx* c, size_t bytes, void** dev_out, unsigned char* handle_out) {
+    ENTER(c);
+    if (!dev_out || !handle_out || bytes == 0) return ctx_fail(c, fail(kErrInvalid, "fls_ipc_alloc: bad argument"));
+    static_assert(sizeof(cudaIpcMemHandle_t) == FLS_IPC_HANDLE_BYTES, "handle size");
+    void* p = nullptr;
+    CTX_CUDA(c, cudaMalloc(&p, bytes));
+    cudaError_t e = cudaMemset(p, 0, bytes);
+    cudaIpcMemHandle_t h;
+    if (e == cudaSuccess) e = cudaIpcGetMemHandle(&h, p);
+    if (e != cudaSuccess) {
+        cudaFree(p);
+        return ctx_fail(c, fail(kErrCuda, "fls_ipc_alloc(%zu bytes): %s", bytes, cudaGetErrorString(e)));
+    }
+    memcpy(handle_out, &h, sizeof(h));
+    c->ipc_owned.push_back(p);
+    c->workspace_bytes += bytes;
+    *dev_out = p;
+    return kOk;
+}
+
+int fls_ipc_free(fls_ctx* c, void* dev) {
+    ENTER(c);
+    auto it = std::find(c->ipc_owned.begin(), c->ipc_owned.end(), dev);
+    if (it == c->ipc_owned.end()) return ctx_fail(c, fail(kErrInvalid, "fls_ipc_free: not a buffer of this context"));
+    CTX_CUDA(c, cudaDeviceSynchronize());
+    c->ipc_owned.erase(it);
+    CTX_CUDA(c, cudaFree(dev));
+    return kOk;
+}
+
+int fls_ipc_open(fls_ctx* c, const unsigned char* handle, void** dev_out) {
+    ENTER(c);
+    if (!handle || !dev_out) return ctx_fail(c, fail(kErrInvalid, "fls_ipc_open: null argument"));
+    cudaIpcMemHandle_t h;
+    memcpy(&h, handle, sizeof(h));
+    void* p = nullptr;
+    // the exporting GPU becomes peer-accessible from this one as part of the mapping (NVLink / NVSwitch)
+    CTX_CUDA(c, cudaIpcOpenMemHandle(&p, h, cudaIpcMemLazyEnablePeerAccess));
+    c->ipc_mapped.push_back(p);
+    *dev_out = p;
+    return kOk;
+}
+
+int fls_ipc_close(fls_ctx* c, void* dev) {
+    ENTER(c);
+    auto it = std::find(c->ipc_mapped.begin(), c->ipc_mapped.end(), dev);
+    if (it == c->ipc_mapped.end()) return ctx_fail(c, fail(kErrInvalid, "fls_ipc_close: not a mapping of this context"));
+    CTX_CUDA(c, cudaDeviceSynchronize());
+    c->ipc_mapped.erase(it);
+    CTX_CUDA(c, cudaIpcCloseMemHandle(dev));
+    return kOk;
+}
+
+int fls_flag_signal(fls_ctx* c, uint32_t* flag_dev, uint32_t value, void* stream) {
+    ENTER(c);
+    if (!flag_dev) return ctx_fail(c, fail(kErrInvalid, "fls_flag_signal: null flag"));
+    CTX_TRY(c, flag_signal_launch(flag_dev, value, as_stream(stream)));
+    c->stats.kernel_launches += 1;
+    return kOk;
+}
+
+int fls_flag_wait(fls_ctx* c, const uint32_t* flag_dev, uint32_t target, uint32_t timeout_ms, void* stream) {
+    ENTER(c);
+    if (!flag_dev) return ctx_fail(c, fail(kErrInvalid, "fls_flag_wait: null flag"));
+    if (!c->flag_timeouts) {
+        CTX_CUDA(c, cudaMalloc(reinterpret_cast<void**>(&c->flag_timeouts), 256));
+        CTX_CUDA(c, cudaMemset(c->flag_timeouts, 0, 256));
+    }
+    CTX_TRY(c, flag_wait_launch(flag_dev, target, timeout_ms, c->flag_timeouts, as_stream(stream)));
+    c->stats.kernel_launches += 1;
+    return kOk;
+}
+
+int fls_flag_timeouts(fls_ctx* c, uint32_t* count_out) {
+    ENTER(c);
+    if (!count_out) return ctx_fail(c, fail(kErrInvalid, "fls_flag_timeouts: null output"));
+    *count_out = 0;
+    if (c->flag_timeouts)
+        CTX_CUDA(c, cudaMemcpy(count_out, c->flag_timeouts, sizeof(uint32_t), cudaMemcpyDeviceToHost));
     return kOk;
 }
 

@@ -91,6 +91,11 @@ int lse_reduce_launch(const float2* partial, int n_rows, int n_blocks, float* ls
 int gather_logprob_launch(const __half* x, int ldx, const __half* W, int ldw, int H, const int32_t* ids, int n_ids,
                           const float* lse, int n_rows, int n_vocab, float* out, cudaStream_t s);
 
+// flag = value once everything enqueued on `s` before has completed (system-scope release; `flag` may be a peer mapping)
+int flag_signal_launch(uint32_t* flag, uint32_t value, cudaStream_t s);
+// holds `s` until *flag >= target (wrap-safe); after timeout_ms gives up and increments *timed_out instead
+int flag_wait_launch(const uint32_t* flag, uint32_t target, uint32_t timeout_ms, uint32_t* timed_out, cudaStream_t s);
+
 // ---- attention (attention.cu) ------------------------------------------------------------------
 // One descriptor per query tile; see include/fls_b200.h fls_attn_tile.
 enum AttnMode : int32_t { kAttnPrefix = 0, kAttnPrefixCausal = 1, kAttnSuffix = 2 };

@@ -249,6 +249,32 @@ __global__ void gather_logprob_kernel(const __half* __restrict__ x, int ldx, con
     if (lane == 0) out[wid] = __half2float(__float2half_rn(acc)) - lse[r];
 }
 
+// Hand-off flags between GPUs (model-parallel pipeline across processes).  A flag is a monotonically growing
+// 32-bit counter in the WAITING GPU's memory; the signalling GPU writes it through a peer (IPC) mapping.
+__global__ void flag_signal_kernel(uint32_t* flag, uint32_t value) {
+    // everything this stream did before (kernels, peer copies) is complete and visible before the flag moves
+    __threadfence_system();
+    asm volatile("st.release.sys.global.u32 [%0], %1;\n" ::"l"(flag), "r"(value) : "memory");
+}
+
+__global__ void flag_wait_kernel(const uint32_t* flag, uint32_t target, unsigned long long timeout_ns,
+                                 uint32_t* timed_out) {
+    unsigned long long t0;
+    asm volatile("mov.u64 %0, %%globaltimer;\n" : "=l"(t0));
+    for (;;) {
+        uint32_t v;
+        asm volatile("ld.acquire.sys.global.u32 %0, [%1];\n" : "=r"(v) : "l"(flag) : "memory");
+        if (static_cast<int32_t>(v - target) >= 0) return;      // counters only grow (wrap-safe comparison)
+        unsigned long long t;
+        asm volatile("mov.u64 %0, %%globaltimer;\n" : "=l"(t));
+        if (t - t0 > timeout_ns) {                               // a dead peer must not hang this GPU for ever
+            atomicAdd(timed_out, 1u);
+            return;
+        }
+        __nanosleep(256);
+    }
+}
+
 int grid_for(long long work_items, int threads) {
     long long b = (work_items + threads - 1) / threads;
     const long long cap = 148LL * 16;  // 16 resident CTAs of 256 threads per SM cover latency; loop beyond
@@ -329,6 +355,18 @@ int swiglu_launch(const __half* gate, const __half* up, int ld_in, int n_rows, i
 int lse_reduce_launch(const float2* partial, int n_rows, int n_blocks, float* lse, cudaStream_t s) {
     if (n_rows <= 0) return kOk;
     lse_reduce_kernel<<<(n_rows + 7) / 8, 256, 0, s>>>(partial, n_rows, n_blocks, lse);
+    FLS_CUDA(cudaGetLastError());
+    return kOk;
+}
+
+int flag_signal_launch(uint32_t* flag, uint32_t value, cudaStream_t s) {
+    flag_signal_kernel<<<1, 1, 0, s>>>(flag, value);
+    FLS_CUDA(cudaGetLastError());
+    return kOk;
+}
+
+int flag_wait_launch(const uint32_t* flag, uint32_t target, uint32_t timeout_ms, uint32_t* timed_out, cudaStream_t s) {
+    flag_wait_kernel<<<1, 1, 0, s>>>(flag, target, static_cast<unsigned long long>(timeout_ms) * 1000000ull, timed_out);
     FLS_CUDA(cudaGetLastError());
     return kOk;
 }

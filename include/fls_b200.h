@@ -199,8 +199,35 @@ int fls_lm_head(fls_ctx* ctx, int slot, int layer_idx, const uint16_t* x_dev, in
 /* Model-parallel hand-off (utils.py:163,185,193-195: the reference passes activations between GPU
  * threads through a shared dict and `.to(self.device)`): copy `bytes` from this context's GPU
  * straight into a buffer on GPU `dst_device` over NVLink (cudaMemcpyPeerAsync on `stream`, peer
- * access enabled on first use).  Ordering with the consumer is the caller's (events). */
+ * access enabled on first use).  Ordering with the consumer is the caller's (events).  `dst_device` < 0:
+ * `dst_dev` is a mapping obtained from fls_ipc_open (another process's buffer). */
 int fls_peer_copy(fls_ctx* ctx, void* dst_dev, int dst_device, const void* src_dev, size_t bytes, void* stream);
+
+/* Model-parallel hand-off between PROCESSES (one rank per GPU under torchrun).  The reference's pipeline
+ * stages are threads of one process that share a Python dict, find out that a prompt is ready by polling
+ * `prompt2layer` in sleep(1) loops (utils.py:179-180,189-190) and bound the stages' run-ahead with
+ * `max_activation_in_cpu` (utils.py:178-180).  Across processes the same three things are:
+ *   - the consumer's inbound ring of micro-batch slots, exported once: fls_ipc_alloc (cudaMalloc, zero-filled,
+ *     + cudaIpcGetMemHandle; the 64 handle bytes travel over any host channel) and mapped by its producer:
+ *     fls_ipc_open (peer access over NVLink is enabled by the mapping); rows then go across with
+ *     fls_peer_copy(dst_device = -1);
+ *   - readiness: a 32-bit counter in the WAITING GPU's memory.  fls_flag_signal enqueues, on `stream`, a
+ *     system-scope release store of `value` (everything the stream did before - kernels, peer copies - is
+ *     complete and visible first); fls_flag_wait holds `stream` on the device until *flag >= target.  No host
+ *     polling, no host round trip;
+ *   - back-pressure: the same counters in the other direction (the consumer signals how many items it has
+ *     released; the producer waits before re-using a ring slot).
+ * A wait gives up after `timeout_ms` (a dead peer must not hang the GPU): the stream then continues and
+ * fls_flag_timeouts (a device read, call it after synchronising) reports how many waits have given up since
+ * the context was created - the host must treat any increase as a failed pass. */
+#define FLS_IPC_HANDLE_BYTES 64
+int fls_ipc_alloc(fls_ctx* ctx, size_t bytes, void** dev_out, unsigned char* handle_out /* [64] */);
+int fls_ipc_free(fls_ctx* ctx, void* dev);
+int fls_ipc_open(fls_ctx* ctx, const unsigned char* handle /* [64] */, void** dev_out);
+int fls_ipc_close(fls_ctx* ctx, void* dev);
+int fls_flag_signal(fls_ctx* ctx, uint32_t* flag_dev, uint32_t value, void* stream);
+int fls_flag_wait(fls_ctx* ctx, const uint32_t* flag_dev, uint32_t target, uint32_t timeout_ms, void* stream);
+int fls_flag_timeouts(fls_ctx* ctx, uint32_t* count_out);
 
 /* ---------------------------------------------------------------------------------------------
  * single kernels on caller-supplied device buffers (unit parity tests, profiling). */
