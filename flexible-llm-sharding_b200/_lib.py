@@ -68,6 +68,7 @@ LAYER_EMBED, LAYER_DECODER, LAYER_NORM, LAYER_HEAD = 0, 1, 2, 3
 EPI_STORE, EPI_RESIDUAL, EPI_SWIGLU = 0, 1, 2
 KV_NONE, KV_SAVE, KV_LOAD = 0, 1, 2
 ATTN_TILE_INTS = 8  # sizeof(fls_attn_tile) / 4
+IPC_HANDLE_BYTES = 64  # FLS_IPC_HANDLE_BYTES
 
 _P = C.c_void_p
 _I = C.c_int

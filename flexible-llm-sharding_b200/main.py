@@ -11,7 +11,9 @@ generated tokens appended to every suffix (main.py:86-98).
 
 Multi-GPU: inside one process the reference's threading model is kept (one host thread per visible
 GPU, main.py:67-73).  Under `torchrun` (WORLD_SIZE set) each rank drives its own GPU instead:
-`--data_parallel` partitions the prompts (np.array_split order) and rank 0 gathers the scores.
+`--data_parallel` partitions the prompts (np.array_split order); without it the ranks form the reference's
+default layer pipeline (shard j on rank j mod G) with the activations handed rank to rank over NVLink
+(pipeline_dist.py).  Rank 0 gathers the scores either way.
 """
 from __future__ import annotations
 
@@ -109,16 +111,35 @@ def score_all(args, input_prompts, devices, device_manager=None):
     return run(devices[0], input_prompts)
 
 
+def distributed_device_manager(args):
+    """DeviceManager of one torchrun rank (one process per GPU of one node).  --data_parallel: the process sees
+    only its own GPU, as a one-device run.  Model parallel: `devices` lists every rank's GPU in rank order, so
+    the reference's shard ownership (utils.py:150-153: rank = index of the own device) holds across processes."""
+    import torch.distributed as dist
+    from .utils import DeviceManager
+    local = int(os.environ.get("LOCAL_RANK", dist.get_rank()))
+    if args.data_parallel:
+        return DeviceManager(args, [f"cuda:{local}"])
+    if local != dist.get_rank():
+        raise SystemExit("the model-parallel pipeline spans the GPUs of ONE node (LOCAL_RANK must equal RANK)")
+    dm = DeviceManager(args, [f"cuda:{i}" for i in range(dist.get_world_size())])
+    dm.distributed = True
+    return dm
+
+
 def score_all_distributed(args, input_prompts, device_manager=None):
-    """torchrun mode: rank r scores its np.array_split part on its own GPU; rank 0 gathers."""
-    import torch
+    """torchrun mode.  --data_parallel: rank r scores its np.array_split part on its own GPU.  Otherwise the ranks
+    form the layer pipeline (pipeline_dist.py): every rank gets the whole list (main.py:72-73) and the owner of
+    `lm_head` returns the scores.  Rank 0 gathers either way."""
     import torch.distributed as dist
     rank, world = dist.get_rank(), dist.get_world_size()
     local = int(os.environ.get("LOCAL_RANK", rank))
-    lo, hi = planner.partition_prompts(len(input_prompts), world)[rank]
-    from .utils import DeviceManager
     device = f"cuda:{local}"
-    dm = device_manager if device_manager is not None else DeviceManager(args, [device])
+    dm = device_manager if device_manager is not None else distributed_device_manager(args)
+    if args.data_parallel:
+        lo, hi = planner.partition_prompts(len(input_prompts), world)[rank]
+    else:
+        lo, hi = 0, len(input_prompts)
     mine = run_sharded_llama(device, input_prompts[lo:hi], dm, args)
     gathered = [None] * world if rank == 0 else None
     dist.gather_object(mine, gathered, dst=0)
@@ -141,10 +162,8 @@ def main(argv=None):
     if distributed:
         import torch.distributed as dist
         if not dist.is_initialized():
-            dist.init_process_group("gloo")       # host-side gather only; no data-path collective
-        if not args.data_parallel:
-            raise SystemExit("under torchrun only --data_parallel True is supported; model parallel runs "
-                             "in-process (python main.py with several visible GPUs)")
+            dist.init_process_group("gloo")       # host-side object exchange only; activations travel over NVLink
+        torch.cuda.set_device(int(os.environ.get("LOCAL_RANK", dist.get_rank())))
         is_root = dist.get_rank() == 0
     else:
         is_root = True
@@ -155,7 +174,7 @@ def main(argv=None):
 
     from .utils import DeviceManager
     if distributed:
-        device_manager = DeviceManager(args, [f"cuda:{int(os.environ.get('LOCAL_RANK', 0))}"])
+        device_manager = distributed_device_manager(args)
     else:
         device_manager = DeviceManager(args, devices)          # created once, like main.py:61
     output_scores, tokenizer = [], None

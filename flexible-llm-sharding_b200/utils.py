@@ -71,6 +71,7 @@ class DeviceManager:
         self.prompt2layer = defaultdict(lambda: -1)
         self.suffix_eos = []
         self.handoff = {}          # pipeline hand-off board: packed prompts, peer buffers, events
+        self.distributed = False   # True: `devices` lists one GPU per PROCESS of the torch.distributed group
         self.models = {}           # device -> ShardedLlama, reused across batches / generated tokens
         self.failed = None
 
@@ -408,6 +409,10 @@ class ShardedLlama:
     def run(self, inputs, want_probs=True, answer_ids=None, packed=None, return_device=False):
         shards, num_gpu, rank, dp = self._plan()
         if not dp:
+            if getattr(self.device_manager, "distributed", False):    # one process per GPU (torchrun)
+                from .pipeline_dist import run_model_parallel_distributed
+                return run_model_parallel_distributed(self, inputs, shards, num_gpu, rank, want_probs, answer_ids,
+                                                      return_device)
             from .pipeline import run_model_parallel
             return run_model_parallel(self, inputs, shards, num_gpu, rank, want_probs, answer_ids, return_device)
         t0 = perf_counter()

@@ -66,3 +66,79 @@ def test_generation_loop_with_prefix_kv_cache_on_two_gpus(tiny_gqa, data_paralle
             assert np.array_equal(a, b), (step, notes)
     assert notes == [["save", "save"], ["load", "load"], ["load", "load"]]
     assert not any(dm.models[d]._kv for d in devices)
+
+
+# ------------------------------------------------------------------ one PROCESS per GPU (torchrun form)
+def _dist_worker(rank, world, port, layer_dir, prompts, kw, passes, q):
+    import os
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port), RANK=str(rank), WORLD_SIZE=str(world),
+                      LOCAL_RANK=str(rank), FLS_HANDOFF_TIMEOUT_MS="60000")
+    import torch.distributed as dist
+    torch.cuda.set_device(rank)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    from flexible_llm_sharding_b200 import main as M
+    args = make_args(layer_dir, **kw)
+    dm = M.distributed_device_manager(args)
+    outs, notes = [], []
+    for step, p in enumerate(passes):
+        if "prefix_kv_cache" in kw:
+            args.prefix_kv_cache = "last" if step == len(passes) - 1 else "on"
+        outs.append(M.score_all_distributed(args, copy.deepcopy(p), dm))
+        model = dm.models[f"cuda:{rank}"]
+        notes.append((model.last_timing.get("prefix_kv"), model.last_timing.get("ring_depth"),
+                      model.last_timing.get("p2p_bytes", 0)))
+    q.put((rank, outs if rank == 0 else None, notes))
+    dist.barrier()
+    dist.destroy_process_group()
+
+
+def _run_distributed(world, layer_dir, passes, **kw):
+    import socket
+    import torch.multiprocessing as mp
+    with socket.socket() as s:
+        s.bind(("127.0.0.1", 0))
+        port = s.getsockname()[1]
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    procs = [ctx.Process(target=_dist_worker, args=(r, world, port, layer_dir, None, kw, passes, q))
+             for r in range(world)]
+    for p in procs:
+        p.start()
+    res = dict()
+    for _ in range(world):
+        rank, outs, notes = q.get(timeout=600)
+        res[rank] = (outs, notes)
+    for p in procs:
+        p.join(timeout=120)
+        assert p.exitcode == 0
+    return res
+
+
+@pytest.mark.parametrize("k,max_rows,num_batch", [(1, 16384, 1), (2, 200, 2), (3, 100, 1)])
+def test_cross_process_pipeline_matches_single_gpu(tiny, k, max_rows, num_batch):
+    """torchrun form of the reference's default mode: one process per GPU, shard j on rank j mod G, rows handed
+    rank to rank through IPC-mapped rings with device-side flags.  Bit-identical to one GPU."""
+    _need_two()
+    _, base = run_model(tiny)
+    res = _run_distributed(2, tiny["layer_dir"], [tiny["prompts"]], layer_num_per_shard=k, max_rows=max_rows,
+                           num_batch=num_batch)
+    out = res[0][0][0]
+    assert len(out) == len(base)
+    for a, b in zip(out, base):
+        assert np.array_equal(a, b)
+    assert res[0][1][0][2] > 0 and res[1][1][0][2] >= 0          # rank 0 handed rows on over NVLink
+
+
+def test_cross_process_pipeline_with_prefix_kv_cache(tiny_gqa):
+    _need_two()
+    from tests.test_scoring_gpu import _extend_options
+    p1 = copy.deepcopy(tiny_gqa["prompts"])
+    p2 = _extend_options(p1, ["w7", "w11", "w5"])
+    p3 = _extend_options(p2, ["w9", "w4"])
+    want = [run_model(tiny_gqa, prompts=copy.deepcopy(p))[1] for p in (p1, p2, p3)]
+    res = _run_distributed(2, tiny_gqa["layer_dir"], [p1, p2, p3], layer_num_per_shard=2, max_rows=300,
+                           prefix_kv_cache="on")
+    for step in range(3):
+        for a, b in zip(res[0][0][step], want[step]):
+            assert np.array_equal(a, b), step
+    assert [n[0] for n in res[0][1]] == ["save", "load", "load"] == [n[0] for n in res[1][1]]
