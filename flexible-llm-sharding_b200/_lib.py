@@ -55,7 +55,7 @@ class ModelDesc(C.Structure):
 class Stats(C.Structure):
     _fields_ = [("kernel_launches", C.c_uint64), ("h2d_bytes", C.c_uint64), ("h2d_ms", C.c_double),
                 ("file_bytes_read", C.c_uint64), ("pinned_bytes", C.c_uint64), ("workspace_bytes", C.c_uint64),
-                ("p2p_bytes", C.c_uint64)]
+                ("p2p_bytes", C.c_uint64), ("mapped_bytes", C.c_uint64)]
 
 
 class KernelProfile(C.Structure):
@@ -89,6 +89,7 @@ _SIGNATURES = {
     "fls_preload_layer_file": (_I, [C.c_char_p]),
     "fls_set_host_cache_limit": (_I, [C.c_size_t]),
     "fls_trim_host_cache": (_I, [C.c_size_t]),
+    "fls_set_host_image_mode": (_I, [_I]),
     "fls_peer_copy": (_I, [_P, _P, _I, _P, C.c_size_t, _P]),
     "fls_ipc_alloc": (_I, [_P, C.c_size_t, C.POINTER(_P), _P]),
     "fls_ipc_free": (_I, [_P, _P]),

@@ -674,6 +674,12 @@ int fls_set_host_cache_limit(size_t max_bytes) {
     return kOk;
 }
 
+int fls_set_host_image_mode(int mode) {
+    if (mode < 0 || mode > 2) return fail(kErrInvalid, "fls_set_host_image_mode: mode %d (0 auto, 1 copy, 2 map)", mode);
+    set_host_image_mode(mode);
+    return kOk;
+}
+
 int fls_trim_host_cache(size_t keep_bytes) {
     trim_host_cache(keep_bytes);
     return kOk;
@@ -1062,6 +1068,7 @@ int fls_get_stats(fls_ctx* c, fls_stats* out) {
     for (auto& t : c->copy_ring) harvest_copy_timing(c, t, true);
     c->stats.file_bytes_read = host_cache_file_bytes();
     c->stats.pinned_bytes = host_cache_pinned_bytes();
+    c->stats.mapped_bytes = host_cache_mapped_bytes();
     c->stats.workspace_bytes = c->workspace_bytes;
     *out = c->stats;
     return kOk;

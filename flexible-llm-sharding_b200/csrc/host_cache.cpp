@@ -8,6 +8,7 @@
 #include "host_cache.h"
 
 #include <fcntl.h>
+#include <sys/mman.h>
 #include <sys/stat.h>
 #include <unistd.h>
 #include <cerrno>
@@ -118,7 +119,80 @@ std::unordered_map<std::string, CacheEntry> g_cache;
 std::atomic<uint64_t> g_clock{0};
 std::atomic<uint64_t> g_file_bytes{0};
 std::atomic<uint64_t> g_pinned_bytes{0};
+std::atomic<uint64_t> g_mapped_bytes{0};
 std::atomic<size_t> g_limit{0};
+std::atomic<int> g_image_mode{-1};  // -1: not set yet -> FLS_WEIGHT_IMAGE (auto | copy | map)
+
+int image_mode() {
+    int m = g_image_mode.load();
+    if (m < 0) {
+        const char* e = getenv("FLS_WEIGHT_IMAGE");
+        m = !e ? 0 : (strcmp(e, "copy") == 0 ? 1 : (strcmp(e, "map") == 0 ? 2 : 0));
+        g_image_mode.store(m);
+    }
+    return m;
+}
+
+// Touch every page of [p, p+n) from a few threads so that the file is read (or the tmpfs pages are found) in
+// parallel before cudaHostRegister walks the range on one thread.
+void prefault(const char* p, size_t n) {
+    const size_t chunk = size_t(64) << 20;
+    const size_t n_chunks = (n + chunk - 1) / chunk;
+    const unsigned hw = std::max(1u, std::thread::hardware_concurrency());
+    const size_t n_threads = std::min<size_t>(std::min<size_t>(8, hw), std::max<size_t>(1, n_chunks));
+    std::atomic<size_t> next{0};
+    std::atomic<unsigned> sink{0};
+    auto work = [&]() {
+        unsigned acc = 0;
+        for (;;) {
+            const size_t c = next.fetch_add(1);
+            if (c >= n_chunks) break;
+            const size_t lo = c * chunk, hi = std::min(n, lo + chunk);
+            for (size_t o = lo; o < hi; o += 4096) acc += static_cast<unsigned char>(p[o]);
+        }
+        sink.fetch_add(acc);
+    };
+    std::vector<std::thread> th;
+    for (size_t i = 1; i < n_threads; ++i) th.emplace_back(work);
+    work();
+    for (auto& t : th) t.join();
+}
+
+// Tries to make `img` the mapped form of its file.  Returns true on success; false (with CUDA's error state
+// cleared) when the mapping or the registration is refused - the caller then falls back to the copied form.
+bool try_map_image(HostLayerImage* img, size_t data_start, size_t file_size, std::string* why) {
+    const int fd = open(img->path.c_str(), O_RDONLY);
+    if (fd < 0) {
+        *why = std::string("open: ") + strerror(errno);
+        return false;
+    }
+    const size_t page = static_cast<size_t>(sysconf(_SC_PAGESIZE));
+    const size_t len = (file_size + page - 1) / page * page;
+    void* m = mmap(nullptr, len, PROT_READ, MAP_SHARED, fd, 0);
+    close(fd);
+    if (m == MAP_FAILED) {
+        *why = std::string("mmap: ") + strerror(errno);
+        return false;
+    }
+    madvise(m, len, MADV_WILLNEED);
+    prefault(static_cast<const char*>(m), file_size);
+    cudaError_t e = cudaHostRegister(m, len, cudaHostRegisterPortable | cudaHostRegisterReadOnly);
+    if (e != cudaSuccess) {
+        cudaGetLastError();
+        *why = std::string("cudaHostRegister: ") + cudaGetErrorString(e);
+        munmap(m, len);
+        return false;
+    }
+    img->map_base = m;
+    img->map_len = len;
+    img->pinned = static_cast<char*>(m) + data_start;
+    img->pinned_bytes = len;
+    for (auto& t : img->tensors) t.host_off = t.begin;
+    g_pinned_bytes.fetch_add(len);
+    g_mapped_bytes.fetch_add(len);
+    g_file_bytes.fetch_add(file_size - data_start);
+    return true;
+}
 
 int parallel_pread(int fd, char* dst, size_t off, size_t n) {
     const size_t chunk = size_t(32) << 20;
@@ -168,7 +242,12 @@ void convert_to_f16(const char* src, const std::string& dtype, size_t n, __half*
 }  // namespace
 
 HostLayerImage::~HostLayerImage() {
-    if (pinned) {
+    if (map_base) {
+        cudaHostUnregister(map_base);
+        munmap(map_base, map_len);
+        g_pinned_bytes.fetch_sub(pinned_bytes);
+        g_mapped_bytes.fetch_sub(pinned_bytes);
+    } else if (pinned) {
         cudaFreeHost(pinned);
         g_pinned_bytes.fetch_sub(pinned_bytes);
     }
@@ -267,13 +346,35 @@ int acquire_host_image(const std::string& path_in, std::shared_ptr<HostLayerImag
     size_t data_start = 0, file_size = 0;
     FLS_TRY(parse_safetensors_header(path, &img->tensors, &data_start, &file_size));
     size_t total = 0;
+    bool all_f16 = true;
     for (auto& t : img->tensors) {
         if (t.dtype != "F16" && t.dtype != "BF16" && t.dtype != "F32")
             return fail(kErrInvalid, "%s: tensor %s has dtype %s; only F16/BF16/F32 weights are supported "
                         "(int8 needs fp16 statistics, as in the reference)", path.c_str(), t.name.c_str(),
                         t.dtype.c_str());
+        all_f16 = all_f16 && t.dtype == "F16" && t.end - t.begin == t.numel * 2 && (data_start + t.begin) % 2 == 0;
         t.host_off = total;
         total += (t.numel * 2 + 255) & ~size_t(255);
+    }
+    const int mode = image_mode();
+    bool mapped = false;
+    if (mode != 1) {
+        std::string why = "the file holds BF16/F32 tensors, which are converted on load";
+        mapped = all_f16 && try_map_image(img.get(), data_start, file_size, &why);
+        if (!mapped && mode == 2)
+            return fail(kErrIo, "%s: cannot lock the file's pages in place (%s)", path.c_str(), why.c_str());
+    }
+    if (mapped) {
+        std::lock_guard<std::mutex> lk(g_mu);
+        auto& slot = g_cache[path];
+        if (!slot.img) slot.img = img;
+        slot.last_use = ++g_clock;
+        *out = slot.img;
+    }
+    if (mapped) {
+        img.reset();
+        if (const size_t lim = g_limit.load()) trim_host_cache(lim);
+        return kOk;
     }
     cudaError_t e = cudaHostAlloc(reinterpret_cast<void**>(&img->pinned), std::max<size_t>(total, 256),
                                   cudaHostAllocPortable);
@@ -307,6 +408,9 @@ int acquire_host_image(const std::string& path_in, std::shared_ptr<HostLayerImag
         }
         g_file_bytes.fetch_add(nbytes);
     }
+    // the pinned copy is the resident one: let the kernel drop the file's pages instead of keeping the model in RAM
+    // twice (reference utils.py:72-73,126-127 reads the whole file into a bytes object first)
+    posix_fadvise(fd, 0, 0, POSIX_FADV_DONTNEED);
     close(fd);
     if (rc != kOk) return rc;
 
@@ -345,5 +449,7 @@ size_t trim_host_cache(size_t keep_bytes) {
 
 uint64_t host_cache_file_bytes() { return g_file_bytes.load(); }
 uint64_t host_cache_pinned_bytes() { return g_pinned_bytes.load(); }
+uint64_t host_cache_mapped_bytes() { return g_mapped_bytes.load(); }
+void set_host_image_mode(int mode) { g_image_mode.store(mode < 0 || mode > 2 ? 0 : mode); }
 
 }  // namespace fls

@@ -16,12 +16,20 @@ struct TensorEntry {
     size_t host_off = 0;  // offset of the fp16 image of this tensor inside HostLayerImage::pinned
 };
 
-// One layer file resident in page-locked host memory as fp16 tensors (256-byte aligned each).
+// One layer file resident in page-locked host memory as fp16 tensors.  Two forms:
+//   mapped  the file's own pages (page cache / tmpfs), mmap'ed read-only and page-locked in place with
+//           cudaHostRegister: no second copy in RAM, and every process that maps the file pins the SAME physical
+//           pages - one host copy of a layer serves every rank of the box (reference utils.py:35-41,67-75 does this
+//           for the threads of one process).  Needs all tensors stored as F16.
+//   copied  a cudaHostAlloc'ed buffer the tensors are read (and, for BF16/F32 files, converted) into, each
+//           256-byte aligned; the file's pages are then dropped from the page cache.
 struct HostLayerImage {
     std::string path;
     std::vector<TensorEntry> tensors;
-    char* pinned = nullptr;
+    char* pinned = nullptr;   // base the tensors' host_off are relative to
     size_t pinned_bytes = 0;
+    void* map_base = nullptr;  // mapped form: the mmap'ed (and registered) range
+    size_t map_len = 0;
     ~HostLayerImage();
     const TensorEntry* find(const std::string& suffix) const {
         for (auto& t : tensors)
@@ -42,5 +50,8 @@ size_t trim_host_cache(size_t keep_bytes);
 void set_host_cache_limit(size_t max_bytes);
 uint64_t host_cache_file_bytes();
 uint64_t host_cache_pinned_bytes();
+uint64_t host_cache_mapped_bytes();  // part of pinned_bytes that is file pages locked in place (no copy)
+// 0 = auto (map when the file allows it and the driver accepts, else copy), 1 = always copy, 2 = map or fail
+void set_host_image_mode(int mode);
 
 }  // namespace fls

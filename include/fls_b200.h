@@ -90,6 +90,8 @@ typedef struct fls_stats {
     uint64_t pinned_bytes;    /* pinned host bytes currently held (process-wide) */
     uint64_t workspace_bytes; /* HBM held by this context (slots + workspace) */
     uint64_t p2p_bytes;       /* activation bytes handed to other GPUs (fls_peer_copy) */
+    uint64_t mapped_bytes;    /* part of pinned_bytes that is file pages locked in place, shared with every
+                                 other process that maps the same files (process-wide) */
 } fls_stats;
 
 /* ---------------------------------------------------------------------------------------------
@@ -151,6 +153,15 @@ int fls_preload_layer_file(const char* path);
 int fls_set_host_cache_limit(size_t max_bytes);
 /* Drop pinned images no context needs any more (process-wide cache). */
 int fls_trim_host_cache(size_t keep_bytes);
+/* How a layer file becomes a page-locked host image (reference utils.py:72-73,126-127: `f.read()` into a bytes
+ * object, then safetensors parses a second copy).  0 (default, or FLS_WEIGHT_IMAGE=auto): files whose tensors are
+ * all stored as F16 are mmap'ed read-only and their own pages (page cache / tmpfs) are locked in place with
+ * cudaHostRegister - no second copy in RAM, and all processes of the box that map the file share one physical
+ * copy (DeviceManager's read-once layer, utils.py:35-41, across processes); BF16/F32 files, or a driver that
+ * refuses the registration, take the copying path (parallel pread into cudaHostAlloc memory, converted to fp16,
+ * the file's pages then dropped from the page cache).  1 (FLS_WEIGHT_IMAGE=copy): always copy.  2 (=map): map
+ * or fail with FLS_ERR_IO. */
+int fls_set_host_image_mode(int mode);
 
 /* ---------------------------------------------------------------------------------------------
  * layer compute on a resident shard.  `x_dev` etc. are fp16 [rows, hidden]. */

@@ -391,3 +391,38 @@ def test_unexpected_tensors_and_max_rows_env(tiny, tmp_path, monkeypatch):
     args = make_args(tiny["layer_dir"])
     model = ShardedLlama(args, DeviceManager(args, ["cuda:0"]), device="cuda:0")
     assert model.max_rows == 96
+
+
+def test_layer_files_are_locked_in_place_not_copied(tiny):
+    """SURVEY.md 8f-2 / DP read-once sharing: F16 layer files are mmap'ed and their own pages page-locked
+    (cudaHostRegister), so a model costs its size in host RAM once per BOX, not once per process plus the page
+    cache.  Same scores as the copying path (which BF16/F32 files still take)."""
+    import gc
+    from flexible_llm_sharding_b200 import _lib
+    from flexible_llm_sharding_b200.utils import DeviceManager, ShardedLlama
+    lib = _lib.load()
+    gc.collect()
+    lib.fls_trim_host_cache(0)
+    outs = {}
+    try:
+        for mode, name in ((2, "map"), (1, "copy")):
+            assert lib.fls_set_host_image_mode(mode) == 0
+            args = make_args(tiny["layer_dir"])
+            model = ShardedLlama(args, DeviceManager(args, ["cuda:0"]), device="cuda:0")
+            before = model.ctx.stats()
+            outs[name] = model(copy.deepcopy(tiny["prompts"]))
+            st = model.ctx.stats()
+            grew = st.mapped_bytes - before.mapped_bytes
+            if name == "map":
+                assert grew >= sum(model._layer_bytes) * 0.9      # every layer file, locked where it lies
+                assert st.pinned_bytes - before.pinned_bytes == grew
+            else:
+                assert grew == 0 and st.pinned_bytes > before.pinned_bytes
+            model.ctx.close()
+            del model
+            gc.collect()
+            lib.fls_trim_host_cache(0)
+    finally:
+        lib.fls_set_host_image_mode(0)
+    for a, b in zip(outs["map"], outs["copy"]):
+        assert np.array_equal(a, b)
