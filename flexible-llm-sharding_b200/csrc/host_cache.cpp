@@ -161,25 +161,29 @@ void prefault(const char* p, size_t n) {
 // Tries to make `img` the mapped form of its file.  Returns true on success; false (with CUDA's error state
 // cleared) when the mapping or the registration is refused - the caller then falls back to the copied form.
 bool try_map_image(HostLayerImage* img, size_t data_start, size_t file_size, std::string* why) {
-    const int fd = open(img->path.c_str(), O_RDONLY);
+    // What this driver accepts (tools/hostreg_probe.cu, B200 box, driver 580): the mapping must be WRITABLE even for
+    // a read-only registration, and file-backed MAP_SHARED pages are accepted on tmpfs (/dev/shm) only - on ext4
+    // every MAP_SHARED variant is refused and MAP_PRIVATE works only by copying each page (no sharing, no saving).
+    // So: open read-write, map shared, never write.  Anything else falls back to the copying path.
+    const int fd = open(img->path.c_str(), O_RDWR);
     if (fd < 0) {
-        *why = std::string("open: ") + strerror(errno);
+        *why = std::string("open for mapping: ") + strerror(errno);
         return false;
     }
     const size_t page = static_cast<size_t>(sysconf(_SC_PAGESIZE));
     const size_t len = (file_size + page - 1) / page * page;
-    void* m = mmap(nullptr, len, PROT_READ, MAP_SHARED, fd, 0);
+    void* m = mmap(nullptr, len, PROT_READ | PROT_WRITE, MAP_SHARED, fd, 0);
     close(fd);
     if (m == MAP_FAILED) {
         *why = std::string("mmap: ") + strerror(errno);
         return false;
     }
-    madvise(m, len, MADV_WILLNEED);
     prefault(static_cast<const char*>(m), file_size);
     cudaError_t e = cudaHostRegister(m, len, cudaHostRegisterPortable | cudaHostRegisterReadOnly);
     if (e != cudaSuccess) {
         cudaGetLastError();
-        *why = std::string("cudaHostRegister: ") + cudaGetErrorString(e);
+        *why = std::string("cudaHostRegister: ") + cudaGetErrorString(e) +
+               " (file pages can be locked in place on tmpfs, e.g. /dev/shm, only)";
         munmap(m, len);
         return false;
     }

@@ -17,7 +17,7 @@ struct TensorEntry {
 };
 
 // One layer file resident in page-locked host memory as fp16 tensors.  Two forms:
-//   mapped  the file's own pages (page cache / tmpfs), mmap'ed read-only and page-locked in place with
+//   mapped  the file's own pages (tmpfs: the driver locks file pages of no other file system), mmap'ed and page-locked in place with
 //           cudaHostRegister: no second copy in RAM, and every process that maps the file pins the SAME physical
 //           pages - one host copy of a layer serves every rank of the box (reference utils.py:35-41,67-75 does this
 //           for the threads of one process).  Needs all tensors stored as F16.

@@ -163,7 +163,8 @@ def main(argv=None):
         import torch.distributed as dist
         if not dist.is_initialized():
             dist.init_process_group("gloo")       # host-side object exchange only; activations travel over NVLink
-        torch.cuda.set_device(int(os.environ.get("LOCAL_RANK", dist.get_rank())))
+        if torch.cuda.is_available():
+            torch.cuda.set_device(int(os.environ.get("LOCAL_RANK", dist.get_rank())))
         is_root = dist.get_rank() == 0
     else:
         is_root = True

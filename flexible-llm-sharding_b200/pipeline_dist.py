@@ -192,6 +192,18 @@ class IpcRing:
     next_ready = property(lambda self: C.c_void_p(self.next_flags))
     prev_free = property(lambda self: C.c_void_p(self.prev_flags + 4 * FREE_FLAG_WORD))
 
+    def close(self):
+        """Collective.  An exported buffer may be freed only after every process that mapped it has let go, so:
+        drop the mappings, meet, then free."""
+        for p in {self.next_slots, self.next_flags, self.prev_flags} - {None}:
+            self.ctx.call("fls_ipc_close", C.c_void_p(p))
+        self.next_slots = self.next_flags = self.prev_flags = None
+        self.coll.barrier()
+        for p in (self.slots, self.flags):
+            if p is not None:
+                self.ctx.call("fls_ipc_free", C.c_void_p(p))
+        self.slots = self.flags = None
+
     def check_timeouts(self):
         n = C.c_uint32()
         self.ctx.call("fls_flag_timeouts", C.byref(n))

@@ -178,18 +178,48 @@ def write_hf_bin_checkpoint(out_dir: str, shape: LlamaShape, seed=0, init_std=0.
         json.dump({"metadata": {}, "weight_map": weight_map}, f)
 
 
+def save_safetensors_raw(path: str, tensors: dict[str, torch.Tensor]) -> None:
+    """Writes the safetensors container (8-byte little-endian header length, JSON header padded with spaces to a
+    multiple of 8, raw tensor bytes in header order; the layout prepare_weights.py's `save_file` produces) straight
+    from the tensors' memory - no intermediate `bytes` copy of the whole file, which is what makes writing the
+    138 GB of a 70B-sized model take tens of seconds instead of minutes.  fp16 CPU tensors only."""
+    names = sorted(tensors)                    # one dtype -> safetensors orders by name
+    header, off = {}, 0
+    for n in names:
+        t = tensors[n]
+        assert t.dtype == torch.float16 and t.device.type == "cpu" and t.is_contiguous(), n
+        nbytes = t.numel() * 2
+        header[n] = {"dtype": "F16", "shape": list(t.shape), "data_offsets": [off, off + nbytes]}
+        off += nbytes
+    blob = json.dumps(header, separators=(",", ":")).encode()
+    blob += b" " * (-len(blob) % 8)
+    with open(path, "wb", buffering=0) as f:
+        f.write(len(blob).to_bytes(8, "little"))
+        f.write(blob)
+        for n in names:
+            f.write(memoryview(tensors[n].numpy()).cast("B"))
+
+
 def write_layer_files(out_dir: str, shape: LlamaShape, seed=0, init_std=0.02, device="cpu",
-                      alias_decoder_layers: int = 0) -> None:
+                      alias_decoder_layers: int = 0, only_layers=None, fast: bool = False) -> None:
     """prepare_weights.py's output layout written directly (reference prepare_weights.py:40-43).
 
     `alias_decoder_layers=n>0` writes only n distinct decoder layers and symlinks the rest to them
     (70B-sized runs on a host whose RAM cannot hold 138 GB of pinned weights plus the files); the
-    caller must say so in its results."""
+    caller must say so in its results.  `only_layers` (a set of layer names) restricts the call to those files, so
+    that several processes can write one model together; `fast` uses `save_safetensors_raw` with a few writer
+    threads (benchmark-sized models) instead of safetensors' own `save_file`."""
+    from concurrent.futures import ThreadPoolExecutor
+
     from safetensors.torch import save_file
 
     write_config(out_dir, shape)
     write_tokenizer(out_dir, shape.vocab_size)
+    pool = ThreadPoolExecutor(max_workers=4) if fast else None
+    pending = []
     for ln in shape.layer_names():
+        if only_layers is not None and ln not in only_layers:
+            continue
         dst = os.path.join(out_dir, f"{ln}.safetensors")
         if alias_decoder_layers and ln.startswith("model.layers."):
             i = int(ln.rsplit(".", 1)[1])
@@ -203,7 +233,17 @@ def write_layer_files(out_dir: str, shape: LlamaShape, seed=0, init_std=0.02, de
                 os.symlink(f"model.layers.{i % alias_decoder_layers}.safetensors", dst)
                 continue
         sd = make_layer_state_dict(shape, ln, seed, init_std, device)
-        save_file({k: v.cpu().contiguous() for k, v in sd.items()}, dst)
+        host = {k: v.cpu().contiguous() for k, v in sd.items()}
+        if pool is None:
+            save_file(host, dst)
+        else:
+            pending.append(pool.submit(save_safetensors_raw, dst, host))
+            while len(pending) > 4:                      # bound the host copies in flight
+                pending.pop(0).result()
+    for f in pending:
+        f.result()
+    if pool is not None:
+        pool.shutdown()
 
 
 # --------------------------------------------------------------------------------------

@@ -41,6 +41,21 @@ def load_tokenizer(model_path):
         return AutoTokenizer.from_pretrained(model_path)
 
 
+def _on_tmpfs(path) -> bool:
+    """True when `path` lies on a RAM file system (its F16 layer files are then page-locked in place)."""
+    try:
+        real = os.path.realpath(path)
+        best, kind = "", ""
+        with open("/proc/mounts") as f:
+            for line in f:
+                _, mnt, fstype = line.split()[:3]
+                if (real == mnt or real.startswith(mnt.rstrip("/") + "/")) and len(mnt) > len(best):
+                    best, kind = mnt, fstype
+        return kind in ("tmpfs", "ramfs")
+    except (OSError, ValueError):
+        return False
+
+
 def clean_memory():
     """Kept for API compatibility (reference utils.py:18-21).  Nothing to do: weight slots and
     workspace are allocated once per context instead of per shard."""
@@ -189,10 +204,25 @@ class ShardedLlama:
             return os.environ.get("RANK", str(rank))
         return str(rank) if self.args.data_parallel else ""
 
+    def close(self):
+        """Release the GPU side of this model now (HBM slots, workspace, streams) instead of at garbage collection.
+        In the cross-process pipeline this is a collective: every rank must call it (the hand-off rings are unmapped
+        by all ranks before their owners free them)."""
+        ring = getattr(self, "_ipc_ring", None)
+        if ring is not None:
+            torch.cuda.synchronize(self.torch_device)
+            ring.close()
+            self._ipc_ring = None
+        self._kv.clear()
+        self._keepalive = None
+        self.ctx.close()
+
     def _set_pinned_limit(self, limit):
         """Bound the pinned host copies of the layer files (the reference's `max_layer_num`, utils.py:31, in bytes).
         "auto": unlimited when the whole model fits 60 % of this process's share of the available host RAM,
         otherwise that share - evicted layers are re-read from their files on the next pass."""
+        if limit == "auto" and _on_tmpfs(self.args.model_path) and os.environ.get("FLS_WEIGHT_IMAGE", "auto") != "copy":
+            limit = 0              # the files' own pages get locked in place: holding them all costs no extra RAM
         if limit == "auto":
             limit = 0
             try:

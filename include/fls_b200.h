@@ -155,10 +155,10 @@ int fls_set_host_cache_limit(size_t max_bytes);
 int fls_trim_host_cache(size_t keep_bytes);
 /* How a layer file becomes a page-locked host image (reference utils.py:72-73,126-127: `f.read()` into a bytes
  * object, then safetensors parses a second copy).  0 (default, or FLS_WEIGHT_IMAGE=auto): files whose tensors are
- * all stored as F16 are mmap'ed read-only and their own pages (page cache / tmpfs) are locked in place with
- * cudaHostRegister - no second copy in RAM, and all processes of the box that map the file share one physical
- * copy (DeviceManager's read-once layer, utils.py:35-41, across processes); BF16/F32 files, or a driver that
- * refuses the registration, take the copying path (parallel pread into cudaHostAlloc memory, converted to fp16,
+ * all stored as F16 and that lie on tmpfs (/dev/shm; writable by the caller) are mmap'ed and their own pages are
+ * locked in place with cudaHostRegister - no second copy in RAM, and all processes of the box that map the file
+ * share one physical copy (DeviceManager's read-once layer, utils.py:35-41, across processes); BF16/F32 files,
+ * files on a disk file system (the driver refuses to lock their pages) take the copying path (parallel pread into cudaHostAlloc memory, converted to fp16,
  * the file's pages then dropped from the page cache).  1 (FLS_WEIGHT_IMAGE=copy): always copy.  2 (=map): map
  * or fail with FLS_ERR_IO. */
 int fls_set_host_image_mode(int mode);

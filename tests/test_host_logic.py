@@ -301,3 +301,17 @@ def test_disk_tier_file_tag_is_the_global_rank_under_torchrun(monkeypatch):
     monkeypatch.setenv("WORLD_SIZE", "4")
     monkeypatch.setenv("RANK", "2")
     assert ShardedLlama._rank_tag(dp, 0) == "2" and ShardedLlama._rank_tag(mp, 0) == "2"
+
+
+def test_raw_safetensors_writer_is_byte_identical_to_save_file(tmp_path):
+    """The benchmark-sized models are written with a streaming writer; same bytes as safetensors' own save_file
+    (the call prepare_weights.py makes, reference prepare_weights.py:40-43)."""
+    from flexible_llm_sharding_b200 import synthetic
+    shape = synthetic.LlamaShape.named("tiny", num_hidden_layers=2)
+    a, b = tmp_path / "a", tmp_path / "b"
+    synthetic.write_layer_files(str(a), shape)
+    synthetic.write_layer_files(str(b), shape, fast=True, only_layers={"model.layers.1", "lm_head"})
+    assert sorted(f for f in os.listdir(b) if f.endswith(".safetensors")) == ["lm_head.safetensors",
+                                                                             "model.layers.1.safetensors"]
+    for fn in ("lm_head.safetensors", "model.layers.1.safetensors"):
+        assert (a / fn).read_bytes() == (b / fn).read_bytes()

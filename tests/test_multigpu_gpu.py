@@ -88,6 +88,8 @@ def _dist_worker(rank, world, port, layer_dir, prompts, kw, passes, q):
         notes.append((model.last_timing.get("prefix_kv"), model.last_timing.get("ring_depth"),
                       model.last_timing.get("p2p_bytes", 0)))
     q.put((rank, outs if rank == 0 else None, notes))
+    for m in dm.models.values():
+        m.close()                      # collective: rings are unmapped everywhere before their owners free them
     dist.barrier()
     dist.destroy_process_group()
 

@@ -400,14 +400,25 @@ def test_layer_files_are_locked_in_place_not_copied(tiny):
     import gc
     from flexible_llm_sharding_b200 import _lib
     from flexible_llm_sharding_b200.utils import DeviceManager, ShardedLlama
+    import shutil
+    import tempfile
+    if not os.path.isdir("/dev/shm"):
+        pytest.skip("no tmpfs to put the layer files on")
     lib = _lib.load()
     gc.collect()
     lib.fls_trim_host_cache(0)
     outs = {}
+    shm_dir = os.path.join(tempfile.mkdtemp(prefix="fls_test_map_", dir="/dev/shm"), "layers")
+    shutil.copytree(tiny["layer_dir"], shm_dir)
     try:
+        # files on a disk file system cannot be locked in place: "map or fail" must say so, "auto" must copy
+        assert lib.fls_set_host_image_mode(2) == 0
+        if os.stat(tiny["layer_dir"]).st_dev != os.stat(shm_dir).st_dev:
+            rc = lib.fls_preload_layer_file(os.path.join(tiny["layer_dir"], "model.norm.safetensors").encode())
+            assert rc == -3 and b"tmpfs" in lib.fls_last_error(None)
         for mode, name in ((2, "map"), (1, "copy")):
             assert lib.fls_set_host_image_mode(mode) == 0
-            args = make_args(tiny["layer_dir"])
+            args = make_args(shm_dir)
             model = ShardedLlama(args, DeviceManager(args, ["cuda:0"]), device="cuda:0")
             before = model.ctx.stats()
             outs[name] = model(copy.deepcopy(tiny["prompts"]))
@@ -424,5 +435,7 @@ def test_layer_files_are_locked_in_place_not_copied(tiny):
             lib.fls_trim_host_cache(0)
     finally:
         lib.fls_set_host_image_mode(0)
-    for a, b in zip(outs["map"], outs["copy"]):
-        assert np.array_equal(a, b)
+        shutil.rmtree(os.path.dirname(shm_dir), ignore_errors=True)
+    _, base = run_model(tiny)                                  # auto mode on the disk copy of the same files
+    for a, b, c in zip(outs["map"], outs["copy"], base):
+        assert np.array_equal(a, b) and np.array_equal(a, c)
