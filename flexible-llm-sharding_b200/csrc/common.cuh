@@ -62,6 +62,7 @@ struct GemmArgs {
     int up_off;
     int group_m;      // m-blocks per raster group (0 = default 16)
     int cache_hints;  // cta_group 2 only: 0 none, 1 A evict-first / B evict-last, 2 the reverse
+    int direct_store;  // 0 (default): epilogue stages tiles in smem and writes them with TMA; 1: per-thread 16-byte stores
     // kEpiStoreRope: rotary position of every row and the fp16 cos/sin tables [n_pos, 128]
     const int32_t* row_pos;
     const __half* cos_tab;

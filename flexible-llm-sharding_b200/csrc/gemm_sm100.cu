@@ -16,13 +16,19 @@
 //               M=128 per CTA, N=256, K=16, fp32 accumulators in TMEM, two accumulator stages
 //               (2 x 256 columns = all 512); tcgen05.commit (multicast to the peer) frees the smem stage
 //   warp 2      TMEM allocator
-//   warps 4-7   epilogue: tcgen05.ld (32 lanes x 32 columns per warp) -> registers -> fused op ->
-//               global.  Overlaps the next tile's main loop through the second accumulator stage.
+//   warps 4-7   epilogue: tcgen05.ld (32 lanes x 32 columns per warp) -> registers -> fused op -> a 32 x 64
+//               sub-tile in shared memory (128-byte swizzle) -> TMA store (full 128-byte lines; rows / columns
+//               beyond M / N are clipped by the tensor map).  The residual operand comes in the same way (TMA load
+//               into the staging sub-tile, prefetched a chunk ahead).  Overlaps the next tile's main loop through
+//               the second accumulator stage.  TS = false keeps the older epilogue (every thread stores 16-byte
+//               pieces of its own row straight to global) as option "gemm_tma_store" = 0 / test comparator.
 // Rounding in the epilogues follows the reference's eager fp16 order (see each epilogue).
 #include <cuda.h>
 
 #include <algorithm>
+#include <functional>
 #include <mutex>
+#include <unordered_map>
 
 #include "common.cuh"
 #include "ptx.cuh"
@@ -37,7 +43,10 @@ constexpr int BLOCK_K = 64;   // 64 fp16 = 128 B = one swizzle row
 constexpr int UMMA_K = 16;
 constexpr int ACC_STAGES = 2;
 constexpr int A_BYTES = BLOCK_M * BLOCK_K * 2;  // 16 KiB
-constexpr int SMEM_BARRIER_BYTES = 256;
+constexpr int SMEM_BARRIER_BYTES = 512;
+constexpr int EPI_CHUNK_COLS = 64;                      // one swizzle row of fp16
+constexpr int EPI_BUF_BYTES = 32 * EPI_CHUNK_COLS * 2;  // 32 rows x 128 B per epilogue warp
+constexpr int EPI_STAGE_BYTES = 4 * 2 * EPI_BUF_BYTES;  // 4 warps x 2 buffers = 32 KiB
 constexpr int MAX_STAGES = 8;
 
 // CG = tcgen05 cta_group.  CG 1: one CTA per 128x256 tile, B tile 256 rows, 4 stages of 48 KiB.
@@ -50,7 +59,7 @@ struct Cfg {
     static constexpr int B_ROWS = BLOCK_N / CG;
     static constexpr int B_BYTES = B_ROWS * BLOCK_K * 2;
     static constexpr int STAGE_BYTES = A_BYTES + B_BYTES;
-    static constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + SMEM_BARRIER_BYTES + 1024;  // + alignment slack
+    static constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + EPI_STAGE_BYTES + SMEM_BARRIER_BYTES + 1024;  // + alignment slack
 };
 constexpr int NUM_THREADS = 256;
 constexpr int EPI_WARP0 = 4;
@@ -95,20 +104,28 @@ __device__ __forceinline__ uint32_t pack_h2(__half a, __half b) {
     return *reinterpret_cast<uint32_t*>(&h);
 }
 
-template <int EPI, int CG>
+// 16-byte piece j (0..7) of row r of a 32 x 64 fp16 sub-tile laid out with the 128-byte swizzle TMA expects
+__device__ __forceinline__ uint4* stage_ptr(uint8_t* buf, int r, int j) {
+    return reinterpret_cast<uint4*>(buf + r * 128 + ((j ^ (r & 7)) << 4));
+}
+
+template <int EPI, int CG, bool TS>
 __global__ void __launch_bounds__(NUM_THREADS, 1)
 gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CUtensorMap tmap_b,
+                    const __grid_constant__ CUtensorMap tmap_c, const __grid_constant__ CUtensorMap tmap_r,
                     const KParams p) {
     constexpr int STAGES = Cfg<CG>::STAGES;
     constexpr int B_BYTES = Cfg<CG>::B_BYTES;
     constexpr int STAGE_BYTES = Cfg<CG>::STAGE_BYTES;
     extern __shared__ uint8_t smem_raw[];
     uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
-    uint64_t* full_bar = reinterpret_cast<uint64_t*>(smem + STAGES * STAGE_BYTES);
+    uint8_t* epi_stage = smem + STAGES * STAGE_BYTES;  // 1024-byte aligned: stages are multiples of 16 KiB
+    uint64_t* full_bar = reinterpret_cast<uint64_t*>(epi_stage + EPI_STAGE_BYTES);
     uint64_t* empty_bar = full_bar + MAX_STAGES;
     uint64_t* tmem_full_bar = empty_bar + MAX_STAGES;
     uint64_t* tmem_empty_bar = tmem_full_bar + ACC_STAGES;
-    uint32_t* tmem_base_slot = reinterpret_cast<uint32_t*>(tmem_empty_bar + ACC_STAGES);
+    uint64_t* res_bar = tmem_empty_bar + ACC_STAGES;  // [4 warps][2 buffers]: residual sub-tile has landed
+    uint32_t* tmem_base_slot = reinterpret_cast<uint32_t*>(res_bar + 8);
 
     const int warp_idx = threadIdx.x >> 5;  // warp-uniform
     const int lane = threadIdx.x & 31;
@@ -118,6 +135,8 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_con
     if (warp_idx == 0 && ptx::elect_one()) {
         ptx::prefetch_tensormap(&tmap_a);
         ptx::prefetch_tensormap(&tmap_b);
+        if constexpr (TS && EPI != kEpiLsePartial) ptx::prefetch_tensormap(&tmap_c);
+        if constexpr (TS && EPI == kEpiResidual) ptx::prefetch_tensormap(&tmap_r);
     }
     if (warp_idx == 1 && ptx::elect_one()) {
         for (int i = 0; i < STAGES; ++i) {
@@ -128,6 +147,7 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_con
             ptx::mbar_init(&tmem_full_bar[i], 1);
             ptx::mbar_init(&tmem_empty_bar[i], 4 * CG);  // one arrive per epilogue warp of every CTA of the pair
         }
+        for (int i = 0; i < 8; ++i) ptx::mbar_init(&res_bar[i], 1);
         ptx::fence_mbar_init();
     }
     if (warp_idx == 2) {
@@ -239,67 +259,49 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_con
     } else if (warp_idx >= EPI_WARP0) {
         // ------------------------------------------------------------------ epilogue
         const int ew = warp_idx - EPI_WARP0;  // == warp_idx % 4 -> TMEM lanes [32*ew, 32*ew+32)
-        int acc = 0;
-        uint32_t acc_phase = 0;
-        for (int tile = worker; tile < num_tiles; tile += n_workers) {
-            int m_blk, n_blk;
-            tile_coords(tile, p.num_m_blocks, p.num_n_blocks, p.group_m, m_blk, n_blk);
-            ptx::mbar_wait(&tmem_full_bar[acc], acc_phase);
-            ptx::tc_fence_after_sync();
-            const int row = (m_blk * CG + static_cast<int>(cta_rank)) * BLOCK_M + ew * 32 + lane;
-            const bool row_ok = row < p.M;
-            const uint32_t taddr = tmem_base + (static_cast<uint32_t>(ew * 32) << 16) + acc * BLOCK_N;
-            const int col0 = n_blk * OUT_COLS;
-
-            if constexpr (EPI == kEpiSwiGLU) {
-                // HF LlamaMLP: act_fn(gate_proj(x)) * up_proj(x), each op rounded to fp16.
-#pragma unroll 1
-                for (int c = 0; c < OUT_COLS / 32; ++c) {
-                    uint32_t g[32], u[32];
-                    ptx::tmem_ld_32x32(taddr + c * 32, g);
-                    ptx::tmem_ld_32x32(taddr + OUT_COLS + c * 32, u);
-                    ptx::tmem_ld_wait();
-                    if (row_ok) {
-                        __half* dst = p.C + static_cast<size_t>(row) * p.ldc + col0 + c * 32;
-#pragma unroll
-                        for (int v = 0; v < 4; ++v) {
-                            if (col0 + c * 32 + v * 8 < p.N) {
-                                uint32_t o[4];
-#pragma unroll
-                                for (int j = 0; j < 4; ++j) {
-                                    __half r2[2];
-#pragma unroll
-                                    for (int e = 0; e < 2; ++e) {
-                                        const int i = v * 8 + j * 2 + e;
-                                        const float gf = __half2float(__float2half_rn(__uint_as_float(g[i])));
-                                        const __half s = __float2half_rn(gf / (1.0f + expf(-gf)));
-                                        const __half uh = __float2half_rn(__uint_as_float(u[i]));
-                                        r2[e] = __hmul(s, uh);
-                                    }
-                                    o[j] = pack_h2(r2[0], r2[1]);
-                                }
-                                *reinterpret_cast<uint4*>(dst + v * 8) = make_uint4(o[0], o[1], o[2], o[3]);
-                            }
-                        }
+        if constexpr (TS && EPI != kEpiLsePartial) {
+            // ---- staged epilogue: registers -> swizzled 32 x 64 sub-tile in smem -> TMA store
+            uint8_t* const buf_base = epi_stage + (ew * 2) * EPI_BUF_BYTES;  // this warp's two staging buffers
+            auto bufp = [&](uint32_t i) { return buf_base + (i & 1) * EPI_BUF_BYTES; };
+            uint64_t* rbar = res_bar + ew * 2;
+            uint32_t q = 0;  // 64-column chunks this warp has produced so far: buffer = q & 1, barrier phase = (q >> 1) & 1
+            int acc = 0;
+            uint32_t acc_phase = 0;
+            for (int tile = worker; tile < num_tiles; tile += n_workers) {
+                int m_blk, n_blk;
+                tile_coords(tile, p.num_m_blocks, p.num_n_blocks, p.group_m, m_blk, n_blk);
+                const int row0 = (m_blk * CG + static_cast<int>(cta_rank)) * BLOCK_M + ew * 32;  // this warp's first row
+                const int row = row0 + lane;
+                const bool row_ok = row < p.M;
+                const int col0 = n_blk * OUT_COLS;
+                const uint32_t taddr = tmem_base + (static_cast<uint32_t>(ew * 32) << 16) + acc * BLOCK_N;
+                if constexpr (EPI == kEpiResidual) {
+                    // the first residual chunk of the tile is fetched while the main loop still runs
+                    if (lane == 0) {
+                        ptx::bulk_wait_group_read<0>();  // whatever last read this buffer has done so
+                        ptx::mbar_arrive_expect_tx(&rbar[q & 1], EPI_BUF_BYTES);
+                        ptx::tma_load_2d(bufp(q & 1), &tmap_r, &rbar[q & 1], col0, row0);
                     }
                 }
-            } else if constexpr (EPI == kEpiStoreRope) {
-                // q/k heads (128 columns each, two per tile): HF apply_rotary_pos_emb on the fp16-rounded
-                // projection, half-split convention, every product and the sum rounded on their own
-                // (bit-identical to rope_kernel).  Columns >= rope_cols (the v heads) are stored as is.
-                const int pos = row_ok ? p.row_pos[row] : 0;
+                ptx::mbar_wait(&tmem_full_bar[acc], acc_phase);
+                ptx::tc_fence_after_sync();
+
+                if constexpr (EPI == kEpiStoreRope) {
+                    // Two 128-wide heads per tile.  A thread holds dims i and i+64 of its row, so a head fills
+                    // both staging buffers at once: buffer 0 <- dims [0,64), buffer 1 <- dims [64,128).
+                    const int pos = row_ok ? p.row_pos[row] : 0;
 #pragma unroll 1
-                for (int h = 0; h < BLOCK_N / 128; ++h) {
-                    const int hcol = col0 + h * 128;
-                    const bool rotate = hcol < p.rope_cols;
+                    for (int h = 0; h < BLOCK_N / 128; ++h) {
+                        const int hcol = col0 + h * 128;
+                        const bool rotate = hcol < p.rope_cols;
+                        if (lane == 0) ptx::bulk_wait_group_read<0>();
+                        __syncwarp();
 #pragma unroll 1
-                    for (int c = 0; c < 2; ++c) {
-                        uint32_t a[32], b[32];  // dims [c*32, +32) and their partners [64 + c*32, +32)
-                        ptx::tmem_ld_32x32(taddr + h * 128 + c * 32, a);
-                        ptx::tmem_ld_32x32(taddr + h * 128 + 64 + c * 32, b);
-                        ptx::tmem_ld_wait();
-                        if (row_ok && hcol < p.N) {
-                            __half* dst = p.C + static_cast<size_t>(row) * p.ldc + hcol + c * 32;
+                        for (int c = 0; c < 2; ++c) {
+                            uint32_t a[32], b[32];  // dims [c*32, +32) and their partners [64 + c*32, +32)
+                            ptx::tmem_ld_32x32(taddr + h * 128 + c * 32, a);
+                            ptx::tmem_ld_32x32(taddr + h * 128 + 64 + c * 32, b);
+                            ptx::tmem_ld_wait();
                             const __half* ct = p.cos_tab + static_cast<size_t>(pos) * 128 + c * 32;
                             const __half* st = p.sin_tab + static_cast<size_t>(pos) * 128 + c * 32;
 #pragma unroll
@@ -329,88 +331,296 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_con
                                     o1[j] = *reinterpret_cast<const uint32_t*>(&x1);
                                     o2[j] = *reinterpret_cast<const uint32_t*>(&x2);
                                 }
-                                *reinterpret_cast<uint4*>(dst + v * 8) = make_uint4(o1[0], o1[1], o1[2], o1[3]);
-                                *reinterpret_cast<uint4*>(dst + 64 + v * 8) = make_uint4(o2[0], o2[1], o2[2], o2[3]);
+                                *stage_ptr(bufp(0), lane, c * 4 + v) = make_uint4(o1[0], o1[1], o1[2], o1[3]);
+                                *stage_ptr(bufp(1), lane, c * 4 + v) = make_uint4(o2[0], o2[1], o2[2], o2[3]);
                             }
                         }
+                        ptx::fence_proxy_async_smem();
+                        __syncwarp();
+                        if (lane == 0 && hcol < p.N) {
+                            ptx::tma_store_2d(&tmap_c, bufp(0), hcol, row0);
+                            ptx::tma_store_2d(&tmap_c, bufp(1), hcol + 64, row0);
+                            ptx::bulk_commit_group();
+                        }
                     }
-                }
-            } else if constexpr (EPI == kEpiLsePartial) {
-                // running (max, sum exp) over this tile's columns of the fp16-rounded logits
-                float m_run = -INFINITY, s_run = 0.f;
+                } else {
+                    float lse = 0.f;
+                    if constexpr (EPI == kEpiProbs) lse = row_ok ? p.lse[row] : 0.f;
+                    constexpr int N_CHUNKS = OUT_COLS / EPI_CHUNK_COLS;
 #pragma unroll 1
-                for (int c = 0; c < BLOCK_N / 32; ++c) {
-                    uint32_t r[32];
-                    ptx::tmem_ld_32x32(taddr + c * 32, r);
-                    ptx::tmem_ld_wait();
-                    float v[32];
-                    float cmax = -INFINITY;
-#pragma unroll
-                    for (int i = 0; i < 32; ++i) {
-                        v[i] = (col0 + c * 32 + i < p.N) ? __half2float(__float2half_rn(__uint_as_float(r[i])))
-                                                         : -INFINITY;
-                        cmax = fmaxf(cmax, v[i]);
-                    }
-                    if (cmax > -INFINITY) {
-                        const float m_new = fmaxf(m_run, cmax);
-                        float s = 0.f;
-#pragma unroll
-                        for (int i = 0; i < 32; ++i) s += __expf(v[i] - m_new);
-                        s_run = s_run * __expf(m_run - m_new) + s;
-                        m_run = m_new;
-                    }
-                }
-                if (row_ok) p.partial[static_cast<size_t>(row) * p.num_n_blocks + n_blk] = make_float2(m_run, s_run);
-            } else {
-                float lse = 0.f;
-                if constexpr (EPI == kEpiProbs) lse = row_ok ? p.lse[row] : 0.f;
+                    for (int ch = 0; ch < N_CHUNKS; ++ch, ++q) {
+                        uint8_t* buf = bufp(q & 1);
+                        uint32_t r0[32], r1[32];  // SwiGLU: gate / up of 32 columns; else 2 x 32 columns
 #pragma unroll 1
-                for (int c = 0; c < BLOCK_N / 32; ++c) {
-                    uint32_t r[32];
-                    ptx::tmem_ld_32x32(taddr + c * 32, r);
-                    ptx::tmem_ld_wait();
-                    if (row_ok) {
-                        const size_t off = static_cast<size_t>(row) * p.ldc + col0 + c * 32;
-#pragma unroll
-                        for (int v = 0; v < 4; ++v) {
-                            if (col0 + c * 32 + v * 8 < p.N) {
-                                uint32_t o[4];
-                                uint4 res = make_uint4(0, 0, 0, 0);
-                                if constexpr (EPI == kEpiResidual)
-                                    res = *reinterpret_cast<const uint4*>(p.R + static_cast<size_t>(row) * p.ldr + col0 +
-                                                                          c * 32 + v * 8);
-                                const uint32_t rr[4] = {res.x, res.y, res.z, res.w};
-#pragma unroll
-                                for (int j = 0; j < 4; ++j) {
-                                    __half h0 = __float2half_rn(__uint_as_float(r[v * 8 + j * 2]));
-                                    __half h1 = __float2half_rn(__uint_as_float(r[v * 8 + j * 2 + 1]));
-                                    if constexpr (EPI == kEpiResidual) {
-                                        // hidden = residual + linear(x): fp16 add of two fp16 values
-                                        const __half2 rh = *reinterpret_cast<const __half2*>(&rr[j]);
-                                        h0 = __hadd(__low2half(rh), h0);
-                                        h1 = __hadd(__high2half(rh), h1);
-                                    } else if constexpr (EPI == kEpiProbs) {
-                                        // softmax evaluated on the fp16 logits (reference utils.py:289)
-                                        h0 = __float2half_rn(__expf(__half2float(h0) - lse));
-                                        h1 = __float2half_rn(__expf(__half2float(h1) - lse));
+                        for (int half = 0; half < (EPI == kEpiSwiGLU ? 2 : 1); ++half) {
+                            if constexpr (EPI == kEpiSwiGLU) {
+                                ptx::tmem_ld_32x32(taddr + ch * 64 + half * 32, r0);
+                                ptx::tmem_ld_32x32(taddr + OUT_COLS + ch * 64 + half * 32, r1);
+                            } else {
+                                ptx::tmem_ld_32x32(taddr + ch * 64, r0);
+                                ptx::tmem_ld_32x32(taddr + ch * 64 + 32, r1);
+                            }
+                            if (half == 0) {
+                                if constexpr (EPI == kEpiResidual) {
+                                    if (lane == 0 && ch + 1 < N_CHUNKS) {  // next chunk's residual into the other buffer
+                                        ptx::bulk_wait_group_read<0>();
+                                        ptx::mbar_arrive_expect_tx(&rbar[(q + 1) & 1], EPI_BUF_BYTES);
+                                        ptx::tma_load_2d(bufp((q + 1) & 1), &tmap_r, &rbar[(q + 1) & 1],
+                                                         col0 + (ch + 1) * EPI_CHUNK_COLS, row0);
                                     }
-                                    o[j] = pack_h2(h0, h1);
+                                } else {
+                                    if (lane == 0) ptx::bulk_wait_group_read<1>();  // the store two chunks back has read `buf`
                                 }
-                                *reinterpret_cast<uint4*>(p.C + off + v * 8) = make_uint4(o[0], o[1], o[2], o[3]);
+                                __syncwarp();
+                            }
+                            ptx::tmem_ld_wait();
+                            if constexpr (EPI == kEpiResidual) ptx::mbar_wait(&rbar[q & 1], (q >> 1) & 1);
+                            if constexpr (EPI == kEpiSwiGLU) {
+                                // HF LlamaMLP: act_fn(gate_proj(x)) * up_proj(x), each op rounded to fp16.
+#pragma unroll
+                                for (int v = 0; v < 4; ++v) {
+                                    uint32_t o[4];
+#pragma unroll
+                                    for (int j = 0; j < 4; ++j) {
+                                        __half r2[2];
+#pragma unroll
+                                        for (int e = 0; e < 2; ++e) {
+                                            const int i = v * 8 + j * 2 + e;
+                                            const float gf = __half2float(__float2half_rn(__uint_as_float(r0[i])));
+                                            const __half sg = __float2half_rn(gf / (1.0f + expf(-gf)));
+                                            const __half uh = __float2half_rn(__uint_as_float(r1[i]));
+                                            r2[e] = __hmul(sg, uh);
+                                        }
+                                        o[j] = pack_h2(r2[0], r2[1]);
+                                    }
+                                    *stage_ptr(buf, lane, half * 4 + v) = make_uint4(o[0], o[1], o[2], o[3]);
+                                }
+                            } else {
+#pragma unroll
+                                for (int part = 0; part < 2; ++part) {
+                                    const uint32_t* r = part == 0 ? r0 : r1;
+#pragma unroll
+                                    for (int v = 0; v < 4; ++v) {
+                                        uint4* sp = stage_ptr(buf, lane, part * 4 + v);
+                                        uint4 res = make_uint4(0, 0, 0, 0);
+                                        if constexpr (EPI == kEpiResidual) res = *sp;
+                                        const uint32_t rr[4] = {res.x, res.y, res.z, res.w};
+                                        uint32_t o[4];
+#pragma unroll
+                                        for (int j = 0; j < 4; ++j) {
+                                            __half h0 = __float2half_rn(__uint_as_float(r[v * 8 + j * 2]));
+                                            __half h1 = __float2half_rn(__uint_as_float(r[v * 8 + j * 2 + 1]));
+                                            if constexpr (EPI == kEpiResidual) {
+                                                // hidden = residual + linear(x): fp16 add of two fp16 values
+                                                const __half2 rh = *reinterpret_cast<const __half2*>(&rr[j]);
+                                                h0 = __hadd(__low2half(rh), h0);
+                                                h1 = __hadd(__high2half(rh), h1);
+                                            } else if constexpr (EPI == kEpiProbs) {
+                                                // softmax evaluated on the fp16 logits (reference utils.py:289)
+                                                h0 = __float2half_rn(__expf(__half2float(h0) - lse));
+                                                h1 = __float2half_rn(__expf(__half2float(h1) - lse));
+                                            }
+                                            o[j] = pack_h2(h0, h1);
+                                        }
+                                        *sp = make_uint4(o[0], o[1], o[2], o[3]);
+                                    }
+                                }
+                            }
+                        }
+                        ptx::fence_proxy_async_smem();
+                        __syncwarp();
+                        if (lane == 0 && col0 + ch * EPI_CHUNK_COLS < p.N) {
+                            ptx::tma_store_2d(&tmap_c, buf, col0 + ch * EPI_CHUNK_COLS, row0);
+                            ptx::bulk_commit_group();
+                        }
+                    }
+                }
+                ptx::tc_fence_before_sync();
+                __syncwarp();
+                if (lane == 0) {
+                    if constexpr (CG == 1) ptx::mbar_arrive(&tmem_empty_bar[acc]);
+                    else ptx::mbar_arrive_cluster(&tmem_empty_bar[acc], 0);  // the leader's MMA thread waits on it
+                }
+                if (++acc == ACC_STAGES) {
+                    acc = 0;
+                    acc_phase ^= 1;
+                }
+            }
+            if (lane == 0) ptx::bulk_wait_group_read<0>();  // the staging buffers must outlive the last stores' reads
+        } else {
+            int acc = 0;
+            uint32_t acc_phase = 0;
+            for (int tile = worker; tile < num_tiles; tile += n_workers) {
+                int m_blk, n_blk;
+                tile_coords(tile, p.num_m_blocks, p.num_n_blocks, p.group_m, m_blk, n_blk);
+                ptx::mbar_wait(&tmem_full_bar[acc], acc_phase);
+                ptx::tc_fence_after_sync();
+                const int row = (m_blk * CG + static_cast<int>(cta_rank)) * BLOCK_M + ew * 32 + lane;
+                const bool row_ok = row < p.M;
+                const uint32_t taddr = tmem_base + (static_cast<uint32_t>(ew * 32) << 16) + acc * BLOCK_N;
+                const int col0 = n_blk * OUT_COLS;
+
+                if constexpr (EPI == kEpiSwiGLU) {
+                    // HF LlamaMLP: act_fn(gate_proj(x)) * up_proj(x), each op rounded to fp16.
+    #pragma unroll 1
+                    for (int c = 0; c < OUT_COLS / 32; ++c) {
+                        uint32_t g[32], u[32];
+                        ptx::tmem_ld_32x32(taddr + c * 32, g);
+                        ptx::tmem_ld_32x32(taddr + OUT_COLS + c * 32, u);
+                        ptx::tmem_ld_wait();
+                        if (row_ok) {
+                            __half* dst = p.C + static_cast<size_t>(row) * p.ldc + col0 + c * 32;
+    #pragma unroll
+                            for (int v = 0; v < 4; ++v) {
+                                if (col0 + c * 32 + v * 8 < p.N) {
+                                    uint32_t o[4];
+    #pragma unroll
+                                    for (int j = 0; j < 4; ++j) {
+                                        __half r2[2];
+    #pragma unroll
+                                        for (int e = 0; e < 2; ++e) {
+                                            const int i = v * 8 + j * 2 + e;
+                                            const float gf = __half2float(__float2half_rn(__uint_as_float(g[i])));
+                                            const __half s = __float2half_rn(gf / (1.0f + expf(-gf)));
+                                            const __half uh = __float2half_rn(__uint_as_float(u[i]));
+                                            r2[e] = __hmul(s, uh);
+                                        }
+                                        o[j] = pack_h2(r2[0], r2[1]);
+                                    }
+                                    *reinterpret_cast<uint4*>(dst + v * 8) = make_uint4(o[0], o[1], o[2], o[3]);
+                                }
+                            }
+                        }
+                    }
+                } else if constexpr (EPI == kEpiStoreRope) {
+                    // q/k heads (128 columns each, two per tile): HF apply_rotary_pos_emb on the fp16-rounded
+                    // projection, half-split convention, every product and the sum rounded on their own
+                    // (bit-identical to rope_kernel).  Columns >= rope_cols (the v heads) are stored as is.
+                    const int pos = row_ok ? p.row_pos[row] : 0;
+    #pragma unroll 1
+                    for (int h = 0; h < BLOCK_N / 128; ++h) {
+                        const int hcol = col0 + h * 128;
+                        const bool rotate = hcol < p.rope_cols;
+    #pragma unroll 1
+                        for (int c = 0; c < 2; ++c) {
+                            uint32_t a[32], b[32];  // dims [c*32, +32) and their partners [64 + c*32, +32)
+                            ptx::tmem_ld_32x32(taddr + h * 128 + c * 32, a);
+                            ptx::tmem_ld_32x32(taddr + h * 128 + 64 + c * 32, b);
+                            ptx::tmem_ld_wait();
+                            if (row_ok && hcol < p.N) {
+                                __half* dst = p.C + static_cast<size_t>(row) * p.ldc + hcol + c * 32;
+                                const __half* ct = p.cos_tab + static_cast<size_t>(pos) * 128 + c * 32;
+                                const __half* st = p.sin_tab + static_cast<size_t>(pos) * 128 + c * 32;
+    #pragma unroll
+                                for (int v = 0; v < 4; ++v) {
+                                    uint4 c1 = make_uint4(0, 0, 0, 0), s1 = c1, c2 = c1, s2 = c1;
+                                    if (rotate) {
+                                        c1 = *reinterpret_cast<const uint4*>(ct + v * 8);
+                                        s1 = *reinterpret_cast<const uint4*>(st + v * 8);
+                                        c2 = *reinterpret_cast<const uint4*>(ct + 64 + v * 8);
+                                        s2 = *reinterpret_cast<const uint4*>(st + 64 + v * 8);
+                                    }
+                                    const __half2* hc1 = reinterpret_cast<const __half2*>(&c1);
+                                    const __half2* hs1 = reinterpret_cast<const __half2*>(&s1);
+                                    const __half2* hc2 = reinterpret_cast<const __half2*>(&c2);
+                                    const __half2* hs2 = reinterpret_cast<const __half2*>(&s2);
+                                    uint32_t o1[4], o2[4];
+    #pragma unroll
+                                    for (int j = 0; j < 4; ++j) {
+                                        const int i = v * 8 + j * 2;
+                                        __half2 x1 = __floats2half2_rn(__uint_as_float(a[i]), __uint_as_float(a[i + 1]));
+                                        __half2 x2 = __floats2half2_rn(__uint_as_float(b[i]), __uint_as_float(b[i + 1]));
+                                        if (rotate) {
+                                            const __half2 r1 = __hadd2_rn(__hmul2_rn(x1, hc1[j]), __hmul2_rn(__hneg2(x2), hs1[j]));
+                                            const __half2 r2 = __hadd2_rn(__hmul2_rn(x2, hc2[j]), __hmul2_rn(x1, hs2[j]));
+                                            x1 = r1, x2 = r2;
+                                        }
+                                        o1[j] = *reinterpret_cast<const uint32_t*>(&x1);
+                                        o2[j] = *reinterpret_cast<const uint32_t*>(&x2);
+                                    }
+                                    *reinterpret_cast<uint4*>(dst + v * 8) = make_uint4(o1[0], o1[1], o1[2], o1[3]);
+                                    *reinterpret_cast<uint4*>(dst + 64 + v * 8) = make_uint4(o2[0], o2[1], o2[2], o2[3]);
+                                }
+                            }
+                        }
+                    }
+                } else if constexpr (EPI == kEpiLsePartial) {
+                    // running (max, sum exp) over this tile's columns of the fp16-rounded logits
+                    float m_run = -INFINITY, s_run = 0.f;
+    #pragma unroll 1
+                    for (int c = 0; c < BLOCK_N / 32; ++c) {
+                        uint32_t r[32];
+                        ptx::tmem_ld_32x32(taddr + c * 32, r);
+                        ptx::tmem_ld_wait();
+                        float v[32];
+                        float cmax = -INFINITY;
+    #pragma unroll
+                        for (int i = 0; i < 32; ++i) {
+                            v[i] = (col0 + c * 32 + i < p.N) ? __half2float(__float2half_rn(__uint_as_float(r[i])))
+                                                             : -INFINITY;
+                            cmax = fmaxf(cmax, v[i]);
+                        }
+                        if (cmax > -INFINITY) {
+                            const float m_new = fmaxf(m_run, cmax);
+                            float s = 0.f;
+    #pragma unroll
+                            for (int i = 0; i < 32; ++i) s += __expf(v[i] - m_new);
+                            s_run = s_run * __expf(m_run - m_new) + s;
+                            m_run = m_new;
+                        }
+                    }
+                    if (row_ok) p.partial[static_cast<size_t>(row) * p.num_n_blocks + n_blk] = make_float2(m_run, s_run);
+                } else {
+                    float lse = 0.f;
+                    if constexpr (EPI == kEpiProbs) lse = row_ok ? p.lse[row] : 0.f;
+    #pragma unroll 1
+                    for (int c = 0; c < BLOCK_N / 32; ++c) {
+                        uint32_t r[32];
+                        ptx::tmem_ld_32x32(taddr + c * 32, r);
+                        ptx::tmem_ld_wait();
+                        if (row_ok) {
+                            const size_t off = static_cast<size_t>(row) * p.ldc + col0 + c * 32;
+    #pragma unroll
+                            for (int v = 0; v < 4; ++v) {
+                                if (col0 + c * 32 + v * 8 < p.N) {
+                                    uint32_t o[4];
+                                    uint4 res = make_uint4(0, 0, 0, 0);
+                                    if constexpr (EPI == kEpiResidual)
+                                        res = *reinterpret_cast<const uint4*>(p.R + static_cast<size_t>(row) * p.ldr + col0 +
+                                                                              c * 32 + v * 8);
+                                    const uint32_t rr[4] = {res.x, res.y, res.z, res.w};
+    #pragma unroll
+                                    for (int j = 0; j < 4; ++j) {
+                                        __half h0 = __float2half_rn(__uint_as_float(r[v * 8 + j * 2]));
+                                        __half h1 = __float2half_rn(__uint_as_float(r[v * 8 + j * 2 + 1]));
+                                        if constexpr (EPI == kEpiResidual) {
+                                            // hidden = residual + linear(x): fp16 add of two fp16 values
+                                            const __half2 rh = *reinterpret_cast<const __half2*>(&rr[j]);
+                                            h0 = __hadd(__low2half(rh), h0);
+                                            h1 = __hadd(__high2half(rh), h1);
+                                        } else if constexpr (EPI == kEpiProbs) {
+                                            // softmax evaluated on the fp16 logits (reference utils.py:289)
+                                            h0 = __float2half_rn(__expf(__half2float(h0) - lse));
+                                            h1 = __float2half_rn(__expf(__half2float(h1) - lse));
+                                        }
+                                        o[j] = pack_h2(h0, h1);
+                                    }
+                                    *reinterpret_cast<uint4*>(p.C + off + v * 8) = make_uint4(o[0], o[1], o[2], o[3]);
+                                }
                             }
                         }
                     }
                 }
-            }
-            ptx::tc_fence_before_sync();
-            __syncwarp();
-            if (lane == 0) {
-                if constexpr (CG == 1) ptx::mbar_arrive(&tmem_empty_bar[acc]);
-                else ptx::mbar_arrive_cluster(&tmem_empty_bar[acc], 0);  // the leader's MMA thread waits on it
-            }
-            if (++acc == ACC_STAGES) {
-                acc = 0;
-                acc_phase ^= 1;
+                ptx::tc_fence_before_sync();
+                __syncwarp();
+                if (lane == 0) {
+                    if constexpr (CG == 1) ptx::mbar_arrive(&tmem_empty_bar[acc]);
+                    else ptx::mbar_arrive_cluster(&tmem_empty_bar[acc], 0);  // the leader's MMA thread waits on it
+                }
+                if (++acc == ACC_STAGES) {
+                    acc = 0;
+                    acc_phase ^= 1;
+                }
             }
         }
     }
@@ -431,9 +641,38 @@ using EncodeTiledFn = CUresult (*)(CUtensorMap*, CUtensorMapDataType, cuuint32_t
                                    CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
 EncodeTiledFn g_encode = nullptr;
 
+// Encoded descriptors are kept per (pointer, shape, box): a pass launches the same few operand shapes thousands of
+// times (weight slots and workspace buffers do not move), and every encode is a driver call.
+struct TmapKey {
+    uintptr_t base;
+    int rows, cols, ld, box_rows;
+    bool operator==(const TmapKey& o) const {
+        return base == o.base && rows == o.rows && cols == o.cols && ld == o.ld && box_rows == o.box_rows;
+    }
+};
+struct TmapKeyHash {
+    size_t operator()(const TmapKey& k) const {
+        size_t h = std::hash<uintptr_t>()(k.base);
+        for (int v : {k.rows, k.cols, k.ld, k.box_rows}) h = h * 1000003u ^ std::hash<int>()(v);
+        return h;
+    }
+};
+std::mutex g_tmap_mu;
+std::unordered_map<TmapKey, CUtensorMap, TmapKeyHash> g_tmap_cache;
+
+// Box = 64 columns (one 128-byte swizzle row) x box_rows.
 int make_tmap(CUtensorMap* tm, const __half* base, int rows, int cols, int ld, int box_rows) {
     if ((reinterpret_cast<uintptr_t>(base) & 15) || (ld % 8))
         return fail(kErrInvalid, "gemm operand must be 16-byte aligned with a row stride multiple of 8 (ld=%d)", ld);
+    const TmapKey key{reinterpret_cast<uintptr_t>(base), rows, cols, ld, box_rows};
+    {
+        std::lock_guard<std::mutex> lk(g_tmap_mu);
+        auto it = g_tmap_cache.find(key);
+        if (it != g_tmap_cache.end()) {
+            *tm = it->second;
+            return kOk;
+        }
+    }
     const cuuint64_t dims[2] = {static_cast<cuuint64_t>(cols), static_cast<cuuint64_t>(rows)};
     const cuuint64_t strides[1] = {static_cast<cuuint64_t>(ld) * sizeof(__half)};
     const cuuint32_t box[2] = {BLOCK_K, static_cast<cuuint32_t>(box_rows)};
@@ -442,16 +681,22 @@ int make_tmap(CUtensorMap* tm, const __half* base, int rows, int cols, int ld, i
                           CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
                           CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
     if (r != CUDA_SUCCESS) return fail(kErrCuda, "cuTensorMapEncodeTiled failed (CUresult %d)", static_cast<int>(r));
+    std::lock_guard<std::mutex> lk(g_tmap_mu);
+    if (g_tmap_cache.size() >= 4096) g_tmap_cache.clear();  // descriptors are values: dropping them is always safe
+    g_tmap_cache.emplace(key, *tm);
     return kOk;
 }
 
-template <int EPI, int CG>
+template <int EPI, int CG, bool TS>
 int launch_t(const GemmArgs& a, int num_sms, cudaStream_t stream) {
     constexpr int OUT_COLS = EPI == kEpiSwiGLU ? BLOCK_N / 2 : BLOCK_N;
     constexpr int B_BOX = (EPI == kEpiSwiGLU || CG == 2) ? BLOCK_N / 2 : BLOCK_N;
     CUtensorMap tma, tmb;
     FLS_TRY(make_tmap(&tma, a.A, a.M, a.K, a.lda, BLOCK_M));
     FLS_TRY(make_tmap(&tmb, a.B, a.b_rows, a.K, a.ldb, B_BOX));
+    CUtensorMap tmc = tma, tmr = tma;  // placeholders where the epilogue has no such operand
+    if constexpr (TS && EPI != kEpiLsePartial) FLS_TRY(make_tmap(&tmc, a.C, a.M, a.N, a.ldc, 32));
+    if constexpr (TS && EPI == kEpiResidual) FLS_TRY(make_tmap(&tmr, a.R, a.M, a.N, a.ldr, 32));
     KParams p;
     p.M = a.M, p.N = a.N, p.K = a.K;
     p.C = a.C, p.ldc = a.ldc, p.R = a.R, p.ldr = a.ldr;
@@ -475,20 +720,26 @@ int launch_t(const GemmArgs& a, int num_sms, cudaStream_t stream) {
     attr[0].val.clusterDim.z = 1;
     cfg.attrs = attr;
     cfg.numAttrs = 1;
-    FLS_CUDA(cudaLaunchKernelEx(&cfg, gemm_tcgen05_kernel<EPI, CG>, tma, tmb, p));
+    FLS_CUDA(cudaLaunchKernelEx(&cfg, gemm_tcgen05_kernel<EPI, CG, TS>, tma, tmb, tmc, tmr, p));
     return kOk;
 }
 
 template <int EPI>
 int launch_cg(const GemmArgs& a, int num_sms, int cta_group, cudaStream_t stream) {
-    return cta_group == 2 ? launch_t<EPI, 2>(a, num_sms, stream) : launch_t<EPI, 1>(a, num_sms, stream);
+    if (a.direct_store)
+        return cta_group == 2 ? launch_t<EPI, 2, false>(a, num_sms, stream) : launch_t<EPI, 1, false>(a, num_sms, stream);
+    return cta_group == 2 ? launch_t<EPI, 2, true>(a, num_sms, stream) : launch_t<EPI, 1, true>(a, num_sms, stream);
 }
 
 template <int EPI>
 int set_smem_attr() {
-    FLS_CUDA(cudaFuncSetAttribute(gemm_tcgen05_kernel<EPI, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+    FLS_CUDA(cudaFuncSetAttribute(gemm_tcgen05_kernel<EPI, 1, false>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                   Cfg<1>::SMEM_BYTES));
-    FLS_CUDA(cudaFuncSetAttribute(gemm_tcgen05_kernel<EPI, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+    FLS_CUDA(cudaFuncSetAttribute(gemm_tcgen05_kernel<EPI, 2, false>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                  Cfg<2>::SMEM_BYTES));
+    FLS_CUDA(cudaFuncSetAttribute(gemm_tcgen05_kernel<EPI, 1, true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                  Cfg<1>::SMEM_BYTES));
+    FLS_CUDA(cudaFuncSetAttribute(gemm_tcgen05_kernel<EPI, 2, true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                   Cfg<2>::SMEM_BYTES));
     return kOk;
 }

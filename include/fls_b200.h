@@ -318,6 +318,8 @@ int fls_get_profile(fls_ctx* ctx, fls_kernel_profile* out);
  * tcgen05 cta_group::2) or 1 (one CTA per 128x256 tile).  "attention_impl": 1 (default; tcgen05
  * kernel for head_dim 128) or 0 (mma.sync kernel).  "fuse_rope": 1 (default; rotary embedding applied in the
  * QKV GEMM epilogue when head_dim is 128) or 0 (separate kernel).  "paced_weight_stream": see fls_prefetch_pump.
+ * "gemm_tma_store": 1 (default; GEMM epilogues stage 32 x 64 sub-tiles in shared memory and write them with TMA
+ * stores, the residual operand arrives by TMA load) or 0 (every thread stores 16-byte pieces of its own row).
  * "gemm_group_m", "gemm_cache_hints": raster group / L2 hint experiments (tools/gemm_probe.py), default 0;
  * "rmsnorm_variant" 0..2: CTA shape of the RMSNorm kernel (tools/norm_probe.py), default 0. */
 int fls_set_option(fls_ctx* ctx, const char* name, int value);

@@ -1,30 +1,46 @@
-"""Sustained-throughput probe of the tcgen05 GEMM on the 7B decoder shapes (M = 16384 rows), with cuBLAS
-(torch.matmul, fp16) timed in the same process under the same power cap, and a sweep of the raster
-group size.  Each measurement loops one launch back to back for ~1.5 s (CUDA events).
-Run on a GPU box: python tools/gemm_probe.py [--secs 1.5]"""
+"""Sustained-throughput probe of the tcgen05 GEMM on the decoder shapes of a model (M = 16384 rows), with cuBLAS
+(torch.matmul, fp16, plain store) timed in the same process under the same power cap.  Each measurement loops one
+launch back to back for ~`--secs` seconds (CUDA events).
+
+    python tools/gemm_probe.py [--models 7b 70b] [--secs 1.5] [--groups 16 8] [--variants tma direct cg1]
+    python tools/gemm_probe.py --ncu 7b        # one launch per class in the order qkv, o, gate/up, down (for
+                                               # `ncu --set full`; bench.py reads the resulting CSV in that order)
+"""
 import argparse
 import ctypes as C
+import json
 import os
 import sys
 
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 import torch
-from flexible_llm_sharding_b200 import _lib
+from flexible_llm_sharding_b200 import _lib, synthetic
 
 ap = argparse.ArgumentParser()
+ap.add_argument("--models", nargs="+", default=["7b", "70b"])
 ap.add_argument("--secs", type=float, default=1.5)
 ap.add_argument("--groups", type=int, nargs="+", default=[16])
-ap.add_argument("--hints", type=int, nargs="*", default=[])
-ap.add_argument("--hint_groups", type=int, nargs="*", default=[16])
+ap.add_argument("--variants", nargs="+", default=["tma", "direct"])
+ap.add_argument("--rows", type=int, default=16384)
+ap.add_argument("--ncu", default="")
+ap.add_argument("--out", default="")
 a = ap.parse_args()
 
 ctx = _lib.Context(_lib.ModelDesc(4096, 11008, 32, 32, 128, 32000, 2, 1e-5), 0)
 ctx.call("fls_configure", 1, C.c_size_t(256), 256, 256)
-M = 16384
+M = a.rows
 dev = "cuda"
 sp = C.c_void_p(torch.cuda.current_stream().cuda_stream)
-SHAPES = [("qkv", 0, 12288, 4096), ("o+res", 1, 4096, 4096), ("gate_up+swiglu", 2, 11008, 4096),
-          ("down+res", 1, 4096, 11008)]
+
+
+def shapes_of(model):
+    s = synthetic.LlamaShape.named(model)
+    H, I = s.hidden_size, s.intermediate_size
+    qkv = (s.num_attention_heads + 2 * s.num_key_value_heads) * s.head_dim
+    # (class, epilogue, N, K): store (the fused-RoPE epilogue needs positions; its cost is the same stores), +residual,
+    # SwiGLU, +residual
+    return [("gemm_qkv", 0, qkv, H), ("gemm_o", 1, H, s.num_attention_heads * s.head_dim),
+            ("gemm_gate_up", 2, I, H), ("gemm_down", 1, H, I)]
 
 
 def sustained(fn, flops):
@@ -41,37 +57,50 @@ def sustained(fn, flops):
     return flops * n / (e0.elapsed_time(e1) * 1e-3) / 1e12
 
 
-for name, epi, N, K in SHAPES:
+def operands(epi, N, K):
     A = (torch.randn((M, K), device=dev) * 0.5).half()
     brows = 2 * N if epi == 2 else N
     B = (torch.randn((brows, K), device=dev) * 0.02).half()
     Cm = torch.zeros((M, N), dtype=torch.float16, device=dev)
-    flops = 2.0 * M * brows * K
-    res = {}
+    return A, B, Cm, brows
 
-    def ours():
-        ctx.call("fls_op_gemm", epi, A.data_ptr(), K, B.data_ptr(), K, brows, M, N, K, Cm.data_ptr(), N,
-                 Cm.data_ptr() if epi == 1 else None, N, N if epi == 2 else 0, sp)
 
-    for cg in (2, 1):
-        ctx.call("fls_set_option", b"gemm_cta_group", cg)
-        for g in (a.groups if cg == 2 else [16]):
-            ctx.call("fls_set_option", b"gemm_group_m", g)
-            res[f"cg{cg}/group{g}"] = round(sustained(ours, flops))
-    ctx.call("fls_set_option", b"gemm_cta_group", 2)
-    ctx.call("fls_set_option", b"gemm_group_m", 0)
-    for hint in a.hints:
-        ctx.call("fls_set_option", b"gemm_cache_hints", hint)
-        for g in a.hint_groups:
-            ctx.call("fls_set_option", b"gemm_group_m", g)
-            res[f"cg2/group{g}/hint{hint}"] = round(sustained(ours, flops))
-    ctx.call("fls_set_option", b"gemm_cache_hints", 0)
-    ctx.call("fls_set_option", b"gemm_group_m", 0)
-    if epi == 1:      # the same shape with the plain-store epilogue: what does the fused residual cost?
-        def plain():
-            ctx.call("fls_op_gemm", 0, A.data_ptr(), K, B.data_ptr(), K, brows, M, N, K, Cm.data_ptr(), N, None, 0, 0, sp)
-        res["cg2/group16/plain-store"] = round(sustained(plain, flops))
-    Bt = B.t()
-    out = torch.empty((M, brows), dtype=torch.float16, device=dev)
-    res["cublas(torch.matmul, plain store)"] = round(sustained(lambda: torch.matmul(A, Bt, out=out), flops))
-    print(name, f"M={M} N={brows} K={K}", res, flush=True)
+def launch(epi, A, B, Cm, brows, N, K):
+    ctx.call("fls_op_gemm", epi, A.data_ptr(), K, B.data_ptr(), K, brows, M, N, K, Cm.data_ptr(), N,
+             Cm.data_ptr() if epi == 1 else None, N, N if epi == 2 else 0, sp)
+
+
+if a.ncu:
+    for name, epi, N, K in shapes_of(a.ncu):
+        A, B, Cm, brows = operands(epi, N, K)
+        launch(epi, A, B, Cm, brows, N, K)
+        torch.cuda.synchronize()
+        del A, B, Cm
+    sys.exit(0)
+
+results = {}
+for model in a.models:
+    for name, epi, N, K in shapes_of(model):
+        A, B, Cm, brows = operands(epi, N, K)
+        flops = 2.0 * M * brows * K
+        res = {}
+        for variant in a.variants:
+            ctx.call("fls_set_option", b"gemm_cta_group", 1 if variant == "cg1" else 2)
+            ctx.call("fls_set_option", b"gemm_tma_store", 0 if variant == "direct" else 1)
+            for g in a.groups:
+                ctx.call("fls_set_option", b"gemm_group_m", g)
+                res[f"{variant}/group{g}"] = round(sustained(lambda: launch(epi, A, B, Cm, brows, N, K), flops))
+        ctx.call("fls_set_option", b"gemm_cta_group", 2)
+        ctx.call("fls_set_option", b"gemm_tma_store", 1)
+        ctx.call("fls_set_option", b"gemm_group_m", 0)
+        Bt = B.t()
+        out = torch.empty((M, brows), dtype=torch.float16, device=dev)
+        res["cublas(torch.matmul, plain store)"] = round(sustained(lambda: torch.matmul(A, Bt, out=out), flops))
+        best = max(v for k, v in res.items() if not k.startswith("cublas"))
+        res["best/cublas"] = round(best / res["cublas(torch.matmul, plain store)"], 3)
+        results[f"{model}/{name} M={M} N={brows} K={K}"] = res
+        print(f"{model}/{name}", f"M={M} N={brows} K={K}", res, flush=True)
+        del A, B, Cm, Bt, out
+if a.out:
+    with open(a.out, "w") as f:
+        json.dump(results, f, indent=1)
