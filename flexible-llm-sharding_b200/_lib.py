@@ -14,9 +14,9 @@ import threading
 PKG_DIR = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(PKG_DIR, "csrc")
 LIB_PATH = os.path.join(CSRC, "libfls_b200.so")
-SOURCES = ["api.cu", "gemm_sm100.cu", "elementwise.cu", "attention.cu", "attention_sm100.cu", "host_cache.cpp",
+SOURCES = ["api.cu", "gemm_sm100.cu", "gemm_wide_sm100.cu", "elementwise.cu", "attention.cu", "attention_sm100.cu", "host_cache.cpp",
            "noalloc.cu"]
-HEADERS = ["common.cuh", "ptx.cuh", "host_cache.h", os.path.join("..", "..", "include", "fls_b200.h")]
+HEADERS = ["common.cuh", "ptx.cuh", "gemm_tile.cuh", "host_cache.h", os.path.join("..", "..", "include", "fls_b200.h")]
 NVCC_FLAGS = ["-shared", "-Xcompiler", "-fPIC", "-std=c++17", "-O3", "-lineinfo",
               "-gencode", "arch=compute_100a,code=sm_100a"]
 

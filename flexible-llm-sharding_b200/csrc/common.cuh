@@ -62,6 +62,8 @@ struct GemmArgs {
     int up_off;
     int group_m;      // m-blocks per raster group (0 = default 16)
     int cache_hints;  // cta_group 2 only: 0 none, 1 A evict-first / B evict-last, 2 the reverse
+    int raster;        // tile order (gemm_tile.cuh tile_coords): 0 m-fastest groups (default), 1 n-fastest, 2/3 serpentine
+    int wide;          // 1: 256 x 512 tiles per CTA pair (gemm_wide_sm100.cu) where the epilogue has that variant
     int direct_store;  // 0 (default): epilogue stages tiles in smem and writes them with TMA; 1: per-thread 16-byte stores
     // kEpiStoreRope: rotary position of every row and the fp16 cos/sin tables [n_pos, 128]
     const int32_t* row_pos;
@@ -70,6 +72,10 @@ struct GemmArgs {
     int rope_cols;
 };
 int gemm_launch(GemmEpilogue epi, const GemmArgs& a, int num_sms, cudaStream_t stream, int cta_group = 2);
+// 256 x 512-tile variant (cta_group::2, staged epilogue): store, store+RoPE, residual and SwiGLU epilogues
+int gemm_wide_init();
+bool gemm_wide_supports(GemmEpilogue epi);
+int gemm_wide_launch(GemmEpilogue epi, const GemmArgs& a, int num_sms, cudaStream_t stream);
 int gemm_init();  // resolves cuTensorMapEncodeTiled and opts kernels into large dynamic smem
 int gemm_lse_blocks(int N);
 

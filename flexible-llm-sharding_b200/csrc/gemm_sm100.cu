@@ -30,84 +30,13 @@
 #include <mutex>
 #include <unordered_map>
 
-#include "common.cuh"
-#include "ptx.cuh"
+#include "gemm_tile.cuh"
 
 namespace fls {
 
+using namespace gemm;
+
 namespace {
-
-constexpr int BLOCK_M = 128;  // rows per CTA (a CTA pair covers 256)
-constexpr int BLOCK_N = 256;  // MMA N (TMEM columns per accumulator stage)
-constexpr int BLOCK_K = 64;   // 64 fp16 = 128 B = one swizzle row
-constexpr int UMMA_K = 16;
-constexpr int ACC_STAGES = 2;
-constexpr int A_BYTES = BLOCK_M * BLOCK_K * 2;  // 16 KiB
-constexpr int SMEM_BARRIER_BYTES = 512;
-constexpr int EPI_CHUNK_COLS = 64;                      // one swizzle row of fp16
-constexpr int EPI_BUF_BYTES = 32 * EPI_CHUNK_COLS * 2;  // 32 rows x 128 B per epilogue warp
-constexpr int EPI_STAGE_BYTES = 4 * 2 * EPI_BUF_BYTES;  // 4 warps x 2 buffers = 32 KiB
-constexpr int MAX_STAGES = 8;
-
-// CG = tcgen05 cta_group.  CG 1: one CTA per 128x256 tile, B tile 256 rows, 4 stages of 48 KiB.
-// CG 2: a CTA pair (cluster of 2) per 256x256 tile; each CTA stages its own 128 A rows and HALF of
-// the B rows (the pair's MMA reads both halves), 6 stages of 32 KiB: half the shared-memory operand
-// traffic per SM and a deeper TMA look-ahead.
-template <int CG>
-struct Cfg {
-    static constexpr int STAGES = CG == 1 ? 4 : 6;
-    static constexpr int B_ROWS = BLOCK_N / CG;
-    static constexpr int B_BYTES = B_ROWS * BLOCK_K * 2;
-    static constexpr int STAGE_BYTES = A_BYTES + B_BYTES;
-    static constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + EPI_STAGE_BYTES + SMEM_BARRIER_BYTES + 1024;  // + alignment slack
-};
-constexpr int NUM_THREADS = 256;
-constexpr int EPI_WARP0 = 4;
-constexpr int GROUP_M = 16;  // default m-blocks per raster group: A bands of a group stay in L2 while n sweeps
-
-struct KParams {
-    int M, N, K;
-    __half* C;
-    int ldc;
-    const __half* R;
-    int ldr;
-    float2* partial;
-    const float* lse;
-    int up_off;
-    int group_m;
-    int cache_hints;
-    int num_m_blocks, num_n_blocks;
-    const int32_t* row_pos;
-    const __half* cos_tab;
-    const __half* sin_tab;
-    int rope_cols;
-};
-
-template <int EPI>
-__device__ __forceinline__ constexpr int out_cols_per_tile() {
-    return EPI == kEpiSwiGLU ? BLOCK_N / 2 : BLOCK_N;
-}
-
-__device__ __forceinline__ void tile_coords(int tile, int num_m_blocks, int num_n_blocks, int group_m, int& m_blk,
-                                            int& n_blk) {
-    const int per_group = group_m * num_n_blocks;
-    const int group = tile / per_group;
-    const int first_m = group * group_m;
-    const int gsize = min(num_m_blocks - first_m, group_m);
-    const int local = tile - group * per_group;
-    m_blk = first_m + local % gsize;
-    n_blk = local / gsize;
-}
-
-__device__ __forceinline__ uint32_t pack_h2(__half a, __half b) {
-    __half2 h = __halves2half2(a, b);
-    return *reinterpret_cast<uint32_t*>(&h);
-}
-
-// 16-byte piece j (0..7) of row r of a 32 x 64 fp16 sub-tile laid out with the 128-byte swizzle TMA expects
-__device__ __forceinline__ uint4* stage_ptr(uint8_t* buf, int r, int j) {
-    return reinterpret_cast<uint4*>(buf + r * 128 + ((j ^ (r & 7)) << 4));
-}
 
 template <int EPI, int CG, bool TS>
 __global__ void __launch_bounds__(NUM_THREADS, 1)
@@ -171,7 +100,7 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_con
             uint32_t phase = 0;
             for (int tile = worker; tile < num_tiles; tile += n_workers) {
                 int m_blk, n_blk;
-                tile_coords(tile, p.num_m_blocks, p.num_n_blocks, p.group_m, m_blk, n_blk);
+                tile_coords(tile, p.num_m_blocks, p.num_n_blocks, p.group_m, p.raster, m_blk, n_blk);
                 const int a_row = (m_blk * CG + static_cast<int>(cta_rank)) * BLOCK_M;
                 int b_row;
                 if constexpr (EPI == kEpiSwiGLU)  // CG 2: leader stages the gate rows, its peer the up rows
@@ -262,179 +191,22 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_con
         if constexpr (TS && EPI != kEpiLsePartial) {
             // ---- staged epilogue: registers -> swizzled 32 x 64 sub-tile in smem -> TMA store
             uint8_t* const buf_base = epi_stage + (ew * 2) * EPI_BUF_BYTES;  // this warp's two staging buffers
-            auto bufp = [&](uint32_t i) { return buf_base + (i & 1) * EPI_BUF_BYTES; };
             uint64_t* rbar = res_bar + ew * 2;
             uint32_t q = 0;  // 64-column chunks this warp has produced so far: buffer = q & 1, barrier phase = (q >> 1) & 1
             int acc = 0;
             uint32_t acc_phase = 0;
             for (int tile = worker; tile < num_tiles; tile += n_workers) {
                 int m_blk, n_blk;
-                tile_coords(tile, p.num_m_blocks, p.num_n_blocks, p.group_m, m_blk, n_blk);
+                tile_coords(tile, p.num_m_blocks, p.num_n_blocks, p.group_m, p.raster, m_blk, n_blk);
                 const int row0 = (m_blk * CG + static_cast<int>(cta_rank)) * BLOCK_M + ew * 32;  // this warp's first row
-                const int row = row0 + lane;
-                const bool row_ok = row < p.M;
                 const int col0 = n_blk * OUT_COLS;
                 const uint32_t taddr = tmem_base + (static_cast<uint32_t>(ew * 32) << 16) + acc * BLOCK_N;
-                if constexpr (EPI == kEpiResidual) {
-                    // the first residual chunk of the tile is fetched while the main loop still runs
-                    if (lane == 0) {
-                        ptx::bulk_wait_group_read<0>();  // whatever last read this buffer has done so
-                        ptx::mbar_arrive_expect_tx(&rbar[q & 1], EPI_BUF_BYTES);
-                        ptx::tma_load_2d(bufp(q & 1), &tmap_r, &rbar[q & 1], col0, row0);
-                    }
-                }
+                // the first residual chunk of the tile is fetched while the main loop still runs
+                if constexpr (EPI == kEpiResidual) epi_prefetch_residual(&tmap_r, buf_base, rbar, q, lane, col0, row0);
                 ptx::mbar_wait(&tmem_full_bar[acc], acc_phase);
                 ptx::tc_fence_after_sync();
 
-                if constexpr (EPI == kEpiStoreRope) {
-                    // Two 128-wide heads per tile.  A thread holds dims i and i+64 of its row, so a head fills
-                    // both staging buffers at once: buffer 0 <- dims [0,64), buffer 1 <- dims [64,128).
-                    const int pos = row_ok ? p.row_pos[row] : 0;
-#pragma unroll 1
-                    for (int h = 0; h < BLOCK_N / 128; ++h) {
-                        const int hcol = col0 + h * 128;
-                        const bool rotate = hcol < p.rope_cols;
-                        if (lane == 0) ptx::bulk_wait_group_read<0>();
-                        __syncwarp();
-#pragma unroll 1
-                        for (int c = 0; c < 2; ++c) {
-                            uint32_t a[32], b[32];  // dims [c*32, +32) and their partners [64 + c*32, +32)
-                            ptx::tmem_ld_32x32(taddr + h * 128 + c * 32, a);
-                            ptx::tmem_ld_32x32(taddr + h * 128 + 64 + c * 32, b);
-                            ptx::tmem_ld_wait();
-                            const __half* ct = p.cos_tab + static_cast<size_t>(pos) * 128 + c * 32;
-                            const __half* st = p.sin_tab + static_cast<size_t>(pos) * 128 + c * 32;
-#pragma unroll
-                            for (int v = 0; v < 4; ++v) {
-                                uint4 c1 = make_uint4(0, 0, 0, 0), s1 = c1, c2 = c1, s2 = c1;
-                                if (rotate) {
-                                    c1 = *reinterpret_cast<const uint4*>(ct + v * 8);
-                                    s1 = *reinterpret_cast<const uint4*>(st + v * 8);
-                                    c2 = *reinterpret_cast<const uint4*>(ct + 64 + v * 8);
-                                    s2 = *reinterpret_cast<const uint4*>(st + 64 + v * 8);
-                                }
-                                const __half2* hc1 = reinterpret_cast<const __half2*>(&c1);
-                                const __half2* hs1 = reinterpret_cast<const __half2*>(&s1);
-                                const __half2* hc2 = reinterpret_cast<const __half2*>(&c2);
-                                const __half2* hs2 = reinterpret_cast<const __half2*>(&s2);
-                                uint32_t o1[4], o2[4];
-#pragma unroll
-                                for (int j = 0; j < 4; ++j) {
-                                    const int i = v * 8 + j * 2;
-                                    __half2 x1 = __floats2half2_rn(__uint_as_float(a[i]), __uint_as_float(a[i + 1]));
-                                    __half2 x2 = __floats2half2_rn(__uint_as_float(b[i]), __uint_as_float(b[i + 1]));
-                                    if (rotate) {
-                                        const __half2 r1 = __hadd2_rn(__hmul2_rn(x1, hc1[j]), __hmul2_rn(__hneg2(x2), hs1[j]));
-                                        const __half2 r2 = __hadd2_rn(__hmul2_rn(x2, hc2[j]), __hmul2_rn(x1, hs2[j]));
-                                        x1 = r1, x2 = r2;
-                                    }
-                                    o1[j] = *reinterpret_cast<const uint32_t*>(&x1);
-                                    o2[j] = *reinterpret_cast<const uint32_t*>(&x2);
-                                }
-                                *stage_ptr(bufp(0), lane, c * 4 + v) = make_uint4(o1[0], o1[1], o1[2], o1[3]);
-                                *stage_ptr(bufp(1), lane, c * 4 + v) = make_uint4(o2[0], o2[1], o2[2], o2[3]);
-                            }
-                        }
-                        ptx::fence_proxy_async_smem();
-                        __syncwarp();
-                        if (lane == 0 && hcol < p.N) {
-                            ptx::tma_store_2d(&tmap_c, bufp(0), hcol, row0);
-                            ptx::tma_store_2d(&tmap_c, bufp(1), hcol + 64, row0);
-                            ptx::bulk_commit_group();
-                        }
-                    }
-                } else {
-                    float lse = 0.f;
-                    if constexpr (EPI == kEpiProbs) lse = row_ok ? p.lse[row] : 0.f;
-                    constexpr int N_CHUNKS = OUT_COLS / EPI_CHUNK_COLS;
-#pragma unroll 1
-                    for (int ch = 0; ch < N_CHUNKS; ++ch, ++q) {
-                        uint8_t* buf = bufp(q & 1);
-                        uint32_t r0[32], r1[32];  // SwiGLU: gate / up of 32 columns; else 2 x 32 columns
-#pragma unroll 1
-                        for (int half = 0; half < (EPI == kEpiSwiGLU ? 2 : 1); ++half) {
-                            if constexpr (EPI == kEpiSwiGLU) {
-                                ptx::tmem_ld_32x32(taddr + ch * 64 + half * 32, r0);
-                                ptx::tmem_ld_32x32(taddr + OUT_COLS + ch * 64 + half * 32, r1);
-                            } else {
-                                ptx::tmem_ld_32x32(taddr + ch * 64, r0);
-                                ptx::tmem_ld_32x32(taddr + ch * 64 + 32, r1);
-                            }
-                            if (half == 0) {
-                                if constexpr (EPI == kEpiResidual) {
-                                    if (lane == 0 && ch + 1 < N_CHUNKS) {  // next chunk's residual into the other buffer
-                                        ptx::bulk_wait_group_read<0>();
-                                        ptx::mbar_arrive_expect_tx(&rbar[(q + 1) & 1], EPI_BUF_BYTES);
-                                        ptx::tma_load_2d(bufp((q + 1) & 1), &tmap_r, &rbar[(q + 1) & 1],
-                                                         col0 + (ch + 1) * EPI_CHUNK_COLS, row0);
-                                    }
-                                } else {
-                                    if (lane == 0) ptx::bulk_wait_group_read<1>();  // the store two chunks back has read `buf`
-                                }
-                                __syncwarp();
-                            }
-                            ptx::tmem_ld_wait();
-                            if constexpr (EPI == kEpiResidual) ptx::mbar_wait(&rbar[q & 1], (q >> 1) & 1);
-                            if constexpr (EPI == kEpiSwiGLU) {
-                                // HF LlamaMLP: act_fn(gate_proj(x)) * up_proj(x), each op rounded to fp16.
-#pragma unroll
-                                for (int v = 0; v < 4; ++v) {
-                                    uint32_t o[4];
-#pragma unroll
-                                    for (int j = 0; j < 4; ++j) {
-                                        __half r2[2];
-#pragma unroll
-                                        for (int e = 0; e < 2; ++e) {
-                                            const int i = v * 8 + j * 2 + e;
-                                            const float gf = __half2float(__float2half_rn(__uint_as_float(r0[i])));
-                                            const __half sg = __float2half_rn(gf / (1.0f + expf(-gf)));
-                                            const __half uh = __float2half_rn(__uint_as_float(r1[i]));
-                                            r2[e] = __hmul(sg, uh);
-                                        }
-                                        o[j] = pack_h2(r2[0], r2[1]);
-                                    }
-                                    *stage_ptr(buf, lane, half * 4 + v) = make_uint4(o[0], o[1], o[2], o[3]);
-                                }
-                            } else {
-#pragma unroll
-                                for (int part = 0; part < 2; ++part) {
-                                    const uint32_t* r = part == 0 ? r0 : r1;
-#pragma unroll
-                                    for (int v = 0; v < 4; ++v) {
-                                        uint4* sp = stage_ptr(buf, lane, part * 4 + v);
-                                        uint4 res = make_uint4(0, 0, 0, 0);
-                                        if constexpr (EPI == kEpiResidual) res = *sp;
-                                        const uint32_t rr[4] = {res.x, res.y, res.z, res.w};
-                                        uint32_t o[4];
-#pragma unroll
-                                        for (int j = 0; j < 4; ++j) {
-                                            __half h0 = __float2half_rn(__uint_as_float(r[v * 8 + j * 2]));
-                                            __half h1 = __float2half_rn(__uint_as_float(r[v * 8 + j * 2 + 1]));
-                                            if constexpr (EPI == kEpiResidual) {
-                                                // hidden = residual + linear(x): fp16 add of two fp16 values
-                                                const __half2 rh = *reinterpret_cast<const __half2*>(&rr[j]);
-                                                h0 = __hadd(__low2half(rh), h0);
-                                                h1 = __hadd(__high2half(rh), h1);
-                                            } else if constexpr (EPI == kEpiProbs) {
-                                                // softmax evaluated on the fp16 logits (reference utils.py:289)
-                                                h0 = __float2half_rn(__expf(__half2float(h0) - lse));
-                                                h1 = __float2half_rn(__expf(__half2float(h1) - lse));
-                                            }
-                                            o[j] = pack_h2(h0, h1);
-                                        }
-                                        *sp = make_uint4(o[0], o[1], o[2], o[3]);
-                                    }
-                                }
-                            }
-                        }
-                        ptx::fence_proxy_async_smem();
-                        __syncwarp();
-                        if (lane == 0 && col0 + ch * EPI_CHUNK_COLS < p.N) {
-                            ptx::tma_store_2d(&tmap_c, buf, col0 + ch * EPI_CHUNK_COLS, row0);
-                            ptx::bulk_commit_group();
-                        }
-                    }
-                }
+                epi_accumulator<EPI>(p, &tmap_c, &tmap_r, taddr, row0, col0, buf_base, rbar, q, lane);
                 ptx::tc_fence_before_sync();
                 __syncwarp();
                 if (lane == 0) {
@@ -452,7 +224,7 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_con
             uint32_t acc_phase = 0;
             for (int tile = worker; tile < num_tiles; tile += n_workers) {
                 int m_blk, n_blk;
-                tile_coords(tile, p.num_m_blocks, p.num_n_blocks, p.group_m, m_blk, n_blk);
+                tile_coords(tile, p.num_m_blocks, p.num_n_blocks, p.group_m, p.raster, m_blk, n_blk);
                 ptx::mbar_wait(&tmem_full_bar[acc], acc_phase);
                 ptx::tc_fence_after_sync();
                 const int row = (m_blk * CG + static_cast<int>(cta_rank)) * BLOCK_M + ew * 32 + lane;
@@ -703,6 +475,7 @@ int launch_t(const GemmArgs& a, int num_sms, cudaStream_t stream) {
     p.partial = a.partial, p.lse = a.lse, p.up_off = a.up_off;
     p.group_m = a.group_m > 0 ? a.group_m : GROUP_M;
     p.cache_hints = a.cache_hints;
+    p.raster = a.raster;
     p.row_pos = a.row_pos, p.cos_tab = a.cos_tab, p.sin_tab = a.sin_tab, p.rope_cols = a.rope_cols;
     p.num_m_blocks = (a.M + BLOCK_M * CG - 1) / (BLOCK_M * CG);
     p.num_n_blocks = (a.N + OUT_COLS - 1) / OUT_COLS;
@@ -772,6 +545,7 @@ int gemm_init() {
     FLS_TRY(set_smem_attr<kEpiLsePartial>());
     FLS_TRY(set_smem_attr<kEpiProbs>());
     FLS_TRY(set_smem_attr<kEpiStoreRope>());
+    FLS_TRY(gemm_wide_init());
     return kOk;
 }
 
@@ -781,13 +555,18 @@ int gemm_launch(GemmEpilogue epi, const GemmArgs& a, int num_sms, cudaStream_t s
     if (a.K % 8 || a.N % 8) return fail(kErrInvalid, "gemm: N and K must be multiples of 8 (N=%d K=%d)", a.N, a.K);
     if (epi != kEpiLsePartial && (a.ldc % 8 || (reinterpret_cast<uintptr_t>(a.C) & 15)))
         return fail(kErrInvalid, "gemm: C must be 16-byte aligned with ldc %% 8 == 0");
+    const bool wide = a.wide && cta_group == 2 && !a.direct_store && gemm_wide_supports(epi);
     switch (epi) {
-        case kEpiStore: return launch_cg<kEpiStore>(a, num_sms, cta_group, stream);
+        case kEpiStore:
+            if (wide) return gemm_wide_launch(epi, a, num_sms, stream);
+            return launch_cg<kEpiStore>(a, num_sms, cta_group, stream);
         case kEpiResidual:
             if (!a.R || a.ldr % 8) return fail(kErrInvalid, "gemm: residual epilogue needs R with ldr %% 8 == 0");
+            if (wide) return gemm_wide_launch(epi, a, num_sms, stream);
             return launch_cg<kEpiResidual>(a, num_sms, cta_group, stream);
         case kEpiSwiGLU:
             if (a.b_rows < a.up_off + a.N) return fail(kErrInvalid, "gemm: SwiGLU needs gate and up rows in B");
+            if (wide) return gemm_wide_launch(epi, a, num_sms, stream);
             return launch_cg<kEpiSwiGLU>(a, num_sms, cta_group, stream);
         case kEpiLsePartial:
             if (!a.partial) return fail(kErrInvalid, "gemm: lse epilogue needs a partial buffer");
@@ -798,6 +577,7 @@ int gemm_launch(GemmEpilogue epi, const GemmArgs& a, int num_sms, cudaStream_t s
         case kEpiStoreRope:
             if (!a.row_pos || !a.cos_tab || !a.sin_tab || a.rope_cols % 128 || a.N % 128)
                 return fail(kErrInvalid, "gemm: rope epilogue needs positions, tables and 128-wide heads");
+            if (wide) return gemm_wide_launch(epi, a, num_sms, stream);
             return launch_cg<kEpiStoreRope>(a, num_sms, cta_group, stream);
     }
     return fail(kErrInvalid, "gemm: unknown epilogue %d", static_cast<int>(epi));

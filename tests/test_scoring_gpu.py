@@ -129,10 +129,10 @@ def test_kernel_variants_give_identical_scores(tiny_gqa):
     args = make_args(tiny_gqa["layer_dir"])
     model = ShardedLlama(args, DeviceManager(args, ["cuda:0"]), device="cuda:0")
     base = model(copy.deepcopy(tiny_gqa["prompts"]))
-    for opt, val in [(b"fuse_rope", 0), (b"gemm_cta_group", 1), (b"gemm_tma_store", 0)]:
+    for opt, val in [(b"fuse_rope", 0), (b"gemm_cta_group", 1), (b"gemm_tma_store", 0), (b"gemm_wide_tiles", 1)]:
         model.ctx.call("fls_set_option", opt, val)
         out = model(copy.deepcopy(tiny_gqa["prompts"]))
-        model.ctx.call("fls_set_option", opt, 2 if opt == b"gemm_cta_group" else 1)
+        model.ctx.call("fls_set_option", opt, 2 if opt in (b"gemm_cta_group", b"gemm_wide_tiles") else 1)
         for a, b in zip(out, base):
             assert np.array_equal(a, b), opt
     model.ctx.call("fls_set_option", b"attention_impl", 0)

@@ -20,8 +20,11 @@ ap = argparse.ArgumentParser()
 ap.add_argument("--models", nargs="+", default=["7b", "70b"])
 ap.add_argument("--secs", type=float, default=1.5)
 ap.add_argument("--groups", type=int, nargs="+", default=[16])
-ap.add_argument("--variants", nargs="+", default=["tma", "direct"])
+ap.add_argument("--variants", nargs="+", default=["wide", "narrow"],
+                help="wide (256x512 tiles) | narrow (256x256, TMA store) | direct (256x256, per-thread stores) | cg1")
 ap.add_argument("--rows", type=int, default=16384)
+ap.add_argument("--rasters", type=int, nargs="+", default=[0])
+ap.add_argument("--only", nargs="*", default=[], help="restrict to these classes (gemm_qkv gemm_o gemm_gate_up gemm_down)")
 ap.add_argument("--ncu", default="")
 ap.add_argument("--out", default="")
 a = ap.parse_args()
@@ -71,27 +74,45 @@ def launch(epi, A, B, Cm, brows, N, K):
 
 
 if a.ncu:
+    variant = a.variants[0]
+    ctx.call("fls_set_option", b"gemm_cta_group", 1 if variant == "cg1" else 2)
+    ctx.call("fls_set_option", b"gemm_tma_store", 0 if variant == "direct" else 1)
+    ctx.call("fls_set_option", b"gemm_wide_tiles", 1 if variant == "wide" else 0)
     for name, epi, N, K in shapes_of(a.ncu):
+        if a.only and name not in a.only:
+            continue
         A, B, Cm, brows = operands(epi, N, K)
-        launch(epi, A, B, Cm, brows, N, K)
-        torch.cuda.synchronize()
+        for r in a.rasters:
+            for g in a.groups:
+                ctx.call("fls_set_option", b"gemm_raster", r)
+                ctx.call("fls_set_option", b"gemm_group_m", g)
+                launch(epi, A, B, Cm, brows, N, K)
+                torch.cuda.synchronize()
+                print("launched", name, variant, "raster", r, "group", g, flush=True)
         del A, B, Cm
     sys.exit(0)
 
 results = {}
 for model in a.models:
     for name, epi, N, K in shapes_of(model):
+        if a.only and name not in a.only:
+            continue
         A, B, Cm, brows = operands(epi, N, K)
         flops = 2.0 * M * brows * K
         res = {}
         for variant in a.variants:
             ctx.call("fls_set_option", b"gemm_cta_group", 1 if variant == "cg1" else 2)
             ctx.call("fls_set_option", b"gemm_tma_store", 0 if variant == "direct" else 1)
-            for g in a.groups:
-                ctx.call("fls_set_option", b"gemm_group_m", g)
-                res[f"{variant}/group{g}"] = round(sustained(lambda: launch(epi, A, B, Cm, brows, N, K), flops))
+            ctx.call("fls_set_option", b"gemm_wide_tiles", 1 if variant == "wide" else 0)
+            for r in a.rasters:
+                ctx.call("fls_set_option", b"gemm_raster", r)
+                for g in a.groups:
+                    ctx.call("fls_set_option", b"gemm_group_m", g)
+                    res[f"{variant}/r{r}/group{g}"] = round(sustained(lambda: launch(epi, A, B, Cm, brows, N, K), flops))
+            ctx.call("fls_set_option", b"gemm_raster", 0)
         ctx.call("fls_set_option", b"gemm_cta_group", 2)
         ctx.call("fls_set_option", b"gemm_tma_store", 1)
+        ctx.call("fls_set_option", b"gemm_wide_tiles", 2)
         ctx.call("fls_set_option", b"gemm_group_m", 0)
         Bt = B.t()
         out = torch.empty((M, brows), dtype=torch.float16, device=dev)
