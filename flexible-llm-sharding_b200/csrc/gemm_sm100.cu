@@ -253,7 +253,7 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_con
                                         for (int e = 0; e < 2; ++e) {
                                             const int i = v * 8 + j * 2 + e;
                                             const float gf = __half2float(__float2half_rn(__uint_as_float(g[i])));
-                                            const __half s = __float2half_rn(gf / (1.0f + expf(-gf)));
+                                            const __half s = __float2half_rn(silu_f32(gf));
                                             const __half uh = __float2half_rn(__uint_as_float(u[i]));
                                             r2[e] = __hmul(s, uh);
                                         }

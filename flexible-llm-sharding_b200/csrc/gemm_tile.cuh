@@ -85,6 +85,14 @@ __device__ __forceinline__ void tile_coords(int tile, int num_m_blocks, int num_
     n_blk = by_n ? f : sl;
 }
 
+// silu(x) = x / (1 + e^-x) on the fp32 value of an fp16 gate, for the fused SwiGLU epilogues.  Hardware exp2 and
+// reciprocal approximations (2 MUFU operations, ~2 ulp of fp32): the fp16-rounded result equals the correctly rounded
+// one except where the fp32 value lies within a few 2^-24 of an fp16 rounding boundary (about one element in a
+// thousand, then off by one fp16 ulp) - the accurate expf + IEEE division cost ~100 issue slots per element and, in the
+// 256 x 512 kernel whose epilogue is not hidden behind the next tile's MMAs, a fifth of the tensor pipe's time
+// (profiles/r02_summary.md).  The stand-alone swiglu_kernel keeps the exact form.
+__device__ __forceinline__ float silu_f32(float x) { return __fdividef(x, 1.0f + __expf(-x)); }
+
 __device__ __forceinline__ uint32_t pack_h2(__half a, __half b) {
     __half2 h = __halves2half2(a, b);
     return *reinterpret_cast<uint32_t*>(&h);
@@ -223,7 +231,7 @@ __device__ __forceinline__ void epi_accumulator(const KParams& p, const CUtensor
                             for (int e = 0; e < 2; ++e) {
                                 const int i = v * 8 + j * 2 + e;
                                 const float gf = __half2float(__float2half_rn(__uint_as_float(r0[i])));
-                                const __half sg = __float2half_rn(gf / (1.0f + expf(-gf)));
+                                const __half sg = __float2half_rn(silu_f32(gf));
                                 const __half uh = __float2half_rn(__uint_as_float(r1[i]));
                                 r2[e] = __hmul(sg, uh);
                             }
