@@ -18,6 +18,7 @@ The JSON line (rank 0, last line of stdout):
         driver's `--steps 20 --warmup 5` cannot be spent on it (BASELINE.md section 6 has the time budget); the block
         carries its own roofline / path_roofline / e2e / weight-stream figures, the number of distinct decoder layers
         and the host bytes really page-locked.
+  dp_13b_k4 (N>1)  BASELINE.json configs[2]: Llama-2-13B, layer_num_per_shard=4, --data_parallel, 1024 prompts per rank.
   mp (N>1)         BASELINE.json configs[3]: the same 70B workload as ONE job over the N ranks - the reference's
         default model-parallel layer pipeline (shard j on rank j mod N, rows handed rank to rank over NVLink):
         strong scaling, with a tiny-model check that the N-rank pipeline returns the 1-GPU scores bit for bit.
@@ -501,6 +502,51 @@ def headline_block(a, pk, device, local, link_gbs):
     return blk
 
 
+# ------------------------------------------------------------------------------------------ 13B, k = 4, data parallel (N > 1)
+def c3_block(a, pk, device, local, rank, world, link_gbs):
+    """configs[2]: Llama-2-13B, layer_num_per_shard = 4, --data_parallel: every rank scores its own 1024 prompts.
+    The layer files lie on tmpfs and every rank page-locks the SAME pages, so the box holds one copy of the model."""
+    from flexible_llm_sharding_b200 import planner
+    from flexible_llm_sharding_b200.utils import DeviceManager, ShardedLlama
+    shape_name, n_prompts, prefix_tokens, n_options, option_tokens = WORKLOADS["13b-1024x512"]
+    shape = synthetic.LlamaShape.named(shape_name)
+    rows_per_prompt = prefix_tokens + n_options * option_tokens
+    md = model_dir_for(shape_name, rank, world, device, 0)
+    prompts = synthetic.make_prompts(n_prompts, shape.vocab_size, prefix_tokens, n_options, option_tokens,
+                                     seed=4321 + rank)
+    args = make_args(md, layer_num_per_shard=4, storage_location="gpu", max_rows=a.max_rows, pinned_limit_bytes=0,
+                     data_parallel=True)
+    model = ShardedLlama(args, DeviceManager(args, [str(device)]), device=str(device))
+    tok = planner.tokenize_prompts(model.tokenizer, prompts)
+    packed = planner.pack_prompts(tok, model.max_rows, model.max_head_rows, model.prefix_causal)
+    dt, prof, stats, clocks = timed_device_passes(model, packed, a.headline_steps, 1, world, device, local)
+    dt_step = dt / a.headline_steps
+    value = world * n_prompts / dt_step
+    with open("/proc/meminfo") as f:
+        shmem_kb = next((int(l.split()[1]) for l in f if l.startswith("Shmem:")), 0)
+    blk = {
+        "workload": f"Llama-2-13b arch random-init fp16, layer_num_per_shard=4, storage_location=gpu, {n_prompts} prompts "
+                    f"x {rows_per_prompt} token rows per GPU, --data_parallel over {world} GPUs (weak scaling)",
+        "metric": METRIC, "value": value, "unit": "prompts/s", "prefill_tok_per_s": value * rows_per_prompt,
+        "steps": a.headline_steps, "warmup": 1, "ms_per_step": 1e3 * dt_step, "scaling": "weak",
+        "roofline": gemm_roofline(prof, dt, a.headline_steps, pk, shape_name, a.max_rows),
+        "path_roofline": path_roofline(shape, n_prompts, n_options, rows_per_prompt, link_gbs, pk, dt_step, stats,
+                                       a.headline_steps),
+        "clocks_rank0": clocks, "model_bytes": model_bytes(shape),
+        "host_bytes_page_locked_per_rank": int(stats.pinned_bytes),
+        "of_which_file_pages_locked_in_place_per_rank": int(stats.mapped_bytes),
+        "box_shmem_bytes": shmem_kb * 1024,
+        "note": "every rank locks the same tmpfs pages: the box holds one copy of the model (box_shmem_bytes counts all "
+                "benchmark models lying in /dev/shm), not one per rank",
+    }
+    model.close()
+    del model
+    release_host_images()
+    if world > 1:
+        torch.distributed.barrier()
+    return blk if rank == 0 else None
+
+
 # ------------------------------------------------------------------------------------------ 70B layer pipeline (N > 1)
 def mp_block(a, pk, device, local, rank, world, link_gbs):
     """configs[3]: one 70B scoring job over all ranks as the reference's default model-parallel layer pipeline
@@ -753,11 +799,12 @@ def main():
     del model
     release_host_images()
 
-    headline = mp = None
+    headline = mp = c3 = None
     if not a.no_headline:
         if world == 1:
             headline = headline_block(a, pk, device, local, link_gbs)
         else:
+            c3 = c3_block(a, pk, device, local, rank, world, link_gbs)
             mp = mp_block(a, pk, device, local, rank, world, link_gbs)
 
     if rank != 0:
@@ -785,6 +832,8 @@ def main():
     }
     if headline is not None:
         line["headline"] = headline
+    if c3 is not None:
+        line["dp_13b_k4"] = c3
     if mp is not None:
         line["mp"] = mp
     print(json.dumps(line), flush=True)

@@ -55,7 +55,7 @@ class ModelDesc(C.Structure):
 class Stats(C.Structure):
     _fields_ = [("kernel_launches", C.c_uint64), ("h2d_bytes", C.c_uint64), ("h2d_ms", C.c_double),
                 ("file_bytes_read", C.c_uint64), ("pinned_bytes", C.c_uint64), ("workspace_bytes", C.c_uint64),
-                ("p2p_bytes", C.c_uint64), ("mapped_bytes", C.c_uint64)]
+                ("p2p_bytes", C.c_uint64), ("h2d_copies", C.c_uint64), ("mapped_bytes", C.c_uint64)]
 
 
 class KernelProfile(C.Structure):

@@ -115,7 +115,7 @@ struct fls_ctx {
     int gemm_cache_hints = 0;
     int gemm_raster = 0;
     int rmsnorm_variant = 0;
-    int fuse_rope = 1;  // 1 = rotary embedding in the QKV GEMM epilogue (head_dim 128), 0 = separate kernel
+    int fuse_rope = 1;  // rotary embedding in the QKV GEMM epilogue (head_dim 128): 1 = with 256 x 256 tiles, 2 = always, 0 = never
     int gemm_tma_store = 1;  // 1 = GEMM epilogues write through smem + TMA store, 0 = per-thread stores
     int gemm_wide = 2;       // 256 x 512 tiles per CTA pair: 0 never, 1 wherever the epilogue has the variant, 2 = when K >= 8192
     // cross-process hand-off: buffers this context exported (fls_ipc_alloc) and peers' buffers it mapped (fls_ipc_open)
@@ -481,7 +481,7 @@ int fls_register_layer_file(fls_ctx* c, int layer_idx, int kind, const char* pat
     L.kind = kind;
     L.path = path;
     size_t ds = 0, fs = 0;
-    CTX_TRY(c, parse_safetensors_header(L.path, &L.header, &ds, &fs));
+    CTX_TRY(c, parse_layer_header(L.path, &L.header, &ds, &fs));
     for (auto& t : L.header)
         if (t.dtype != "F16" && t.dtype != "BF16" && t.dtype != "F32")
             return ctx_fail(c, fail(kErrInvalid, "%s: tensor %s has dtype %s; int8/quantised weights are not supported",
@@ -619,6 +619,24 @@ int fls_prefetch_shard(fls_ctx* c, int slot, const int32_t* layer_ids, int n) {
         s.pins.push_back(L.img);
         L.img.reset();  // the slot keeps the image alive while its copies fly; afterwards the cache may evict it
     }
+    // Runs of copies that are contiguous on both sides (a packed layer file lies in slot order) become one range,
+    // re-cut into 32 MiB pieces.
+    {
+        std::vector<Slot::CopyOp> merged;
+        for (const Slot::CopyOp& op : s.pending_ops) {
+            if (!merged.empty() && merged.back().dst + merged.back().bytes == op.dst &&
+                merged.back().src + merged.back().bytes == op.src)
+                merged.back().bytes += op.bytes;
+            else
+                merged.push_back(op);
+        }
+        s.pending_ops.clear();
+        const size_t piece = size_t(32) << 20;
+        for (const Slot::CopyOp& op : merged)
+            for (size_t o = 0; o < op.bytes; o += piece)
+                s.pending_ops.push_back({op.dst + o, op.src + o, std::min(piece, op.bytes - o)});
+        c->stats.h2d_copies += s.pending_ops.size();
+    }
     timing.bytes = off;
     s.in_use = true;
     s.freed_valid = false;
@@ -747,7 +765,11 @@ int fls_decoder_layer_kv(fls_ctx* c, int slot, int layer_idx, uint16_t* x_dev, i
     a.A = c->xn, a.lda = Hd, a.B = r->dec.wqkv, a.ldb = Hd, a.b_rows = c->qkv_dim;
     __half* qkv_new = c->qkv + static_cast<size_t>(row0) * c->qkv_dim;     // where this call's rows go
     a.M = n_rows, a.N = c->qkv_dim, a.K = Hd, a.C = qkv_new, a.ldc = c->qkv_dim;
-    const bool fused_rope = c->fuse_rope && m.head_dim == 128;
+    // With 256 x 512 tiles the epilogue is not hidden behind the next tile's MMAs, and the rotary epilogue (a table
+    // row per thread) is the longest one: there the plain store + the stand-alone RoPE kernel is faster (70B layer:
+    // 184.8 vs 188.0 ms per 65536 rows, tools/layer_probe.py); with 256 x 256 tiles the fused form wins.
+    const bool wide_qkv = c->gemm_cg == 2 && c->gemm_tma_store && (c->gemm_wide == 1 || (c->gemm_wide == 2 && Hd >= 8192));
+    const bool fused_rope = m.head_dim == 128 && (c->fuse_rope == 2 || (c->fuse_rope == 1 && !wide_qkv));
     {
         ProfScope ps(c, FLS_PROF_GEMM_QKV, 2.0 * R * c->qkv_dim * Hd, st);
         if (fused_rope) {
@@ -1063,7 +1085,8 @@ int fls_set_option(fls_ctx* c, const char* name, int value) {
         return kOk;
     }
     if (strcmp(name, "fuse_rope") == 0) {
-        c->fuse_rope = value != 0;
+        if (value < 0 || value > 2) return ctx_fail(c, fail(kErrInvalid, "fuse_rope must be 0, 1 or 2"));
+        c->fuse_rope = value;
         return kOk;
     }
     if (strcmp(name, "attention_impl") == 0) {

@@ -328,6 +328,64 @@ int parse_safetensors_header(const std::string& path, std::vector<TensorEntry>* 
     return kOk;
 }
 
+namespace {
+bool is_pack_path(const std::string& path) {
+    static const char kExt[] = ".flspack";
+    return path.size() > sizeof(kExt) - 1 && path.compare(path.size() - (sizeof(kExt) - 1), sizeof(kExt) - 1, kExt) == 0;
+}
+}  // namespace
+
+// Packed layer file (prepare_weights.py --packed): 4096-byte header {"FLSPACK1", u32 kind, u32 n, u64 data_offset,
+// u64 data_bytes, n x {char name[96]; u64 rows, cols, offset, nbytes}}, then fp16 tensors, each 256-byte aligned, in
+// HBM slot order; data_bytes is a whole number of 4096-byte pages.
+int parse_pack_header(const std::string& path, std::vector<TensorEntry>* out, size_t* data_start, size_t* file_size) {
+    const int fd = open(path.c_str(), O_RDONLY);
+    if (fd < 0) return fail(kErrIo, "cannot open %s: %s", path.c_str(), strerror(errno));
+    struct stat st;
+    fstat(fd, &st);
+    unsigned char head[4096];
+    const ssize_t got = pread(fd, head, sizeof(head), 0);
+    close(fd);
+    uint32_t n = 0;
+    uint64_t data_off = 0, data_bytes = 0;
+    if (got == static_cast<ssize_t>(sizeof(head))) {
+        memcpy(&n, head + 12, 4);
+        memcpy(&data_off, head + 16, 8);
+        memcpy(&data_bytes, head + 24, 8);
+    }
+    if (got != static_cast<ssize_t>(sizeof(head)) || memcmp(head, "FLSPACK1", 8) != 0 || data_off != 4096 || n == 0 ||
+        n > 31 || data_off + data_bytes != static_cast<uint64_t>(st.st_size) || data_bytes % 4096)
+        return fail(kErrIo, "%s: not a packed layer file (bad header)", path.c_str());
+    for (uint32_t i = 0; i < n; ++i) {
+        const unsigned char* e = head + 32 + i * 128;
+        uint64_t rows, cols, off, nb;
+        memcpy(&rows, e + 96, 8);
+        memcpy(&cols, e + 104, 8);
+        memcpy(&off, e + 112, 8);
+        memcpy(&nb, e + 120, 8);
+        TensorEntry t;
+        t.name.assign(reinterpret_cast<const char*>(e), strnlen(reinterpret_cast<const char*>(e), 96));
+        t.dtype = "F16";
+        t.shape.push_back(static_cast<long long>(rows));
+        if (cols) t.shape.push_back(static_cast<long long>(cols));
+        t.numel = static_cast<size_t>(rows) * (cols ? cols : 1);
+        t.begin = off;
+        t.end = off + nb;
+        if (nb != t.numel * 2 || off % 256 || t.end > data_bytes)
+            return fail(kErrIo, "%s: tensor %s has an inconsistent entry in the packed header", path.c_str(),
+                        t.name.c_str());
+        out->push_back(std::move(t));
+    }
+    *data_start = data_off;
+    *file_size = static_cast<size_t>(st.st_size);
+    return kOk;
+}
+
+int parse_layer_header(const std::string& path, std::vector<TensorEntry>* out, size_t* data_start, size_t* file_size) {
+    return is_pack_path(path) ? parse_pack_header(path, out, data_start, file_size)
+                              : parse_safetensors_header(path, out, data_start, file_size);
+}
+
 int acquire_host_image(const std::string& path_in, std::shared_ptr<HostLayerImage>* out) {
     // key by the resolved path: symlinked layer files share one pinned image
     std::string path = path_in;
@@ -348,7 +406,8 @@ int acquire_host_image(const std::string& path_in, std::shared_ptr<HostLayerImag
     auto img = std::make_shared<HostLayerImage>();
     img->path = path;
     size_t data_start = 0, file_size = 0;
-    FLS_TRY(parse_safetensors_header(path, &img->tensors, &data_start, &file_size));
+    FLS_TRY(parse_layer_header(path, &img->tensors, &data_start, &file_size));
+    const bool packed = is_pack_path(path);
     size_t total = 0;
     bool all_f16 = true;
     for (auto& t : img->tensors) {
@@ -357,9 +416,10 @@ int acquire_host_image(const std::string& path_in, std::shared_ptr<HostLayerImag
                         "(int8 needs fp16 statistics, as in the reference)", path.c_str(), t.name.c_str(),
                         t.dtype.c_str());
         all_f16 = all_f16 && t.dtype == "F16" && t.end - t.begin == t.numel * 2 && (data_start + t.begin) % 2 == 0;
-        t.host_off = total;
+        t.host_off = packed ? t.begin : total;     // packed: the image IS the file's data section
         total += (t.numel * 2 + 255) & ~size_t(255);
     }
+    if (packed) total = file_size - data_start;
     const int mode = image_mode();
     bool mapped = false;
     if (mode != 1) {
@@ -387,6 +447,29 @@ int acquire_host_image(const std::string& path_in, std::shared_ptr<HostLayerImag
     img->pinned_bytes = total;
     g_pinned_bytes.fetch_add(total);
 
+    if (packed) {
+        // one page-aligned range straight into the page-locked buffer, past the page cache where the file system
+        // allows it (O_DIRECT; tmpfs does not)
+        int fd = open(path.c_str(), O_RDONLY | O_DIRECT);
+        const bool direct = fd >= 0;
+        if (!direct) fd = open(path.c_str(), O_RDONLY);
+        if (fd < 0) return fail(kErrIo, "cannot open %s: %s", path.c_str(), strerror(errno));
+        const int prc = parallel_pread(fd, img->pinned, data_start, total);
+        if (!direct) posix_fadvise(fd, 0, 0, POSIX_FADV_DONTNEED);
+        close(fd);
+        if (prc) return fail(kErrIo, "%s: short read of the packed data", path.c_str());
+        g_file_bytes.fetch_add(total);
+        std::lock_guard<std::mutex> lk(g_mu);
+        auto& slot = g_cache[path];
+        if (!slot.img) slot.img = img;
+        slot.last_use = ++g_clock;
+        *out = slot.img;
+    }
+    if (packed) {
+        img.reset();
+        if (const size_t lim = g_limit.load()) trim_host_cache(lim);
+        return kOk;
+    }
     const int fd = open(path.c_str(), O_RDONLY);
     if (fd < 0) return fail(kErrIo, "cannot open %s: %s", path.c_str(), strerror(errno));
     int rc = kOk;

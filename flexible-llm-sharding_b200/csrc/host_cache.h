@@ -41,6 +41,8 @@ struct HostLayerImage {
 
 int parse_safetensors_header(const std::string& path, std::vector<TensorEntry>* out, size_t* data_start,
                              size_t* file_size);
+// `<layer>.flspack` (prepare_weights.py --packed) or `<layer>.safetensors`, by extension
+int parse_layer_header(const std::string& path, std::vector<TensorEntry>* out, size_t* data_start, size_t* file_size);
 // Returns the cached image for `path`, reading the file on first use.
 int acquire_host_image(const std::string& path, std::shared_ptr<HostLayerImage>* out);
 // Evicts least-recently-used images nobody holds until at most keep_bytes remain; returns bytes held.

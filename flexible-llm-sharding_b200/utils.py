@@ -155,8 +155,15 @@ class ShardedLlama:
                               self.vocab, L, float(cfg.get("rms_norm_eps", 1e-6)))
         idx = self.torch_device.index if self.torch_device.index is not None else 0
         self.ctx = _lib.Context(desc, idx)
+        # `<layer>.flspack` (prepare_weights.py --packed) is preferred where it exists next to the reference layout
+        use_packed = str(getattr(args, "use_packed", os.environ.get("FLS_USE_PACKED", "1"))) not in ("0", "False")
+        self.layer_files = []
         for i, (name, kind) in enumerate(zip(self.layer_names, self.layer_kinds)):
             path = os.path.join(args.model_path, f"{name}.safetensors")
+            packed = os.path.join(args.model_path, f"{name}.flspack")
+            if use_packed and os.path.exists(packed):
+                path = packed
+            self.layer_files.append(path)
             self.ctx.call("fls_register_layer_file", i, kind, path.encode(), 0)
         self._layer_bytes = []
         for i in range(len(self.layer_names)):

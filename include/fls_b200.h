@@ -90,6 +90,7 @@ typedef struct fls_stats {
     uint64_t pinned_bytes;    /* pinned host bytes currently held (process-wide) */
     uint64_t workspace_bytes; /* HBM held by this context (slots + workspace) */
     uint64_t p2p_bytes;       /* activation bytes handed to other GPUs (fls_peer_copy) */
+    uint64_t h2d_copies;      /* cudaMemcpyAsync calls the weight stream was cut into */
     uint64_t mapped_bytes;    /* part of pinned_bytes that is file pages locked in place, shared with every
                                  other process that maps the same files (process-wide) */
 } fls_stats;
@@ -120,7 +121,9 @@ int fls_set_rope_table(fls_ctx* ctx, const uint16_t* cos_host, const uint16_t* s
  * header, raw tensors) and bind it to `layer_idx`.  The file is read into pinned memory at the
  * first prefetch that needs it (or now, if `load_now`).  F16 tensors are used as stored; BF16/F32
  * are converted to fp16 once on load (the reference casts to fp16 too, utils.py:130); integer
- * dtypes are rejected like utils.py:129. */
+ * dtypes are rejected like utils.py:129.  A path ending in `.flspack` names a packed layer file
+ * (prepare_weights.py --packed: the same tensors as fp16 in slot order behind a 4096-byte header); it is read as
+ * ONE page-aligned range (O_DIRECT from a disk, locked in place on tmpfs) and uploaded as one run of pieces. */
 int fls_register_layer_file(fls_ctx* ctx, int layer_idx, int kind, const char* path, int load_now);
 /* HBM bytes layer `layer_idx` needs in a slot. */
 int fls_layer_slot_bytes(fls_ctx* ctx, int layer_idx, size_t* out_bytes);
@@ -317,7 +320,8 @@ int fls_get_profile(fls_ctx* ctx, fls_kernel_profile* out);
 /* Tuning knobs.  "gemm_cta_group": 2 (default; CTA pairs share a 256x256 tile through
  * tcgen05 cta_group::2) or 1 (one CTA per 128x256 tile).  "attention_impl": 1 (default; tcgen05
  * kernel for head_dim 128) or 0 (mma.sync kernel).  "fuse_rope": 1 (default; rotary embedding applied in the
- * QKV GEMM epilogue when head_dim is 128) or 0 (separate kernel).  "paced_weight_stream": see fls_prefetch_pump.
+ * QKV GEMM epilogue when head_dim is 128 and the GEMM runs 256 x 256 tiles), 2 (also with 256 x 512 tiles) or 0
+ * (separate kernel).  "paced_weight_stream": see fls_prefetch_pump.
  * "gemm_wide_tiles": with cta_group 2, 256 x 512 tiles per CTA pair (one staged A slice feeds both TMEM
  * accumulators: a quarter less L2->SM traffic, fewer DRAM re-reads at large K; the epilogue no longer overlaps the
  * next tile's MMAs) - 2 (default) where K >= 8192, 1 wherever the epilogue has the variant, 0 never (256 x 256

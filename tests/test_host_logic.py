@@ -315,3 +315,38 @@ def test_raw_safetensors_writer_is_byte_identical_to_save_file(tmp_path):
                                                                              "model.layers.1.safetensors"]
     for fn in ("lm_head.safetensors", "model.layers.1.safetensors"):
         assert (a / fn).read_bytes() == (b / fn).read_bytes()
+
+
+def test_packed_layer_files_keep_the_reference_layout_and_slot_order(tmp_path):
+    """prepare_weights.py --packed: the reference layout is still written byte for byte; the
+    packed twin holds the same tensors as fp16, 256-byte aligned, in HBM slot order, in whole 4096-byte pages."""
+    import torch
+    from safetensors.torch import load_file
+    from flexible_llm_sharding_b200 import prepare_weights as PW, synthetic
+    shape = synthetic.LlamaShape.named("tiny-gqa", num_hidden_layers=2)
+    hf = tmp_path / "hf"
+    synthetic.write_hf_bin_checkpoint(str(hf), shape, seed=0, init_std=0.05)
+    plain, packed = tmp_path / "plain", tmp_path / "packed"
+    PW.split_into_layers(str(hf), str(plain))
+    PW.main([str(hf), str(packed), "--packed"])
+    for fn in sorted(os.listdir(plain)):
+        assert (plain / fn).read_bytes() == (packed / fn).read_bytes()
+    for layer in shape.layer_names():
+        sd = load_file(str(packed / f"{layer}.safetensors"))
+        entries = PW.read_packed_header(str(packed / f"{layer}.flspack"))
+        assert [e[0] for e in entries] == PW.pack_order(layer, sd)
+        size = os.path.getsize(packed / f"{layer}.flspack")
+        assert size % 4096 == 0
+        raw = (packed / f"{layer}.flspack").read_bytes()
+        prev_end = 0
+        for name, rows, cols, off, nb in entries:
+            assert off % 256 == 0 and off >= prev_end
+            want = sd[name].to(torch.float16).contiguous().numpy().tobytes()
+            assert raw[4096 + off:4096 + off + nb] == want and tuple(sd[name].shape) == ((rows, cols) if cols else (rows,))
+            prev_end = off + nb
+    # q|k|v and gate|up are adjacent: one GEMM operand each without repacking
+    e = {n.split(".", 3)[-1]: (off, nb) for n, _, _, off, nb in PW.read_packed_header(str(packed / "model.layers.1.flspack"))}
+    assert e["self_attn.k_proj.weight"][0] == sum(e["self_attn.q_proj.weight"])
+    assert e["mlp.up_proj.weight"][0] == sum(e["mlp.gate_proj.weight"])
+    with pytest.raises(ValueError, match="no place in the packed layout"):
+        PW.pack_order("model.layers.0", list(load_file(str(packed / "model.layers.0.safetensors"))) + ["model.layers.0.self_attn.q_proj.bias"])

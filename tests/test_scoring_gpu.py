@@ -439,3 +439,39 @@ def test_layer_files_are_locked_in_place_not_copied(tiny):
     _, base = run_model(tiny)                                  # auto mode on the disk copy of the same files
     for a, b, c in zip(outs["map"], outs["copy"], base):
         assert np.array_equal(a, b) and np.array_equal(a, c)
+
+
+@pytest.mark.parametrize("where", ["disk", "tmpfs"])
+def test_packed_layer_files_give_identical_scores(tiny_gqa, tmp_path, where):
+    """a directory that also holds `<layer>.flspack` files scores bit-identically, reads exactly the
+    packed bytes (one contiguous range per layer) and needs fewer, larger weight copies."""
+    import shutil
+    import tempfile
+    from flexible_llm_sharding_b200 import _lib, prepare_weights as PW
+    from flexible_llm_sharding_b200.utils import DeviceManager, ShardedLlama
+    if where == "tmpfs" and not os.path.isdir("/dev/shm"):
+        pytest.skip("no tmpfs")
+    base_dir = tempfile.mkdtemp(prefix="fls_test_pack_", dir="/dev/shm") if where == "tmpfs" else str(tmp_path)
+    d = os.path.join(base_dir, "layers")
+    shutil.copytree(tiny_gqa["layer_dir"], d)
+    try:
+        args = make_args(d, layer_num_per_shard=2)
+        plain = ShardedLlama(args, DeviceManager(args, ["cuda:0"]), device="cuda:0")
+        want = plain(copy.deepcopy(tiny_gqa["prompts"]))
+        copies_plain = plain.ctx.stats().h2d_copies
+        assert all(f.endswith(".safetensors") for f in plain.layer_files)
+        plain.close()
+        PW.pack_layer_dir(d)
+        model = ShardedLlama(args, DeviceManager(args, ["cuda:0"]), device="cuda:0")
+        assert all(f.endswith(".flspack") for f in model.layer_files)
+        got = model(copy.deepcopy(tiny_gqa["prompts"]))
+        st = model.ctx.stats()
+        for a, b in zip(got, want):
+            assert np.array_equal(a, b)
+        assert st.h2d_copies < copies_plain                    # 9 tensors per decoder layer became one range
+        if where == "tmpfs":
+            assert st.mapped_bytes > 0                         # locked in place, like the safetensors files
+        model.close()
+    finally:
+        if where == "tmpfs":
+            shutil.rmtree(base_dir, ignore_errors=True)
