@@ -46,6 +46,7 @@ import types
 
 ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, ROOT)
+T_START = time.perf_counter()
 
 import numpy as np  # noqa: E402
 import torch  # noqa: E402
@@ -477,15 +478,21 @@ def headline_block(a, pk, device, local, link_gbs):
     dt, prof, stats, clocks = timed_device_passes(model, packed, a.headline_steps, 0, 1, device, local)
     dt_step = dt / a.headline_steps
     value = n_prompts / dt_step
-    et, out, e2e = timed_e2e(model, prompts, 1, 1, device, warm=False)
-    assert len(out) == n_prompts and out[0].shape == (n_options, 1, shape.vocab_size)
+    # The end-to-end pass is a fourth minute-long pass: it is dropped (and said so) when the run is already long, so
+    # that the driver's per-run limit is never what ends this program.
+    spent = time.perf_counter() - T_START
+    if spent > float(os.environ.get("FLS_BENCH_E2E_CUTOFF_S", "650")):
+        et, e2e = None, {"skipped": f"run already {spent:.0f}s long"}
+    else:
+        et, out, e2e = timed_e2e(model, prompts, 1, 1, device, warm=False)
+        assert len(out) == n_prompts and out[0].shape == (n_options, 1, shape.vocab_size)
     blk = {
         "workload": f"Llama-2-70b arch random-init fp16, layer_num_per_shard=1, storage_location=gpu, {n_prompts} "
                     f"prompts x {rows_per_prompt} token rows (prefix {prefix_tokens} + {n_options} options x "
                     f"{option_tokens}), 1 GPU, every shard streamed from page-locked host memory every pass",
         "metric": METRIC, "value": value, "unit": "prompts/s", "prefill_tok_per_s": value * rows_per_prompt,
         "steps": a.headline_steps, "warmup": 1, "ms_per_step": 1e3 * dt_step,
-        "e2e": {"value": n_prompts / et, "unit": "prompts/s", "steps": 1, **e2e},
+        "e2e": {"value": n_prompts / et if et else None, "unit": "prompts/s", "steps": 1, **e2e},
         "roofline": gemm_roofline(prof, dt, a.headline_steps, pk, shape_name, a.max_rows),
         "path_roofline": path_roofline(shape, n_prompts, n_options, rows_per_prompt, link_gbs, pk, dt_step, stats,
                                        a.headline_steps),
