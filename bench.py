@@ -745,8 +745,9 @@ def main():
     torch.cuda.set_device(local)
     device = torch.device(f"cuda:{local}")
     if world > 1:
-        # NCCL_DEBUG is left as the caller set it (the driver reads NCCL's own lines); the JSON line is the LAST
-        # line this program prints
+        # NCCL_DEBUG is left as the caller set it, but NCCL's own lines (version banner, INFO) go to stderr unless the
+        # caller names a file: stdout carries exactly one line, the JSON
+        os.environ.setdefault("NCCL_DEBUG_FILE", "/dev/stderr")
         torch.distributed.init_process_group("nccl", device_id=device)
     import __graft_entry__ as ge
     if rank == 0:

@@ -21,7 +21,7 @@ ap.add_argument("--models", nargs="+", default=["7b", "70b"])
 ap.add_argument("--secs", type=float, default=1.5)
 ap.add_argument("--groups", type=int, nargs="+", default=[16])
 ap.add_argument("--variants", nargs="+", default=["wide", "narrow"],
-                help="wide (256x512 tiles) | narrow (256x256, TMA store) | direct (256x256, per-thread stores) | cg1")
+                help="auto (what a pass uses: wide where K >= 8192) | wide (256x512 tiles) | narrow (256x256, TMA store) | direct (256x256, per-thread stores) | cg1")
 ap.add_argument("--rows", type=int, default=16384)
 ap.add_argument("--rasters", type=int, nargs="+", default=[0])
 ap.add_argument("--only", nargs="*", default=[], help="restrict to these classes (gemm_qkv gemm_o gemm_gate_up gemm_down)")
@@ -77,7 +77,7 @@ if a.ncu:
     variant = a.variants[0]
     ctx.call("fls_set_option", b"gemm_cta_group", 1 if variant == "cg1" else 2)
     ctx.call("fls_set_option", b"gemm_tma_store", 0 if variant == "direct" else 1)
-    ctx.call("fls_set_option", b"gemm_wide_tiles", 1 if variant == "wide" else 0)
+    ctx.call("fls_set_option", b"gemm_wide_tiles", {"wide": 1, "auto": 2}.get(variant, 0))
     for name, epi, N, K in shapes_of(a.ncu):
         if a.only and name not in a.only:
             continue
@@ -103,7 +103,7 @@ for model in a.models:
         for variant in a.variants:
             ctx.call("fls_set_option", b"gemm_cta_group", 1 if variant == "cg1" else 2)
             ctx.call("fls_set_option", b"gemm_tma_store", 0 if variant == "direct" else 1)
-            ctx.call("fls_set_option", b"gemm_wide_tiles", 1 if variant == "wide" else 0)
+            ctx.call("fls_set_option", b"gemm_wide_tiles", {"wide": 1, "auto": 2}.get(variant, 0))
             for r in a.rasters:
                 ctx.call("fls_set_option", b"gemm_raster", r)
                 for g in a.groups:
