@@ -106,9 +106,19 @@ gemm_wide_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
                     // both CTAs' bytes are credited to the leader's barrier (peer bit cleared)
                     if (is_leader) ptx::mbar_arrive_expect_tx(&full_bar[stage], 2 * W_STAGE_BYTES);
                     const uint32_t bar = ptx::smem_u32(&full_bar[stage]) & 0xFEFFFFFFu;
-                    ptx::tma_load_2d_cta2(sa, &tmap_a, bar, kb * BLOCK_K, a_row);
-                    ptx::tma_load_2d_cta2(sa + A_BYTES, &tmap_b, bar, kb * BLOCK_K, b_row[0]);
-                    ptx::tma_load_2d_cta2(sa + A_BYTES + W_B_HALF_BYTES, &tmap_b, bar, kb * BLOCK_K, b_row[1]);
+                    if (p.cache_hints == 0) {
+                        ptx::tma_load_2d_cta2(sa, &tmap_a, bar, kb * BLOCK_K, a_row);
+                        ptx::tma_load_2d_cta2(sa + A_BYTES, &tmap_b, bar, kb * BLOCK_K, b_row[0]);
+                        ptx::tma_load_2d_cta2(sa + A_BYTES + W_B_HALF_BYTES, &tmap_b, bar, kb * BLOCK_K, b_row[1]);
+                    } else {  // L2 eviction-priority experiments (same encoding as gemm_sm100.cu)
+                        const uint64_t ha = p.cache_hints == 1 ? ptx::kL2EvictFirst
+                                            : p.cache_hints == 3 ? ptx::kL2EvictNormal : ptx::kL2EvictLast;
+                        const uint64_t hb = p.cache_hints == 2 ? ptx::kL2EvictFirst
+                                            : p.cache_hints == 4 ? ptx::kL2EvictNormal : ptx::kL2EvictLast;
+                        ptx::tma_load_2d_cta2_hint(sa, &tmap_a, bar, kb * BLOCK_K, a_row, ha);
+                        ptx::tma_load_2d_cta2_hint(sa + A_BYTES, &tmap_b, bar, kb * BLOCK_K, b_row[0], hb);
+                        ptx::tma_load_2d_cta2_hint(sa + A_BYTES + W_B_HALF_BYTES, &tmap_b, bar, kb * BLOCK_K, b_row[1], hb);
+                    }
                     if (++stage == W_STAGES) {
                         stage = 0;
                         phase ^= 1;
@@ -202,7 +212,7 @@ int launch_wide_t(const GemmArgs& a, int num_sms, cudaStream_t stream) {
     p.C = a.C, p.ldc = a.ldc, p.R = a.R, p.ldr = a.ldr;
     p.partial = a.partial, p.lse = a.lse, p.up_off = a.up_off;
     p.group_m = a.group_m > 0 ? a.group_m : GROUP_M;
-    p.cache_hints = 0;
+    p.cache_hints = a.cache_hints;
     p.raster = a.raster;
     p.row_pos = a.row_pos, p.cos_tab = a.cos_tab, p.sin_tab = a.sin_tab, p.rope_cols = a.rope_cols;
     p.num_m_blocks = (a.M + 2 * BLOCK_M - 1) / (2 * BLOCK_M);

@@ -24,6 +24,7 @@ ap.add_argument("--variants", nargs="+", default=["wide", "narrow"],
                 help="auto (what a pass uses: wide where K >= 8192) | wide (256x512 tiles) | narrow (256x256, TMA store) | direct (256x256, per-thread stores) | cg1")
 ap.add_argument("--rows", type=int, default=16384)
 ap.add_argument("--rasters", type=int, nargs="+", default=[0])
+ap.add_argument("--hints", type=int, nargs="+", default=[0], help="gemm_cache_hints values to sweep")
 ap.add_argument("--only", nargs="*", default=[], help="restrict to these classes (gemm_qkv gemm_o gemm_gate_up gemm_down)")
 ap.add_argument("--ncu", default="")
 ap.add_argument("--out", default="")
@@ -108,7 +109,11 @@ for model in a.models:
                 ctx.call("fls_set_option", b"gemm_raster", r)
                 for g in a.groups:
                     ctx.call("fls_set_option", b"gemm_group_m", g)
-                    res[f"{variant}/r{r}/group{g}"] = round(sustained(lambda: launch(epi, A, B, Cm, brows, N, K), flops))
+                    for h in a.hints:
+                        ctx.call("fls_set_option", b"gemm_cache_hints", h)
+                        res[f"{variant}/r{r}/group{g}" + (f"/hint{h}" if h else "")] = round(
+                            sustained(lambda: launch(epi, A, B, Cm, brows, N, K), flops))
+                    ctx.call("fls_set_option", b"gemm_cache_hints", 0)
             ctx.call("fls_set_option", b"gemm_raster", 0)
         ctx.call("fls_set_option", b"gemm_cta_group", 2)
         ctx.call("fls_set_option", b"gemm_tma_store", 1)
