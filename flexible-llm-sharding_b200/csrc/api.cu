@@ -117,6 +117,7 @@ struct fls_ctx {
     int rmsnorm_variant = 0;
     int fuse_rope = 1;  // rotary embedding in the QKV GEMM epilogue (head_dim 128): 1 = with 256 x 256 tiles, 2 = always, 0 = never
     int gemm_tma_store = 1;  // 1 = GEMM epilogues write through smem + TMA store, 0 = per-thread stores
+    int gemm_wide_lockstep = 0;  // 1: both accumulators of a wide tile advance in lock step (comparator)
     int gemm_wide = 2;       // 256 x 512 tiles per CTA pair: 0 never, 1 wherever the epilogue has the variant, 2 = when K >= 8192
     // cross-process hand-off: buffers this context exported (fls_ipc_alloc) and peers' buffers it mapped (fls_ipc_open)
     std::vector<void*> ipc_owned, ipc_mapped;
@@ -296,7 +297,7 @@ int head_impl(fls_ctx* c, const __half* x, const __half* W, int n_rows, int V, i
     const double flops = 2.0 * n_rows * V * K;
     {
         ProfScope ps(c, FLS_PROF_GEMM_HEAD, flops, st);
-        a.direct_store = !c->gemm_tma_store, a.wide = c->gemm_wide == 1 || (c->gemm_wide == 2 && a.K >= 8192);
+        a.direct_store = !c->gemm_tma_store, a.wide = (c->gemm_wide == 1 || (c->gemm_wide == 2 && a.K >= 8192)) ? (c->gemm_wide_lockstep ? 3 : 1) : 0;
         FLS_TRY(gemm_launch(kEpiLsePartial, a, c->num_sms, st, c->gemm_cg));
     }
     {
@@ -307,7 +308,7 @@ int head_impl(fls_ctx* c, const __half* x, const __half* W, int n_rows, int V, i
     if (probs) {
         a.C = probs, a.ldc = V, a.lse = c->lse;
         ProfScope ps(c, FLS_PROF_GEMM_HEAD, flops, st);
-        a.direct_store = !c->gemm_tma_store, a.wide = c->gemm_wide == 1 || (c->gemm_wide == 2 && a.K >= 8192);
+        a.direct_store = !c->gemm_tma_store, a.wide = (c->gemm_wide == 1 || (c->gemm_wide == 2 && a.K >= 8192)) ? (c->gemm_wide_lockstep ? 3 : 1) : 0;
         FLS_TRY(gemm_launch(kEpiProbs, a, c->num_sms, st, c->gemm_cg));
         c->stats.kernel_launches += 1;
     }
@@ -775,10 +776,10 @@ int fls_decoder_layer_kv(fls_ctx* c, int slot, int layer_idx, uint16_t* x_dev, i
         if (fused_rope) {
             a.row_pos = row_pos, a.cos_tab = c->rope_cos, a.sin_tab = c->rope_sin;
             a.rope_cols = c->q_dim + c->kv_dim;
-            a.direct_store = !c->gemm_tma_store, a.wide = c->gemm_wide == 1 || (c->gemm_wide == 2 && a.K >= 8192);
+            a.direct_store = !c->gemm_tma_store, a.wide = (c->gemm_wide == 1 || (c->gemm_wide == 2 && a.K >= 8192)) ? (c->gemm_wide_lockstep ? 3 : 1) : 0;
             CTX_TRY(c, gemm_launch(kEpiStoreRope, a, c->num_sms, st, c->gemm_cg));
         } else {
-            a.direct_store = !c->gemm_tma_store, a.wide = c->gemm_wide == 1 || (c->gemm_wide == 2 && a.K >= 8192);
+            a.direct_store = !c->gemm_tma_store, a.wide = (c->gemm_wide == 1 || (c->gemm_wide == 2 && a.K >= 8192)) ? (c->gemm_wide_lockstep ? 3 : 1) : 0;
             CTX_TRY(c, gemm_launch(kEpiStore, a, c->num_sms, st, c->gemm_cg));
         }
     }
@@ -806,7 +807,7 @@ int fls_decoder_layer_kv(fls_ctx* c, int slot, int layer_idx, uint16_t* x_dev, i
     a.M = n_rows, a.N = Hd, a.K = c->q_dim, a.C = x, a.ldc = Hd, a.R = x, a.ldr = Hd;
     {
         ProfScope ps(c, FLS_PROF_GEMM_O, 2.0 * R * Hd * c->q_dim, st);
-        a.direct_store = !c->gemm_tma_store, a.wide = c->gemm_wide == 1 || (c->gemm_wide == 2 && a.K >= 8192);
+        a.direct_store = !c->gemm_tma_store, a.wide = (c->gemm_wide == 1 || (c->gemm_wide == 2 && a.K >= 8192)) ? (c->gemm_wide_lockstep ? 3 : 1) : 0;
         CTX_TRY(c, gemm_launch(kEpiResidual, a, c->num_sms, st, c->gemm_cg));
     }
 
@@ -821,7 +822,7 @@ int fls_decoder_layer_kv(fls_ctx* c, int slot, int layer_idx, uint16_t* x_dev, i
     a.M = n_rows, a.N = I, a.K = Hd, a.C = c->hmid, a.ldc = I, a.up_off = I;
     {
         ProfScope ps(c, FLS_PROF_GEMM_GATE_UP, 2.0 * R * (2.0 * I) * Hd, st);
-        a.direct_store = !c->gemm_tma_store, a.wide = c->gemm_wide == 1 || (c->gemm_wide == 2 && a.K >= 8192);
+        a.direct_store = !c->gemm_tma_store, a.wide = (c->gemm_wide == 1 || (c->gemm_wide == 2 && a.K >= 8192)) ? (c->gemm_wide_lockstep ? 3 : 1) : 0;
         CTX_TRY(c, gemm_launch(kEpiSwiGLU, a, c->num_sms, st, c->gemm_cg));
     }
     a = GemmArgs{};
@@ -829,7 +830,7 @@ int fls_decoder_layer_kv(fls_ctx* c, int slot, int layer_idx, uint16_t* x_dev, i
     a.M = n_rows, a.N = Hd, a.K = I, a.C = x, a.ldc = Hd, a.R = x, a.ldr = Hd;
     {
         ProfScope ps(c, FLS_PROF_GEMM_DOWN, 2.0 * R * Hd * I, st);
-        a.direct_store = !c->gemm_tma_store, a.wide = c->gemm_wide == 1 || (c->gemm_wide == 2 && a.K >= 8192);
+        a.direct_store = !c->gemm_tma_store, a.wide = (c->gemm_wide == 1 || (c->gemm_wide == 2 && a.K >= 8192)) ? (c->gemm_wide_lockstep ? 3 : 1) : 0;
         CTX_TRY(c, gemm_launch(kEpiResidual, a, c->num_sms, st, c->gemm_cg));
     }
     c->stats.kernel_launches += fused_rope ? 7 : 8;
@@ -983,7 +984,7 @@ int fls_op_gemm(fls_ctx* c, int epilogue, const uint16_t* a_dev, int lda, const 
     a.group_m = c->gemm_group_m;
     a.cache_hints = c->gemm_cache_hints;
     a.raster = c->gemm_raster;
-    a.direct_store = !c->gemm_tma_store, a.wide = c->gemm_wide == 1 || (c->gemm_wide == 2 && a.K >= 8192);
+    a.direct_store = !c->gemm_tma_store, a.wide = (c->gemm_wide == 1 || (c->gemm_wide == 2 && a.K >= 8192)) ? (c->gemm_wide_lockstep ? 3 : 1) : 0;
     CTX_TRY(c, gemm_launch(static_cast<GemmEpilogue>(epilogue), a, c->num_sms, as_stream(stream), c->gemm_cg));
     c->stats.kernel_launches += 1;
     return kOk;
@@ -1073,6 +1074,10 @@ int fls_set_option(fls_ctx* c, const char* name, int value) {
     if (strcmp(name, "gemm_group_m") == 0) {
         if (value < 0 || value > 1024) return ctx_fail(c, fail(kErrInvalid, "gemm_group_m out of range"));
         c->gemm_group_m = value;
+        return kOk;
+    }
+    if (strcmp(name, "gemm_wide_lockstep") == 0) {
+        c->gemm_wide_lockstep = value != 0;
         return kOk;
     }
     if (strcmp(name, "gemm_wide_tiles") == 0) {

@@ -198,7 +198,194 @@ gemm_wide_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
     }
 }
 
+
+// ---------------------------------------------------------------------------------------------------------------------
+// Skewed form of the 256 x 512 tile: the two accumulators are fed by two INDEPENDENT MMA streams that share the A ring.
+// In the lock-step kernel above both accumulators finish together and the tensor pipe idles while the epilogue drains
+// them one after the other (5-10 % of a K = 8192 tile).  Here each accumulator has its own issuing thread, its own B
+// ring and its own full / empty barriers; an A slot is released when BOTH streams have used it.  The epilogue drains
+// accumulator 0 first, so stream 0 restarts first and from then on runs a few k-blocks ahead of stream 1 (as far as the
+// A ring lets it): at the end of a tile accumulator 0 is drained while stream 1 still multiplies, and accumulator 1
+// while stream 0 already works on the next tile - the tensor pipe always has one stream to run.
+//   warp 0   TMA producer: A ring (6 slots) + B ring of stream 0 (3 slots)
+//   warp 1   MMA stream 0 (leader CTA): accumulator columns [0, 256)
+//   warp 2   TMEM allocator, then TMA producer of stream 1's B ring (3 slots)
+//   warp 3   MMA stream 1 (leader CTA): accumulator columns [256, 512)
+//   warps 4-7 staged epilogue (gemm_tile.cuh), accumulator 0 then accumulator 1 of every tile
+constexpr int S_NA = 6;
+constexpr int S_NB = 3;
+constexpr int S_BLK_BYTES = BLOCK_M * BLOCK_K * 2;  // one 128 x 64 fp16 operand block: 16 KiB
+constexpr int S_SMEM_BYTES = (S_NA + 2 * S_NB) * S_BLK_BYTES + EPI_STAGE_BYTES + SMEM_BARRIER_BYTES + 1024;
+
 template <int EPI>
+__global__ void __launch_bounds__(NUM_THREADS, 1)
+gemm_wide_skew_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CUtensorMap tmap_b,
+                      const __grid_constant__ CUtensorMap tmap_c, const __grid_constant__ CUtensorMap tmap_r,
+                      const KParams p) {
+    extern __shared__ uint8_t smem_raw[];
+    uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+    uint8_t* a_ring = smem;
+    uint8_t* b_ring = smem + S_NA * S_BLK_BYTES;  // stream s: b_ring + s * S_NB * S_BLK_BYTES
+    uint8_t* epi_stage = b_ring + 2 * S_NB * S_BLK_BYTES;
+    uint64_t* a_full = reinterpret_cast<uint64_t*>(epi_stage + EPI_STAGE_BYTES);
+    uint64_t* a_empty = a_full + S_NA;
+    uint64_t* b_full = a_empty + S_NA;          // [2][S_NB]
+    uint64_t* b_empty = b_full + 2 * S_NB;      // [2][S_NB]
+    uint64_t* tmem_full_bar = b_empty + 2 * S_NB;   // [2]
+    uint64_t* tmem_empty_bar = tmem_full_bar + 2;   // [2]
+    uint64_t* res_bar = tmem_empty_bar + 2;         // [4 warps][2 buffers]
+    uint32_t* tmem_base_slot = reinterpret_cast<uint32_t*>(res_bar + 8);
+
+    const int warp_idx = threadIdx.x >> 5;
+    const int lane = threadIdx.x & 31;
+    const uint32_t cta_rank = ptx::cluster_ctarank();
+    const bool is_leader = cta_rank == 0;
+
+    if (warp_idx == 0 && ptx::elect_one()) {
+        ptx::prefetch_tensormap(&tmap_a);
+        ptx::prefetch_tensormap(&tmap_b);
+        ptx::prefetch_tensormap(&tmap_c);
+        if constexpr (EPI == kEpiResidual) ptx::prefetch_tensormap(&tmap_r);
+    }
+    if (warp_idx == 1 && ptx::elect_one()) {
+        for (int i = 0; i < S_NA; ++i) {
+            ptx::mbar_init(&a_full[i], 1);
+            ptx::mbar_init(&a_empty[i], 2);   // one tcgen05.commit from each MMA stream
+        }
+        for (int i = 0; i < 2 * S_NB; ++i) {
+            ptx::mbar_init(&b_full[i], 1);
+            ptx::mbar_init(&b_empty[i], 1);
+        }
+        for (int i = 0; i < 2; ++i) {
+            ptx::mbar_init(&tmem_full_bar[i], 1);
+            ptx::mbar_init(&tmem_empty_bar[i], 8);   // 4 epilogue warps of both CTAs
+        }
+        for (int i = 0; i < 8; ++i) ptx::mbar_init(&res_bar[i], 1);
+        ptx::fence_mbar_init();
+    }
+    if (warp_idx == 2) {
+        ptx::tmem_alloc<2>(tmem_base_slot, 512);
+        ptx::tmem_relinquish<2>();
+    }
+    ptx::tc_fence_before_sync();
+    ptx::cluster_sync_all();
+    ptx::tc_fence_after_sync();
+    const uint32_t tmem_base = *tmem_base_slot;
+
+    constexpr int OUT_COLS = out_cols_per_tile<EPI>();
+    const int num_tiles = p.num_m_blocks * p.num_n_blocks;
+    const int k_blocks = (p.K + BLOCK_K - 1) / BLOCK_K;
+    const int worker = blockIdx.x / 2, n_workers = gridDim.x / 2;
+
+    // first B row this CTA stages for accumulator t of the tile whose n block is n_blk
+    auto b_row_of = [&](int n_blk, int t) {
+        const int n256 = n_blk * 2 + t;
+        if constexpr (EPI == kEpiSwiGLU) return n256 * OUT_COLS + static_cast<int>(cta_rank) * p.up_off;
+        else return n256 * BLOCK_N + static_cast<int>(cta_rank) * (BLOCK_N / 2);
+    };
+
+    if (warp_idx == 0 || warp_idx == 2) {
+        // ------------------------------------------------------------------ TMA producers (both CTAs)
+        if (ptx::elect_one()) {
+            const int s = warp_idx >> 1;            // warp 0: A ring + stream 0's B ring; warp 2: stream 1's B ring
+            uint64_t* bf = b_full + s * S_NB;
+            uint64_t* be = b_empty + s * S_NB;
+            uint8_t* br = b_ring + s * S_NB * S_BLK_BYTES;
+            int ia = 0, ib = 0;
+            uint32_t pa = 0, pb = 0;
+            for (int tile = worker; tile < num_tiles; tile += n_workers) {
+                int m_blk, n_blk;
+                tile_coords(tile, p.num_m_blocks, p.num_n_blocks, p.group_m, p.raster, m_blk, n_blk);
+                const int a_row = (m_blk * 2 + static_cast<int>(cta_rank)) * BLOCK_M;
+                const int b_row = b_row_of(n_blk, s);
+                for (int kb = 0; kb < k_blocks; ++kb) {
+                    if (s == 0) {
+                        ptx::mbar_wait(&a_empty[ia], pa ^ 1);
+                        if (is_leader) ptx::mbar_arrive_expect_tx(&a_full[ia], 2 * S_BLK_BYTES);
+                        ptx::tma_load_2d_cta2(a_ring + ia * S_BLK_BYTES, &tmap_a, ptx::smem_u32(&a_full[ia]) & 0xFEFFFFFFu,
+                                              kb * BLOCK_K, a_row);
+                        if (++ia == S_NA) ia = 0, pa ^= 1;
+                    }
+                    ptx::mbar_wait(&be[ib], pb ^ 1);
+                    if (is_leader) ptx::mbar_arrive_expect_tx(&bf[ib], 2 * S_BLK_BYTES);
+                    ptx::tma_load_2d_cta2(br + ib * S_BLK_BYTES, &tmap_b, ptx::smem_u32(&bf[ib]) & 0xFEFFFFFFu, kb * BLOCK_K,
+                                          b_row);
+                    if (++ib == S_NB) ib = 0, pb ^= 1;
+                }
+            }
+        }
+    } else if (warp_idx == 1 || warp_idx == 3) {
+        // ------------------------------------------------------------------ MMA streams (leader CTA only)
+        if (is_leader && ptx::elect_one()) {
+            constexpr uint32_t idesc = ptx::umma_idesc_f16_f32(BLOCK_M * 2, BLOCK_N);
+            const int s = warp_idx >> 1;
+            uint64_t* bf = b_full + s * S_NB;
+            uint64_t* be = b_empty + s * S_NB;
+            const uint32_t br = ptx::smem_u32(b_ring + s * S_NB * S_BLK_BYTES);
+            const uint32_t ar = ptx::smem_u32(a_ring);
+            const uint32_t tmem_d = tmem_base + s * BLOCK_N;
+            int ia = 0, ib = 0;
+            uint32_t pa = 0, pb = 0, tphase = 0;
+            for (int tile = worker; tile < num_tiles; tile += n_workers) {
+                ptx::mbar_wait(&tmem_empty_bar[s], tphase ^ 1);   // the epilogue has read this accumulator
+                ptx::tc_fence_after_sync();
+                for (int kb = 0; kb < k_blocks; ++kb) {
+                    ptx::mbar_wait(&a_full[ia], pa);
+                    ptx::mbar_wait(&bf[ib], pb);
+                    ptx::tc_fence_after_sync();
+                    const uint64_t da = ptx::umma_smem_desc_sw128(ar + ia * S_BLK_BYTES);
+                    const uint64_t db = ptx::umma_smem_desc_sw128(br + ib * S_BLK_BYTES);
+#pragma unroll
+                    for (int k = 0; k < BLOCK_K / UMMA_K; ++k)
+                        ptx::umma_f16<2>(tmem_d, da + 2 * k, db + 2 * k, idesc, (kb | k) != 0);
+                    ptx::umma_commit_cta2(&a_empty[ia], 0b11);   // the A slot is free once BOTH streams have said so
+                    ptx::umma_commit_cta2(&be[ib], 0b11);
+                    if (++ia == S_NA) ia = 0, pa ^= 1;
+                    if (++ib == S_NB) ib = 0, pb ^= 1;
+                }
+                ptx::umma_commit_cta2(&tmem_full_bar[s], 0b11);
+                tphase ^= 1;
+            }
+        }
+    } else if (warp_idx >= EPI_WARP0) {
+        // ------------------------------------------------------------------ epilogue (both CTAs)
+        const int ew = warp_idx - EPI_WARP0;
+        uint8_t* const buf_base = epi_stage + (ew * 2) * EPI_BUF_BYTES;
+        uint64_t* rbar = res_bar + ew * 2;
+        uint32_t q = 0, tphase = 0;
+        for (int tile = worker; tile < num_tiles; tile += n_workers) {
+            int m_blk, n_blk;
+            tile_coords(tile, p.num_m_blocks, p.num_n_blocks, p.group_m, p.raster, m_blk, n_blk);
+            const int row0 = (m_blk * 2 + static_cast<int>(cta_rank)) * BLOCK_M + ew * 32;
+            const uint32_t taddr = tmem_base + (static_cast<uint32_t>(ew * 32) << 16);
+#pragma unroll 1
+            for (int t = 0; t < 2; ++t) {
+                const int col0 = (n_blk * 2 + t) * OUT_COLS;
+                const bool live = col0 < p.N;   // odd number of 256-column blocks: the last second accumulator is padding
+                if constexpr (EPI == kEpiResidual)
+                    if (live) epi_prefetch_residual(&tmap_r, buf_base, rbar, q, lane, col0, row0);
+                ptx::mbar_wait(&tmem_full_bar[t], tphase);
+                ptx::tc_fence_after_sync();
+                if (live) epi_accumulator<EPI>(p, &tmap_c, &tmap_r, taddr + t * BLOCK_N, row0, col0, buf_base, rbar, q, lane);
+                ptx::tc_fence_before_sync();
+                __syncwarp();
+                if (lane == 0) ptx::mbar_arrive_cluster(&tmem_empty_bar[t], 0);
+            }
+            tphase ^= 1;
+        }
+        if (lane == 0) ptx::bulk_wait_group_read<0>();
+    }
+
+    ptx::tc_fence_before_sync();
+    __syncwarp();
+    ptx::cluster_sync_all();
+    if (warp_idx == 2) {
+        ptx::tc_fence_after_sync();
+        ptx::tmem_dealloc<2>(tmem_base, 512);
+    }
+}
+
+template <int EPI, bool SKEW>
 int launch_wide_t(const GemmArgs& a, int num_sms, cudaStream_t stream) {
     constexpr int OUT_COLS = EPI == kEpiSwiGLU ? BLOCK_N / 2 : BLOCK_N;
     CUtensorMap tma, tmb, tmc, tmr;
@@ -222,7 +409,7 @@ int launch_wide_t(const GemmArgs& a, int num_sms, cudaStream_t stream) {
     cudaLaunchConfig_t cfg{};
     cfg.gridDim = dim3(workers * 2);
     cfg.blockDim = dim3(NUM_THREADS);
-    cfg.dynamicSmemBytes = W_SMEM_BYTES;
+    cfg.dynamicSmemBytes = SKEW ? S_SMEM_BYTES : W_SMEM_BYTES;
     cfg.stream = stream;
     cudaLaunchAttribute attr[1];
     attr[0].id = cudaLaunchAttributeClusterDimension;
@@ -231,13 +418,15 @@ int launch_wide_t(const GemmArgs& a, int num_sms, cudaStream_t stream) {
     attr[0].val.clusterDim.z = 1;
     cfg.attrs = attr;
     cfg.numAttrs = 1;
-    FLS_CUDA(cudaLaunchKernelEx(&cfg, gemm_wide_kernel<EPI>, tma, tmb, tmc, tmr, p));
+    if constexpr (SKEW) FLS_CUDA(cudaLaunchKernelEx(&cfg, gemm_wide_skew_kernel<EPI>, tma, tmb, tmc, tmr, p));
+    else FLS_CUDA(cudaLaunchKernelEx(&cfg, gemm_wide_kernel<EPI>, tma, tmb, tmc, tmr, p));
     return kOk;
 }
 
 template <int EPI>
 int set_wide_attr() {
     FLS_CUDA(cudaFuncSetAttribute(gemm_wide_kernel<EPI>, cudaFuncAttributeMaxDynamicSharedMemorySize, W_SMEM_BYTES));
+    FLS_CUDA(cudaFuncSetAttribute(gemm_wide_skew_kernel<EPI>, cudaFuncAttributeMaxDynamicSharedMemorySize, S_SMEM_BYTES));
     return kOk;
 }
 
@@ -256,11 +445,14 @@ bool gemm_wide_supports(GemmEpilogue epi) {
 }
 
 int gemm_wide_launch(GemmEpilogue epi, const GemmArgs& a, int num_sms, cudaStream_t stream) {
+    const bool skew = a.wide != 3;   // 3 = the lock-step form (comparator)
     switch (epi) {
-        case kEpiStore: return launch_wide_t<kEpiStore>(a, num_sms, stream);
-        case kEpiResidual: return launch_wide_t<kEpiResidual>(a, num_sms, stream);
-        case kEpiSwiGLU: return launch_wide_t<kEpiSwiGLU>(a, num_sms, stream);
-        case kEpiStoreRope: return launch_wide_t<kEpiStoreRope>(a, num_sms, stream);
+        case kEpiStore: return skew ? launch_wide_t<kEpiStore, true>(a, num_sms, stream) : launch_wide_t<kEpiStore, false>(a, num_sms, stream);
+        case kEpiResidual:
+            return skew ? launch_wide_t<kEpiResidual, true>(a, num_sms, stream) : launch_wide_t<kEpiResidual, false>(a, num_sms, stream);
+        case kEpiSwiGLU: return skew ? launch_wide_t<kEpiSwiGLU, true>(a, num_sms, stream) : launch_wide_t<kEpiSwiGLU, false>(a, num_sms, stream);
+        case kEpiStoreRope:
+            return skew ? launch_wide_t<kEpiStoreRope, true>(a, num_sms, stream) : launch_wide_t<kEpiStoreRope, false>(a, num_sms, stream);
         default: return fail(kErrInvalid, "gemm (wide tiles): epilogue %d has no wide variant", static_cast<int>(epi));
     }
 }

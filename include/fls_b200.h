@@ -325,7 +325,9 @@ int fls_get_profile(fls_ctx* ctx, fls_kernel_profile* out);
  * "gemm_wide_tiles": with cta_group 2, 256 x 512 tiles per CTA pair (one staged A slice feeds both TMEM
  * accumulators: a quarter less L2->SM traffic, fewer DRAM re-reads at large K; the epilogue no longer overlaps the
  * next tile's MMAs) - 2 (default) where K >= 8192, 1 wherever the epilogue has the variant, 0 never (256 x 256
- * tiles with two accumulator stages).  "gemm_raster" 0..3: tile order experiments (csrc/gemm_tile.cuh).
+ * tiles with two accumulator stages); "gemm_wide_lockstep" 1 = both accumulators of a wide tile advance in lock step
+ * (comparator; default 0 = two skewed MMA streams so that one accumulator's epilogue overlaps the other's MMAs).
+ * "gemm_raster" 0..3: tile order experiments (csrc/gemm_tile.cuh).
  * "gemm_tma_store": 1 (default; GEMM epilogues stage 32 x 64 sub-tiles in shared memory and write them with TMA
  * stores, the residual operand arrives by TMA load) or 0 (every thread stores 16-byte pieces of its own row).
  * "gemm_group_m", "gemm_cache_hints": raster group / L2 hint experiments (tools/gemm_probe.py), default 0;

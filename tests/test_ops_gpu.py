@@ -37,19 +37,22 @@ GEMM_SHAPES = [(128, 256, 64), (256, 512, 512), (200, 256, 128), (130, 1000, 512
                (4096, 2304, 512), (1000, 512, 1408), (257, 384, 72), (5000, 4096, 256)]
 
 
-@pytest.fixture(params=[(2, 1, 1), (2, 1, 0), (1, 1, 0), (2, 0, 0), (1, 0, 0)],
-                ids=["cta_group2-wide", "cta_group2", "cta_group1", "cta_group2-direct_store", "cta_group1-direct_store"])
+@pytest.fixture(params=[(2, 1, 1), (2, 1, 3), (2, 1, 0), (1, 1, 0), (2, 0, 0), (1, 0, 0)],
+                ids=["cta_group2-wide", "cta_group2-wide-lockstep", "cta_group2", "cta_group1", "cta_group2-direct_store",
+                     "cta_group1-direct_store"])
 def cta_group(request, env):
     """GEMM variants: CTA pairs (256 x 512 or 256 x 256 tiles) or single CTAs; epilogue through smem + TMA store
     (default) or per-thread stores."""
     cg, tma_store, wide = request.param
     env["ctx"].call("fls_set_option", b"gemm_cta_group", cg)
     env["ctx"].call("fls_set_option", b"gemm_tma_store", tma_store)
-    env["ctx"].call("fls_set_option", b"gemm_wide_tiles", wide)
+    env["ctx"].call("fls_set_option", b"gemm_wide_tiles", 1 if wide else 0)
+    env["ctx"].call("fls_set_option", b"gemm_wide_lockstep", 1 if wide == 3 else 0)
     yield cg
     env["ctx"].call("fls_set_option", b"gemm_cta_group", 2)
     env["ctx"].call("fls_set_option", b"gemm_tma_store", 1)
     env["ctx"].call("fls_set_option", b"gemm_wide_tiles", 2)
+    env["ctx"].call("fls_set_option", b"gemm_wide_lockstep", 0)
 
 
 @pytest.mark.parametrize("M,N,K", GEMM_SHAPES)

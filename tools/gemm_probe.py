@@ -21,7 +21,7 @@ ap.add_argument("--models", nargs="+", default=["7b", "70b"])
 ap.add_argument("--secs", type=float, default=1.5)
 ap.add_argument("--groups", type=int, nargs="+", default=[16])
 ap.add_argument("--variants", nargs="+", default=["wide", "narrow"],
-                help="auto (what a pass uses: wide where K >= 8192) | wide (256x512 tiles) | narrow (256x256, TMA store) | direct (256x256, per-thread stores) | cg1")
+                help="auto (what a pass uses: wide where K >= 8192) | wide (256x512 tiles, skewed streams) | lockstep (256x512, both accumulators in lock step) | narrow (256x256, TMA store) | direct (256x256, per-thread stores) | cg1")
 ap.add_argument("--rows", type=int, default=16384)
 ap.add_argument("--rasters", type=int, nargs="+", default=[0])
 ap.add_argument("--hints", type=int, nargs="+", default=[0], help="gemm_cache_hints values to sweep")
@@ -78,7 +78,8 @@ if a.ncu:
     variant = a.variants[0]
     ctx.call("fls_set_option", b"gemm_cta_group", 1 if variant == "cg1" else 2)
     ctx.call("fls_set_option", b"gemm_tma_store", 0 if variant == "direct" else 1)
-    ctx.call("fls_set_option", b"gemm_wide_tiles", {"wide": 1, "auto": 2}.get(variant, 0))
+    ctx.call("fls_set_option", b"gemm_wide_tiles", {"wide": 1, "lockstep": 1, "auto": 2}.get(variant, 0))
+    ctx.call("fls_set_option", b"gemm_wide_lockstep", 1 if variant == "lockstep" else 0)
     for name, epi, N, K in shapes_of(a.ncu):
         if a.only and name not in a.only:
             continue
@@ -104,7 +105,8 @@ for model in a.models:
         for variant in a.variants:
             ctx.call("fls_set_option", b"gemm_cta_group", 1 if variant == "cg1" else 2)
             ctx.call("fls_set_option", b"gemm_tma_store", 0 if variant == "direct" else 1)
-            ctx.call("fls_set_option", b"gemm_wide_tiles", {"wide": 1, "auto": 2}.get(variant, 0))
+            ctx.call("fls_set_option", b"gemm_wide_tiles", {"wide": 1, "lockstep": 1, "auto": 2}.get(variant, 0))
+            ctx.call("fls_set_option", b"gemm_wide_lockstep", 1 if variant == "lockstep" else 0)
             for r in a.rasters:
                 ctx.call("fls_set_option", b"gemm_raster", r)
                 for g in a.groups:
