@@ -90,6 +90,7 @@ _SIGNATURES = {
     "fls_set_host_cache_limit": (_I, [C.c_size_t]),
     "fls_trim_host_cache": (_I, [C.c_size_t]),
     "fls_set_host_image_mode": (_I, [_I]),
+    "fls_set_stage_dir": (_I, [C.c_char_p]),
     "fls_peer_copy": (_I, [_P, _P, _I, _P, C.c_size_t, _P]),
     "fls_ipc_alloc": (_I, [_P, C.c_size_t, C.POINTER(_P), _P]),
     "fls_ipc_free": (_I, [_P, _P]),

@@ -57,6 +57,7 @@ struct Slot {
         char* dst;
         const char* src;
         size_t bytes;
+        const void* image;   // host image the source lies in: ranges of different page-locked regions never merge
     };
     std::vector<CopyOp> pending_ops;
     size_t next_op = 0;
@@ -589,7 +590,7 @@ int fls_prefetch_shard(fls_ctx* c, int slot, const int32_t* layer_ids, int n) {
         // behind a whole shard
         const size_t total = t->numel * 2, piece = size_t(32) << 20;
         for (size_t o = 0; o < total; o += piece)
-            s.pending_ops.push_back({s.dev + off + o, img.pinned + t->host_off + o, std::min(piece, total - o)});
+            s.pending_ops.push_back({s.dev + off + o, img.pinned + t->host_off + o, std::min(piece, total - o), &img});
         *dst = reinterpret_cast<const __half*>(s.dev + off);
         off += align256(t->numel * 2);
         return kOk;
@@ -625,7 +626,7 @@ int fls_prefetch_shard(fls_ctx* c, int slot, const int32_t* layer_ids, int n) {
     {
         std::vector<Slot::CopyOp> merged;
         for (const Slot::CopyOp& op : s.pending_ops) {
-            if (!merged.empty() && merged.back().dst + merged.back().bytes == op.dst &&
+            if (!merged.empty() && merged.back().image == op.image && merged.back().dst + merged.back().bytes == op.dst &&
                 merged.back().src + merged.back().bytes == op.src)
                 merged.back().bytes += op.bytes;
             else
@@ -635,7 +636,7 @@ int fls_prefetch_shard(fls_ctx* c, int slot, const int32_t* layer_ids, int n) {
         const size_t piece = size_t(32) << 20;
         for (const Slot::CopyOp& op : merged)
             for (size_t o = 0; o < op.bytes; o += piece)
-                s.pending_ops.push_back({op.dst + o, op.src + o, std::min(piece, op.bytes - o)});
+                s.pending_ops.push_back({op.dst + o, op.src + o, std::min(piece, op.bytes - o), op.image});
         c->stats.h2d_copies += s.pending_ops.size();
     }
     timing.bytes = off;
@@ -701,6 +702,11 @@ int fls_set_host_cache_limit(size_t max_bytes) {
 int fls_set_host_image_mode(int mode) {
     if (mode < 0 || mode > 2) return fail(kErrInvalid, "fls_set_host_image_mode: mode %d (0 auto, 1 copy, 2 map)", mode);
     set_host_image_mode(mode);
+    return kOk;
+}
+
+int fls_set_stage_dir(const char* dir) {
+    set_stage_dir(dir);
     return kOk;
 }
 

@@ -17,6 +17,7 @@
 
 #include <algorithm>
 #include <atomic>
+#include <functional>
 #include <cstring>
 #include <mutex>
 #include <thread>
@@ -158,14 +159,97 @@ void prefault(const char* p, size_t n) {
     for (auto& t : th) t.join();
 }
 
+int parallel_pread(int fd, char* dst, size_t off, size_t n);
+
+std::mutex g_stage_mu;
+std::string g_stage_dir;   // empty = no staging
+
+// Copy of a disk-resident layer file in the staging directory (tmpfs), made once per BOX: the first process to get
+// there creates `<name>.lock`, copies the file (past the page cache where the file system allows) into `<name>.tmp`
+// and renames it to `<name>`; the others wait for `<name>` to appear.  The name carries the source's size and
+// modification time, so a changed source file is staged afresh.  Returns false (and says why) when staging is off, the
+// directory cannot take the file, or the copying process does not finish in time - the caller then copies privately.
+bool stage_file(const std::string& src, size_t file_size, std::string* staged, std::string* why) {
+    std::string dir;
+    {
+        std::lock_guard<std::mutex> lk(g_stage_mu);
+        dir = g_stage_dir;
+    }
+    if (dir.empty()) {
+        *why = "no staging directory";
+        return false;
+    }
+    struct stat st;
+    if (stat(src.c_str(), &st) != 0) {
+        *why = std::string("stat: ") + strerror(errno);
+        return false;
+    }
+    const size_t h = std::hash<std::string>()(src);
+    char name[160];
+    const char* base = strrchr(src.c_str(), '/');
+    snprintf(name, sizeof(name), "%016zx-%zu-%lld-%.80s", h, file_size, static_cast<long long>(st.st_mtime),
+             base ? base + 1 : src.c_str());
+    const std::string final_path = dir + "/" + name, lock_path = final_path + ".lock", tmp_path = final_path + ".tmp";
+    auto exists = [](const std::string& p) { struct stat s2; return stat(p.c_str(), &s2) == 0; };
+    if (exists(final_path)) {
+        *staged = final_path;
+        return true;
+    }
+    const int lock_fd = open(lock_path.c_str(), O_CREAT | O_EXCL | O_WRONLY, 0600);
+    if (lock_fd < 0) {
+        if (errno != EEXIST) {
+            *why = std::string("staging directory: ") + strerror(errno);
+            return false;
+        }
+        for (int i = 0; i < 6000; ++i) {   // another process is copying: up to 10 minutes
+            if (exists(final_path)) {
+                *staged = final_path;
+                return true;
+            }
+            if (!exists(lock_path)) break;   // it gave up
+            usleep(100000);
+        }
+        *why = "the process staging this file did not finish";
+        return false;
+    }
+    close(lock_fd);
+    bool ok = false;
+    const int out_fd = open(tmp_path.c_str(), O_CREAT | O_TRUNC | O_RDWR, 0600);
+    if (out_fd >= 0 && ftruncate(out_fd, static_cast<off_t>(file_size)) == 0) {
+        const size_t page = static_cast<size_t>(sysconf(_SC_PAGESIZE));
+        const size_t len = (file_size + page - 1) / page * page;
+        void* m = mmap(nullptr, len, PROT_READ | PROT_WRITE, MAP_SHARED, out_fd, 0);
+        if (m != MAP_FAILED) {
+            const int in_fd = open(src.c_str(), O_RDONLY);
+            if (in_fd >= 0) {
+                ok = parallel_pread(in_fd, static_cast<char*>(m), 0, file_size) == 0;
+                posix_fadvise(in_fd, 0, 0, POSIX_FADV_DONTNEED);   // tmpfs now holds the bytes: not twice in RAM
+                close(in_fd);
+                if (ok) g_file_bytes.fetch_add(file_size);
+            }
+            munmap(m, len);
+        }
+    }
+    if (out_fd >= 0) close(out_fd);
+    if (ok) ok = rename(tmp_path.c_str(), final_path.c_str()) == 0;
+    if (!ok) {
+        *why = std::string("copy into the staging directory failed: ") + strerror(errno);
+        unlink(tmp_path.c_str());
+    }
+    unlink(lock_path.c_str());
+    if (ok) *staged = final_path;
+    return ok;
+}
+
 // Tries to make `img` the mapped form of its file.  Returns true on success; false (with CUDA's error state
 // cleared) when the mapping or the registration is refused - the caller then falls back to the copied form.
-bool try_map_image(HostLayerImage* img, size_t data_start, size_t file_size, std::string* why) {
+bool try_map_image(HostLayerImage* img, const std::string& map_path, size_t data_start, size_t file_size,
+                   std::string* why) {
     // What this driver accepts (tools/hostreg_probe.cu, B200 box, driver 580): the mapping must be WRITABLE even for
     // a read-only registration, and file-backed MAP_SHARED pages are accepted on tmpfs (/dev/shm) only - on ext4
     // every MAP_SHARED variant is refused and MAP_PRIVATE works only by copying each page (no sharing, no saving).
     // So: open read-write, map shared, never write.  Anything else falls back to the copying path.
-    const int fd = open(img->path.c_str(), O_RDWR);
+    const int fd = open(map_path.c_str(), O_RDWR);
     if (fd < 0) {
         *why = std::string("open for mapping: ") + strerror(errno);
         return false;
@@ -194,7 +278,7 @@ bool try_map_image(HostLayerImage* img, size_t data_start, size_t file_size, std
     for (auto& t : img->tensors) t.host_off = t.begin;
     g_pinned_bytes.fetch_add(len);
     g_mapped_bytes.fetch_add(len);
-    g_file_bytes.fetch_add(file_size - data_start);
+    if (map_path == img->path) g_file_bytes.fetch_add(file_size - data_start);   // (a staged copy was counted when made)
     return true;
 }
 
@@ -424,7 +508,15 @@ int acquire_host_image(const std::string& path_in, std::shared_ptr<HostLayerImag
     bool mapped = false;
     if (mode != 1) {
         std::string why = "the file holds BF16/F32 tensors, which are converted on load";
-        mapped = all_f16 && try_map_image(img.get(), data_start, file_size, &why);
+        mapped = all_f16 && try_map_image(img.get(), path, data_start, file_size, &why);
+        if (!mapped && all_f16) {
+            // a file on a disk file system: one shared copy per box in the staging directory, if there is one
+            std::string staged, why_stage;
+            if (stage_file(path, file_size, &staged, &why_stage))
+                mapped = try_map_image(img.get(), staged, data_start, file_size, &why);
+            else if (why_stage != "no staging directory")
+                why += "; staging: " + why_stage;
+        }
         if (!mapped && mode == 2)
             return fail(kErrIo, "%s: cannot lock the file's pages in place (%s)", path.c_str(), why.c_str());
     }
@@ -537,6 +629,10 @@ size_t trim_host_cache(size_t keep_bytes) {
 uint64_t host_cache_file_bytes() { return g_file_bytes.load(); }
 uint64_t host_cache_pinned_bytes() { return g_pinned_bytes.load(); }
 uint64_t host_cache_mapped_bytes() { return g_mapped_bytes.load(); }
+void set_stage_dir(const char* dir) {
+    std::lock_guard<std::mutex> lk(g_stage_mu);
+    g_stage_dir = dir ? dir : "";
+}
 void set_host_image_mode(int mode) { g_image_mode.store(mode < 0 || mode > 2 ? 0 : mode); }
 
 }  // namespace fls

@@ -55,5 +55,8 @@ uint64_t host_cache_pinned_bytes();
 uint64_t host_cache_mapped_bytes();  // part of pinned_bytes that is file pages locked in place (no copy)
 // 0 = auto (map when the file allows it and the driver accepts, else copy), 1 = always copy, 2 = map or fail
 void set_host_image_mode(int mode);
+// Directory on tmpfs in which disk-resident F16 layer files are staged once per box and then locked in place by every
+// process (nullptr / "" = off).
+void set_stage_dir(const char* dir);
 
 }  // namespace fls

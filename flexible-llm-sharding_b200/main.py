@@ -111,6 +111,33 @@ def score_all(args, input_prompts, devices, device_manager=None):
     return run(devices[0], input_prompts)
 
 
+def setup_staging(args):
+    """Ranks that score the same model from a DISK directory would each hold their own pinned copy of every layer
+    (8 x 26 GB for 13B on 8 GPUs).  Only files on tmpfs can be page-locked in place and shared, so with --data_parallel
+    under torchrun the layer files are staged once per box in a tmpfs directory (`fls_set_stage_dir`) when it has
+    room: FLS_STAGE_DIR names it (then it is the user's to remove; "" switches staging off), otherwise
+    /dev/shm/fls_stage_<uid>_<port> is used and removed by local rank 0 at the end of main().  Returns the
+    directory this call created, else None."""
+    import shutil
+    from . import _lib
+    from .utils import _on_tmpfs
+    d, created = os.environ.get("FLS_STAGE_DIR"), None
+    if d is None and args.data_parallel and int(os.environ.get("WORLD_SIZE", "1")) > 1 \
+            and not _on_tmpfs(args.model_path) and os.path.isdir("/dev/shm"):
+        try:
+            need = sum(os.path.getsize(os.path.join(args.model_path, f)) for f in os.listdir(args.model_path)
+                       if f.endswith(".safetensors"))
+            free = shutil.disk_usage("/dev/shm").free
+        except OSError:
+            need, free = 1, 0
+        if need * 1.05 < free:
+            d = created = f"/dev/shm/fls_stage_{os.getuid()}_{os.environ.get('MASTER_PORT', '0')}"
+    if d:
+        os.makedirs(d, exist_ok=True)
+        _lib.load().fls_set_stage_dir(d.encode())
+    return created
+
+
 def distributed_device_manager(args):
     """DeviceManager of one torchrun rank (one process per GPU of one node).  --data_parallel: the process sees
     only its own GPU, as a one-device run.  Model parallel: `devices` lists every rank's GPU in rank order, so
@@ -174,7 +201,9 @@ def main(argv=None):
             raise SystemExit("no CUDA device visible: this implementation has no CPU path")
 
     from .utils import DeviceManager
+    stage_dir = None
     if distributed:
+        stage_dir = setup_staging(args)
         device_manager = distributed_device_manager(args)
     else:
         device_manager = DeviceManager(args, devices)          # created once, like main.py:61
@@ -211,6 +240,14 @@ def main(argv=None):
     args.prefix_kv_cache = kv_user
     for model in getattr(device_manager, "models", {}).values():
         model.drop_prefix_kv_cache()
+    if stage_dir is not None:                 # every rank is done with the staged files before they go
+        import shutil
+        import torch.distributed as dist
+        for model in getattr(device_manager, "models", {}).values():
+            model.close()
+        dist.barrier()
+        if int(os.environ.get("LOCAL_RANK", "0")) == 0:
+            shutil.rmtree(stage_dir, ignore_errors=True)
     if is_root:
         with open(args.prompt_pickle.replace(".pkl", "_updated.pkl"), "wb") as f:
             pickle.dump(input_prompts, f)

@@ -165,6 +165,13 @@ int fls_trim_host_cache(size_t keep_bytes);
  * the file's pages then dropped from the page cache).  1 (FLS_WEIGHT_IMAGE=copy): always copy.  2 (=map): map
  * or fail with FLS_ERR_IO. */
 int fls_set_host_image_mode(int mode);
+/* Staging directory (on tmpfs) for layer files that lie on a disk file system: the first process of the box that
+ * needs a file copies it there once (read past the page cache, lock file + atomic rename; the name carries the
+ * source's size and modification time), every process then locks THAT copy's pages in place - DeviceManager's "read
+ * each layer to RAM once and hand it to every GPU" (utils.py:35-41,67-75) for ranks that are processes.  NULL or ""
+ * switches staging off (default; each process then holds its own pinned copy).  The directory and its files are the
+ * caller's to remove. */
+int fls_set_stage_dir(const char* dir);
 
 /* ---------------------------------------------------------------------------------------------
  * layer compute on a resident shard.  `x_dev` etc. are fp16 [rows, hidden]. */

@@ -475,3 +475,52 @@ def test_packed_layer_files_give_identical_scores(tiny_gqa, tmp_path, where):
     finally:
         if where == "tmpfs":
             shutil.rmtree(base_dir, ignore_errors=True)
+
+
+def test_disk_resident_layers_are_staged_once_and_locked_in_place(tiny, tmp_path):
+    """Layer files on a disk file system cannot be page-locked in place; with a staging directory on tmpfs they are
+    copied there ONCE (the copy every process of the box then maps), and a later load finds the staged copy."""
+    import gc
+    import shutil
+    import tempfile
+    from flexible_llm_sharding_b200 import _lib
+    from flexible_llm_sharding_b200.utils import DeviceManager, ShardedLlama, _on_tmpfs
+    if not os.path.isdir("/dev/shm") or _on_tmpfs(tiny["layer_dir"]):
+        pytest.skip("needs a disk-resident layer directory and a tmpfs")
+    lib = _lib.load()
+    stage = tempfile.mkdtemp(prefix="fls_test_stage_", dir="/dev/shm")
+    gc.collect()
+    lib.fls_trim_host_cache(0)
+    first, base = run_model(tiny)                              # no staging: private pinned copies
+    first.close()                                              # (its weight slots hold on to the last images)
+    del first
+    gc.collect()
+    lib.fls_trim_host_cache(0)
+    try:
+        assert lib.fls_set_stage_dir(stage.encode()) == 0
+        args = make_args(tiny["layer_dir"])
+        model = ShardedLlama(args, DeviceManager(args, ["cuda:0"]), device="cuda:0")
+        s0 = model.ctx.stats()
+        out = model(copy.deepcopy(tiny["prompts"]))
+        s1 = model.ctx.stats()
+        assert s1.mapped_bytes - s0.mapped_bytes >= 0.9 * sum(model._layer_bytes)
+        staged = [f for f in os.listdir(stage) if f.endswith(".safetensors")]
+        assert len(staged) == len(model.layer_names) and not [f for f in os.listdir(stage) if f.endswith((".tmp", ".lock"))]
+        for a, b in zip(out, base):
+            assert np.array_equal(a, b)
+        model.close()
+        del model
+        gc.collect()
+        lib.fls_trim_host_cache(0)
+        model = ShardedLlama(args, DeviceManager(args, ["cuda:0"]), device="cuda:0")
+        r0 = model.ctx.stats().file_bytes_read
+        out2 = model(copy.deepcopy(tiny["prompts"]))
+        assert model.ctx.stats().file_bytes_read == r0         # the staged copies were found, nothing read again
+        for a, b in zip(out2, base):
+            assert np.array_equal(a, b)
+        model.close()
+    finally:
+        lib.fls_set_stage_dir(None)
+        gc.collect()
+        lib.fls_trim_host_cache(0)
+        shutil.rmtree(stage, ignore_errors=True)
