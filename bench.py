@@ -745,9 +745,8 @@ def main():
     torch.cuda.set_device(local)
     device = torch.device(f"cuda:{local}")
     if world > 1:
-        # NCCL_DEBUG is left as the caller set it, but NCCL's own lines (version banner, INFO) go to stderr unless the
-        # caller names a file: stdout carries exactly one line, the JSON
-        os.environ.setdefault("NCCL_DEBUG_FILE", "/dev/stderr")
+        # NCCL_DEBUG / NCCL_DEBUG_FILE are left exactly as the caller set them (the driver reads NCCL's own lines to
+        # count ranks); whatever NCCL prints comes first, the JSON line is the LAST line of stdout
         torch.distributed.init_process_group("nccl", device_id=device)
     import __graft_entry__ as ge
     if rank == 0:
