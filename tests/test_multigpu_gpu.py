@@ -1,6 +1,7 @@
 """Two-GPU runs (skipped on a one-GPU box): the in-process model-parallel layer pipeline with
 peer-to-peer hand-off and the data-parallel thread fan-out must return exactly the single-GPU scores."""
 import copy
+import os
 
 import numpy as np
 import pytest
@@ -144,3 +145,55 @@ def test_cross_process_pipeline_with_prefix_kv_cache(tiny_gqa):
         for a, b in zip(res[0][0][step], want[step]):
             assert np.array_equal(a, b), step
     assert [n[0] for n in res[0][1]] == ["save", "load", "load"] == [n[0] for n in res[1][1]]
+
+
+def _cli_worker(rank, world, port, argv, q):
+    import os
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port), RANK=str(rank), WORLD_SIZE=str(world),
+                      LOCAL_RANK=str(rank), LOCAL_WORLD_SIZE=str(world))
+    os.environ.pop("FLS_STAGE_DIR", None)
+    from flexible_llm_sharding_b200 import main as M
+    from flexible_llm_sharding_b200 import _lib
+    res = M.main(argv)
+    q.put((rank, None if res is None else len(res), _lib.load().fls_version()))
+    import torch.distributed as dist
+    dist.barrier()
+    dist.destroy_process_group()
+
+
+@pytest.mark.parametrize("data_parallel", [True, False])
+def test_torchrun_cli_on_two_gpus(tiny, tmp_path, data_parallel):
+    """`torchrun --nproc-per-node 2 main.py ...` as the user would run it: with --data_parallel the disk-resident
+    layer files are staged once on tmpfs (and the staging directory is gone afterwards), without it the two ranks form
+    the layer pipeline; the pickles rank 0 writes hold the single-GPU scores, bit for bit."""
+    _need_two()
+    import pickle
+    import socket
+    import torch.multiprocessing as mp
+    _, base = run_model(tiny)
+    pp, outp = tmp_path / "prompts.pkl", tmp_path / "scores.pkl"
+    with open(pp, "wb") as f:
+        pickle.dump(tiny["prompts"], f)
+    argv = ["--model_path", tiny["layer_dir"], "--prompt_pickle", str(pp), "--output_file", str(outp),
+            "--storage_location", "gpu", "--layer_num_per_shard", "2"] + (["--data_parallel", "True"] if data_parallel else [])
+    with socket.socket() as s:
+        s.bind(("127.0.0.1", 0))
+        port = s.getsockname()[1]
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    procs = [ctx.Process(target=_cli_worker, args=(r, 2, port, argv, q)) for r in range(2)]
+    for p in procs:
+        p.start()
+    res = dict()
+    for _ in range(2):
+        rank, n, _version = q.get(timeout=600)
+        res[rank] = n
+    for p in procs:
+        p.join(timeout=120)
+        assert p.exitcode == 0
+    assert res[0] == len(base) and res[1] is None
+    assert not os.path.isdir(f"/dev/shm/fls_stage_{os.getuid()}_{port}")     # the automatic staging directory is gone
+    with open(outp, "rb") as f:
+        scores = pickle.load(f)
+    for a, b in zip(scores, base):
+        assert np.array_equal(a[:, :1], b)
