@@ -192,7 +192,7 @@ class ActivationStore:
         """(prefix file, suffix file, first row in the micro-batch, len_p, S, len_s) per prompt."""
         for p in range(mb.prompt_lo, mb.prompt_hi):
             len_p, S, len_s = self.packed.shapes[p]
-            pf, sf = self._names(p)
+            pf, sf = self._names(self.packed.prompt_index(p))     # the reference's name: the caller's prompt index
             yield pf, sf, int(self.packed.prompt_row[p]) - mb.row_lo, len_p, S, len_s
 
     def _disk_save(self, mb, s: int, d2h_done):

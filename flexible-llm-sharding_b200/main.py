@@ -81,6 +81,9 @@ def build_parser() -> argparse.ArgumentParser:
     # also settable through the FLS_MAX_ROWS environment variable
     parser.add_argument("--max_rows", type=int, default=None,
                         help="token rows per micro-batch (default 16384); raise it for prompts with more rows")
+    # not a reference flag either (FLS_PACK_ORDER): how prompts are assigned to micro-batches; the scores do not change
+    parser.add_argument("--pack_order", choices=["length", "input"], default=None,
+                        help="length (default): balanced, longest-first micro-batches; input: in the order given")
     return parser
 
 

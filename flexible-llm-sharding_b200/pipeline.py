@@ -111,7 +111,8 @@ def _run(model, dm, inputs, shards, G, rank, serial, want_probs, answer_ids, ret
                 kv_note = "off (last pass)" if ask["policy"] == "last" else "skipped: no room on every rank"
     if rank == 0:
         packed = planner.pack_prompts(tok, model.max_rows, model.max_head_rows, model.prefix_causal,
-                                      cached_prefix=kv_mode == _lib.KV_LOAD) if tok else None
+                                      cached_prefix=kv_mode == _lib.KV_LOAD,
+                                      bucketed=model.pack_order == "length" and model._kv_policy() == "off") if tok else None
         _board_post(dm, ("packed", serial), packed)
     else:
         packed = _board_wait(dm, ("packed", serial))

@@ -266,7 +266,8 @@ def run_model_parallel_distributed(model, inputs, shards, G, rank, want_probs, a
             else:
                 kv_note = "off (last pass)" if ask["policy"] == "last" else "skipped: no room on every rank"
     packed = planner.pack_prompts(tok, model.max_rows, model.max_head_rows, model.prefix_causal,
-                                  cached_prefix=kv_mode == _lib.KV_LOAD)
+                                  cached_prefix=kv_mode == _lib.KV_LOAD,
+                                  bucketed=model.pack_order == "length" and model._kv_policy() == "off")
     t_tok = perf_counter() - t0
 
     model._configure(shards)

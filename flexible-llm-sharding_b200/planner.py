@@ -12,6 +12,7 @@ per-tile attention descriptors replacing the reference's per-prompt mask/KV-expa
 """
 from __future__ import annotations
 
+import heapq
 from dataclasses import dataclass, field
 
 import numpy as np
@@ -105,8 +106,10 @@ def tokenize_prompts(tokenizer, prompts) -> list[TokenizedPrompt]:
         backend.enable_truncation(max_length=MAX_TOKEN_LEN, stride=0, strategy="longest_first",
                                   direction=getattr(tokenizer, "truncation_side", "right"))
         backend.no_padding()
-        pre = [e.ids for e in backend.encode_batch(pre_txt, add_special_tokens=True)]
-        flat = [e.ids for e in backend.encode_batch(flat_txt, add_special_tokens=True)]
+        # `encode_batch_fast` (tokenizers >= 0.20) skips the character offsets nobody reads here: same ids, a third faster
+        encode = getattr(backend, "encode_batch_fast", None) or backend.encode_batch
+        pre = [e.ids for e in encode(pre_txt, add_special_tokens=True)]
+        flat = [e.ids for e in encode(flat_txt, add_special_tokens=True)]
     else:
         kw = dict(return_attention_mask=False, truncation=True, max_length=MAX_TOKEN_LEN)
         pre = tokenizer(pre_txt, **kw)["input_ids"]
@@ -151,11 +154,28 @@ class PackedPrompts:
     micro_batches: list[MicroBatch] = field(default_factory=list)
     cached_prefix: bool = False          # rows hold the options only; prefix K/V come from a cache (prefix_len rows)
     prefix_len: list[int] = field(default_factory=list)     # real prefix length of every prompt
+    # Every per-prompt field above is in PACKED order.  `order[p]` = the caller's index of the prompt packed at
+    # position p (None: packed in the caller's order); results are handed back through `head_range`.
+    order: np.ndarray | None = None
+    _position: np.ndarray | None = None
 
     @property
     def total_rows(self): return int(self.prompt_row[-1])
     @property
     def total_head_rows(self): return int(self.head_row[-1])
+
+    def prompt_index(self, p: int) -> int:
+        """The caller's index of the prompt at packed position `p`."""
+        return p if self.order is None else int(self.order[p])
+
+    def head_range(self, i: int) -> tuple[int, int]:
+        """Scored rows [lo, hi) of the caller's prompt `i`."""
+        if self.order is not None:
+            if self._position is None:
+                self._position = np.empty(len(self.order), dtype=np.int64)
+                self._position[self.order] = np.arange(len(self.order))
+            i = int(self._position[i])
+        return int(self.head_row[i]), int(self.head_row[i + 1])
 
 
 ATTN_PREFIX, ATTN_PREFIX_CAUSAL, ATTN_SUFFIX = 0, 1, 2
@@ -193,24 +213,91 @@ def prompt_tiles(base: int, len_p: int, S: int, len_s: int, prefix_causal: bool,
     return t
 
 
+def balanced_bins(tok: list[TokenizedPrompt], max_rows: int, max_head_rows: int) -> list[list[int]]:
+    """Length-bucketed assignment of prompts to micro-batches.  Packed rows carry no padding
+    between prompts, so bucketing by length cannot save rows here; what it buys on ragged data is BALANCE: the
+    fewest micro-batches the two caps allow, all about the same size (equal pipeline items across GPUs, no small
+    trailing launch), and inside a micro-batch the long prompts first, so the attention grid - dispatched in tile
+    order - ends on its cheapest tiles.  Longest-first into the emptiest micro-batch that still has room; another
+    micro-batch is opened only when a prompt fits none.  Ties keep the caller's order, so prompts of one common
+    shape come out exactly as the in-order packing puts them."""
+    n = len(tok)
+    rows = [t.rows for t in tok]
+    heads = [t.n_options for t in tok]
+    n_bins = max(1, -(-sum(rows) // max_rows), -(-sum(heads) // max_head_rows))
+    by_len = sorted(range(n), key=lambda i: -rows[i])              # stable: equal lengths stay in caller order
+    while True:
+        bins = [[] for _ in range(n_bins)]
+        n_heads = [0] * n_bins
+        heap = [(0, b) for b in range(n_bins)]                     # (rows held, micro-batch): emptiest on top
+        ok = True
+        for i in by_len:
+            aside = []                                             # emptier micro-batches whose head rows are used up
+            while heap and heap[0][0] + rows[i] <= max_rows and n_heads[heap[0][1]] + heads[i] > max_head_rows:
+                aside.append(heapq.heappop(heap))
+            if not heap or heap[0][0] + rows[i] > max_rows:        # the emptiest one left has no room: none has
+                ok = False
+                break
+            filled, b = heapq.heappop(heap)
+            bins[b].append(i)
+            n_heads[b] += heads[i]
+            heapq.heappush(heap, (filled + rows[i], b))
+            for item in aside:
+                heapq.heappush(heap, item)
+        if ok:
+            break
+        n_bins += 1
+        if n_bins > n:
+            raise ValueError(f"a prompt does not fit a micro-batch (max_rows {max_rows}, max_head_rows {max_head_rows})")
+    bins = [b for b in bins if b]
+    if all(rows[i] == rows[0] for i in range(n)):
+        # one common shape: the round-robin above deals prompts out like cards; hand them back as contiguous runs
+        flat, sizes = list(range(n)), [len(b) for b in bins]
+        bins, k = [], 0
+        for sz in sizes:
+            bins.append(flat[k:k + sz])
+            k += sz
+    else:
+        bins.sort(key=lambda b: min(b))                            # micro-batches in the order of their first prompt
+    return bins
+
+
 def pack_prompts(tok: list[TokenizedPrompt], max_rows: int, max_head_rows: int,
-                 prefix_causal: bool = False, cached_prefix: bool = False) -> PackedPrompts:
+                 prefix_causal: bool = False, cached_prefix: bool = False, bucketed: bool = False) -> PackedPrompts:
     """Packs the prompts' token rows and cuts them into micro-batches of <= max_rows rows.
     `cached_prefix`: only the option rows are packed (the prefix K/V of every layer come from a cache filled by
     an earlier pass over the same prefixes); a micro-batch's attention then works in the row space
-    [its prompts' cached prefix rows | its option rows], which is what max_rows bounds."""
+    [its prompts' cached prefix rows | its option rows], which is what max_rows bounds.
+    `bucketed`: prompts are assigned to micro-batches by `balanced_bins` instead of in the caller's order
+    (`PackedPrompts.order` / `head_range` map results back); not combined with the prefix cache, whose rows are
+    laid out in the order of the pass that filled it."""
+    order, ranges = None, None
+    if bucketed and not cached_prefix and len(tok) > 1:
+        for i, t in enumerate(tok):                                # same refusals, with the caller's prompt index
+            if t.rows > max_rows:
+                raise ValueError(f"prompt {i} has {t.rows} token rows; raise max_rows (currently {max_rows})")
+        bins = balanced_bins(tok, max_rows, max_head_rows)
+        flat = [i for b in bins for i in b]
+        if flat != list(range(len(tok))):
+            order = np.asarray(flat, dtype=np.int64)
+            tok = [tok[i] for i in flat]
+        ranges, k = [], 0
+        for b in bins:
+            ranges.append((k, k + len(b)))
+            k += len(b)
     n = len(tok)
     prompt_row = np.zeros(n + 1, dtype=np.int64)
     head_row = np.zeros(n + 1, dtype=np.int64)
     kv_row = np.zeros(n + 1, dtype=np.int64)
     for i, t in enumerate(tok):
+        who = i if order is None else int(order[i])
         if t.len_p + t.len_s > MAX_TOKEN_LEN:
             # the reference would fail slicing its 4096^2 mask (utils.py:276)
-            raise ValueError(f"prompt {i}: prefix + option length {t.len_p + t.len_s} exceeds {MAX_TOKEN_LEN}")
+            raise ValueError(f"prompt {who}: prefix + option length {t.len_p + t.len_s} exceeds {MAX_TOKEN_LEN}")
         if t.rows > max_rows:
-            raise ValueError(f"prompt {i} has {t.rows} token rows; raise max_rows (currently {max_rows})")
+            raise ValueError(f"prompt {who} has {t.rows} token rows; raise max_rows (currently {max_rows})")
         if t.len_s == 0:
-            raise ValueError(f"prompt {i}: every option is empty")
+            raise ValueError(f"prompt {who}: every option is empty")
         prompt_row[i + 1] = prompt_row[i] + (t.rows - t.len_p if cached_prefix else t.rows)
         head_row[i + 1] = head_row[i] + t.n_options
         kv_row[i + 1] = kv_row[i] + t.len_p
@@ -228,18 +315,22 @@ def pack_prompts(tok: list[TokenizedPrompt], max_rows: int, max_head_rows: int,
         row_pos[so:so + t.n_options * t.len_s] = np.tile(np.arange(t.len_p, t.len_p + t.len_s), t.n_options)
         shapes.append((0 if cached_prefix else t.len_p, t.n_options, t.len_s))
     packed = PackedPrompts(ids, row_pos, prompt_row, head_row, shapes, cached_prefix=cached_prefix,
-                           prefix_len=[t.len_p for t in tok])
+                           prefix_len=[t.len_p for t in tok], order=order)
 
     def space(lo, hi):      # rows of the attention workspace prompts [lo, hi) need
         return int(prompt_row[hi] - prompt_row[lo]) + (int(kv_row[hi] - kv_row[lo]) if cached_prefix else 0)
 
-    lo = 0
-    while lo < n:
-        hi = lo
-        while hi < n and space(lo, hi + 1) <= max_rows and head_row[hi + 1] - head_row[lo] <= max_head_rows:
-            hi += 1
-        if hi == lo:
-            raise ValueError(f"prompt {lo} does not fit a micro-batch (max_rows {max_rows}, max_head_rows {max_head_rows})")
+    if ranges is None:                                             # in order: each micro-batch takes what fits
+        ranges, lo = [], 0
+        while lo < n:
+            hi = lo
+            while hi < n and space(lo, hi + 1) <= max_rows and head_row[hi + 1] - head_row[lo] <= max_head_rows:
+                hi += 1
+            if hi == lo:
+                raise ValueError(f"prompt {lo} does not fit a micro-batch (max_rows {max_rows}, max_head_rows {max_head_rows})")
+            ranges.append((lo, hi))
+            lo = hi
+    for lo, hi in ranges:
         row_lo = int(prompt_row[lo])
         kv_lo, n_kv = int(kv_row[lo]), int(kv_row[hi] - kv_row[lo])
         tiles, gather, kv_rows = [], [], []
@@ -262,7 +353,6 @@ def pack_prompts(tok: list[TokenizedPrompt], max_rows: int, max_head_rows: int,
             lo, hi, row_lo, int(prompt_row[hi]) - row_lo, int(head_row[lo]), int(head_row[hi] - head_row[lo]),
             np.asarray(tiles, dtype=np.int32).reshape(-1, 8), np.asarray(gather, dtype=np.int32), kv_lo, n_kv,
             None if cached_prefix else (np.concatenate(kv_rows) if kv_rows else np.zeros(0, np.int32))))
-        lo = hi
     return packed
 
 

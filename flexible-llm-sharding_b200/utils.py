@@ -140,6 +140,11 @@ class ShardedLlama:
         self.max_head_rows = int(getattr(args, "max_head_rows", 4096))
         self.force_tier = bool(getattr(args, "force_storage_tier", False) or os.environ.get("FLS_FORCE_STORAGE"))
         self.hbm_activation_budget = getattr(args, "hbm_activation_budget", None)
+        # "length" = prompts go to micro-batches by planner.balanced_bins; "input" = in the
+        # caller's order.  Scores come back in the caller's order either way, bit for bit the same.
+        self.pack_order = str(getattr(args, "pack_order", None) or os.environ.get("FLS_PACK_ORDER", "length"))
+        if self.pack_order not in ("length", "input"):
+            raise ValueError(f"pack_order must be 'length' or 'input', not {self.pack_order!r}")
         # Weight residency: "auto" keeps every shard of this rank in HBM across calls when they
         # fit `resident_weight_fraction` of the free HBM (one slot per shard, streamed once); "never" always
         # streams through two slots like the reference re-loads per call; "always" insists.
@@ -303,7 +308,7 @@ class ShardedLlama:
             return []
         out = []
         for i in range(len(packed.shapes)):
-            lo, hi = int(packed.head_row[i]), int(packed.head_row[i + 1])
+            lo, hi = packed.head_range(i)
             out.append(np.expand_dims(probs[lo:hi], axis=1))
         return out
 
@@ -314,7 +319,7 @@ class ShardedLlama:
         lp, packed = self.run(inputs, want_probs=False, answer_ids=ids)
         if lp is None:
             return []
-        return [lp[int(packed.head_row[i]):int(packed.head_row[i + 1])] for i in range(len(packed.shapes))]
+        return [lp[slice(*packed.head_range(i))] for i in range(len(packed.shapes))]
 
     # ------------------------------------------------------------------ engine
     def _device_inputs(self, packed, dev, kv_mode=_lib.KV_NONE):
@@ -453,7 +458,14 @@ class ShardedLlama:
             from .pipeline import run_model_parallel
             return run_model_parallel(self, inputs, shards, num_gpu, rank, want_probs, answer_ids, return_device)
         t0 = perf_counter()
+        live = [s for s in shards if len(s)]
         if packed is None:
+            if len(inputs) and live:
+                # The first shard's weights (the embedding table) start their way to the GPU before the prompts are
+                # tokenised: the copy - and on a first pass the file read behind it - runs under the tokeniser.
+                with torch.cuda.device(self.torch_device):
+                    self._configure(shards)
+                    self._stage_shard(live, 0)
             tok = planner.tokenize_prompts(self.tokenizer, inputs)
             for i in range(len(inputs)):
                 inputs[i] = None                                  # utils.py:259
@@ -462,7 +474,8 @@ class ShardedLlama:
             self._configure(shards)
             kv_mode, kv_cache, kv_note, kv_sig = self._kv_plan(tok, range(len(self.layer_names)))
             packed = planner.pack_prompts(tok, self.max_rows, self.max_head_rows, self.prefix_causal,
-                                          cached_prefix=kv_mode == _lib.KV_LOAD)
+                                          cached_prefix=kv_mode == _lib.KV_LOAD,
+                                          bucketed=self.pack_order == "length" and self._kv_policy() == "off")
         elif packed.cached_prefix:
             raise ValueError("a pre-packed pass cannot use the prefix K/V cache")
         else:
@@ -482,7 +495,6 @@ class ShardedLlama:
                                     hbm_budget_bytes=self.hbm_activation_budget, force_tier=self.force_tier,
                                     pinned_pool=self._pinned_pool)
             out = self._alloc_outputs(packed, dev, want_probs, answer_ids)
-            live = [s for s in shards if len(s)]
             # Host/disk activation tiers copy rows host->device on the same copy engine as the weight stream, which
             # serves requests in arrival order: pace the stream (a slice per micro-batch) so those copies interleave.
             paced = store.tier != "gpu"

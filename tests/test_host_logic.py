@@ -350,3 +350,78 @@ def test_packed_layer_files_keep_the_reference_layout_and_slot_order(tmp_path):
     assert e["mlp.up_proj.weight"][0] == sum(e["mlp.gate_proj.weight"])
     with pytest.raises(ValueError, match="no place in the packed layout"):
         PW.pack_order("model.layers.0", list(load_file(str(packed / "model.layers.0.safetensors"))) + ["model.layers.0.self_attn.q_proj.bias"])
+
+
+def _ragged_shapes(n, seed):
+    rng = np.random.default_rng(seed)
+    return [(int(rng.integers(1, 900)), int(rng.integers(1, 6)), int(rng.integers(1, 60))) for _ in range(n)]
+
+
+@pytest.mark.parametrize("seed", [0, 1, 2])
+def test_length_bucketed_packing_is_a_balanced_permutation(seed):
+    """same prompts, same rows per prompt, fewer and more even micro-batches, long prompts first."""
+    shapes = _ragged_shapes(200, seed)
+    tok = _tok(shapes, seed)
+    plain = planner.pack_prompts(tok, max_rows=4096, max_head_rows=64)
+    buck = planner.pack_prompts(tok, max_rows=4096, max_head_rows=64, bucketed=True)
+    assert plain.order is None and buck.order is not None
+    assert sorted(buck.order.tolist()) == list(range(len(tok)))
+    assert buck.total_rows == plain.total_rows and buck.total_head_rows == plain.total_head_rows
+    # every prompt's token rows, positions and shape are the ones the in-order packing holds for it
+    for p, i in enumerate(buck.order.tolist()):
+        assert buck.shapes[p] == plain.shapes[i] and buck.prompt_index(p) == i
+        a, b = int(buck.prompt_row[p]), int(buck.prompt_row[p + 1])
+        c, d = int(plain.prompt_row[i]), int(plain.prompt_row[i + 1])
+        assert np.array_equal(buck.ids[a:b], plain.ids[c:d]) and np.array_equal(buck.row_pos[a:b], plain.row_pos[c:d])
+        lo, hi = buck.head_range(i)
+        assert (lo, hi) == (int(buck.head_row[p]), int(buck.head_row[p + 1])) and hi - lo == shapes[i][1]
+    # the gather rows point at the same tokens
+    def gathered(pk):
+        out = {}
+        for mb in pk.micro_batches:
+            k = 0
+            for p in range(mb.prompt_lo, mb.prompt_hi):
+                S = pk.shapes[p][1]
+                rows = mb.gather[k:k + S] + mb.row_lo - int(pk.prompt_row[p])
+                out[pk.prompt_index(p)] = rows.tolist()
+                k += S
+        return out
+    assert gathered(buck) == gathered(plain)
+    # caps hold, no more micro-batches than in order, and they are even: the spread is at most one prompt
+    sizes = [mb.n_rows for mb in buck.micro_batches]
+    assert all(mb.n_rows <= 4096 and mb.n_head <= 64 for mb in buck.micro_batches)
+    assert len(buck.micro_batches) <= len(plain.micro_batches)
+    assert max(sizes) - min(sizes) <= max(lp + S * ls for lp, S, ls in shapes)
+    plain_sizes = [mb.n_rows for mb in plain.micro_batches]
+    assert max(sizes) - min(sizes) <= max(plain_sizes) - min(plain_sizes)
+    for mb in buck.micro_batches:                      # longest first inside a micro-batch
+        rows = [sum(x * y for x, y in [(1, buck.shapes[p][0]), (buck.shapes[p][1], buck.shapes[p][2])])
+                for p in range(mb.prompt_lo, mb.prompt_hi)]
+        assert rows == sorted(rows, reverse=True)
+    # micro-batches still tile the packed rows
+    for a, b in zip(buck.micro_batches, buck.micro_batches[1:]):
+        assert a.prompt_hi == b.prompt_lo and a.row_lo + a.n_rows == b.row_lo and a.head_lo + a.n_head == b.head_lo
+
+
+def test_length_bucketed_packing_leaves_uniform_prompts_in_order():
+    tok = _tok([(384, 4, 32)] * 72)
+    buck = planner.pack_prompts(tok, max_rows=16384, max_head_rows=4096, bucketed=True)
+    assert buck.order is None                                        # nothing moved
+    assert [mb.prompt_hi - mb.prompt_lo for mb in buck.micro_batches] == [24, 24, 24]   # in order it would be 32, 32, 8
+    full = planner.pack_prompts(_tok([(384, 4, 32)] * 64), max_rows=16384, max_head_rows=4096, bucketed=True)
+    plain = planner.pack_prompts(_tok([(384, 4, 32)] * 64), max_rows=16384, max_head_rows=4096)
+    assert [(m.prompt_lo, m.prompt_hi) for m in full.micro_batches] == [(m.prompt_lo, m.prompt_hi) for m in plain.micro_batches]
+
+
+def test_length_bucketed_packing_limits_and_refusals():
+    # the head-row cap, not the row cap, decides the micro-batch count here
+    tok = _tok([(10, 5, 2)] * 7 + [(300, 1, 3)])
+    buck = planner.pack_prompts(tok, max_rows=1000, max_head_rows=10, bucketed=True)
+    assert all(mb.n_head <= 10 for mb in buck.micro_batches) and len(buck.micro_batches) == 4
+    with pytest.raises(ValueError, match="prompt 2 has"):
+        planner.pack_prompts(_tok([(10, 1, 2), (10, 1, 2), (500, 2, 10)]), max_rows=100, max_head_rows=6, bucketed=True)
+    # with a cached prefix the packing stays in the order of the pass that filled the cache
+    tok = _tok(_ragged_shapes(20, 5), 5)
+    assert planner.pack_prompts(tok, max_rows=4096, max_head_rows=64, cached_prefix=True, bucketed=True).order is None
+    # one prompt, and no prompts
+    assert planner.pack_prompts(tok[:1], max_rows=4096, max_head_rows=64, bucketed=True).order is None

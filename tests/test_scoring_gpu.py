@@ -95,6 +95,35 @@ def test_schedule_does_not_change_scores(tiny, k, storage, num_batch, max_rows, 
         assert not [f for f in os.listdir(tmp_path / "act") if f.endswith(".npy")]      # cleaned up
 
 
+@pytest.mark.parametrize("storage,max_rows", [("gpu", 400), ("cpu", 330), ("disk", 450), ("gpu", 16384)])
+def test_length_bucketed_packing_does_not_change_scores(tiny_gqa, storage, max_rows, tmp_path):
+    """assigning prompts to micro-batches by length (the default) instead of in the order given
+    moves rows between launches, nothing else - every prompt's scores are bit for bit the same, in the caller's order."""
+    from flexible_llm_sharding_b200 import planner
+    from flexible_llm_sharding_b200.utils import DeviceManager, ShardedLlama
+    prompts = list(tiny_gqa["prompts"]) + list(tiny_gqa["edge_prompts"])
+    outs, moved = {}, None
+    for order in ("input", "length"):
+        args = make_args(tiny_gqa["layer_dir"], storage_location=storage, max_rows=max_rows, force_storage_tier=True,
+                         disk_folder=str(tmp_path / f"act_{order}"), pack_order=order)
+        model = ShardedLlama(args, DeviceManager(args, ["cuda:0"]), device="cuda:0")
+        assert model.pack_order == order
+        probs, packed = model.run(copy.deepcopy(prompts))
+        outs[order] = [probs[slice(*packed.head_range(i))] for i in range(len(prompts))]
+        if order == "length":
+            moved = packed.order
+            tok = planner.tokenize_prompts(model.tokenizer, copy.deepcopy(prompts))
+            assert [packed.shapes[p] for p in range(len(tok))] == \
+                   [(tok[packed.prompt_index(p)].len_p, tok[packed.prompt_index(p)].n_options,
+                     tok[packed.prompt_index(p)].len_s) for p in range(len(tok))]
+        else:
+            assert packed.order is None
+        model.close()
+    assert moved is not None and sorted(moved.tolist()) == list(range(len(prompts)))   # the prompts really moved
+    for a, b in zip(outs["input"], outs["length"]):
+        assert a.shape == b.shape and np.array_equal(a, b)
+
+
 def test_disk_tier_writes_the_reference_file_layout(tiny, tmp_path, monkeypatch):
     """`storage_location=disk` keeps the reference's files (utils.py:171-177): `prefix{rank}-{idx:05d}.npy`
     [1, len_p, H] and `suffix…` [S, len_s, H], float16, one pair per prompt, loadable with plain np.load."""
