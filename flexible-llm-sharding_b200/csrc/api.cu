@@ -109,6 +109,7 @@ struct fls_ctx {
     unsigned long long peer_enabled_mask = 0;
     int gemm_cg = 2;  // tcgen05 cta_group of the GEMM kernels (2 = CTA pairs, 1 = single CTA)
     int attn_impl = 1;  // 1 = tcgen05 attention (head_dim 128), 0 = mma.sync attention
+    int attn_k_stages = 0;  // K buffers per CTA of the tcgen05 attention: 0 = chosen per device at init (3 where two CTAs fit an SM), 2, 3
     std::vector<cudaEvent_t> pace_events;
     size_t pace_next = 0;
     int paced_stream = 0;  // 1: fls_prefetch_shard only prepares the copies; fls_prefetch_pump enqueues them
@@ -282,7 +283,8 @@ inline __half* H(uint16_t* p) { return reinterpret_cast<__half*>(p); }
 int attention_dispatch(fls_ctx* c, const __half* qkv, int ld, int n_rows, int n_q_heads, int n_kv_heads, int head_dim,
                        const AttnTile* tiles, int n_tiles, __half* out, int ld_out, cudaStream_t st) {
     if (c->attn_impl == 1 && head_dim == 128)
-        return attention_sm100_launch(qkv, ld, n_rows, n_q_heads, n_kv_heads, tiles, n_tiles, out, ld_out, st);
+        return attention_sm100_launch(qkv, ld, n_rows, n_q_heads, n_kv_heads, tiles, n_tiles, out, ld_out, st,
+                                      c->attn_k_stages);
     return attention_launch(qkv, ld, n_q_heads, n_kv_heads, head_dim, tiles, n_tiles, out, ld_out, st);
 }
 
@@ -1103,6 +1105,12 @@ int fls_set_option(fls_ctx* c, const char* name, int value) {
     if (strcmp(name, "attention_impl") == 0) {
         if (value != 0 && value != 1) return ctx_fail(c, fail(kErrInvalid, "attention_impl must be 0 or 1"));
         c->attn_impl = value;
+        return kOk;
+    }
+    if (strcmp(name, "attention_k_stages") == 0) {
+        if (value != 0 && value != 2 && value != 3)
+            return ctx_fail(c, fail(kErrInvalid, "attention_k_stages must be 0 (this device's default), 2 or 3"));
+        c->attn_k_stages = value;
         return kOk;
     }
     return ctx_fail(c, fail(kErrInvalid, "fls_set_option: unknown option '%s'", name));

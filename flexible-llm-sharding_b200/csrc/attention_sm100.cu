@@ -4,9 +4,9 @@
 // reference's two eager attention calls per layer (reference utils.py:272 and :275-279).
 //
 // One CTA = one query tile (<= 128 rows) x one head, 192 threads:
-//   warp 0      TMA producer: Q tile once (2 x [128 x 64] sub-tiles, 128B swizzle), then K/V tiles of
-//               64 keys (K and V each 2 x [64 x 64] sub-tiles) through a 2-stage ring.  A key tile
-//               never straddles the two key segments (prefix rows / option rows).
+//   warp 0      TMA producer: Q tile once (2 x [128 x 64] sub-tiles, 128B swizzle), then K and V tiles of
+//               64 keys (each 2 x [64 x 64] sub-tiles) through two rings: NK = 3 buffers for K (which later
+//               hold P), 2 for V.  A key tile never straddles the two key segments (prefix rows / option rows).
 //   warp 1      MMA issuer (one elected thread):  S = Q K^T  (tcgen05.mma M128 N64 K16 x 8, K-major
 //               operands) into TMEM columns [0,64);  O += P V (M128 N128 K16 x 4, A = P K-major, B = V
 //               MN-major exactly as it lies in memory - no transpose) into TMEM columns [128,256).
@@ -17,9 +17,18 @@
 //               through the (by then dead) Q buffer and written as full 128-byte lines.
 // S is double buffered: Q K^T of tile j+1 is issued before P V of tile j, so it runs while the
 // softmax warps work on tile j.  `pv_done` tells the softmax warps when O may be rescaled/read.
-// Shared memory: Q 32 KiB + 2 stages x 32 KiB = 96 KiB -> two CTAs per SM, whose softmax and MMA
-// phases overlap; TMEM: 256 columns per CTA.
+// Why K and V have rings of their own: a K buffer is busy from its load until P V of its tile has retired (P is
+// written over K), so with K and V sharing two stages the load of tile j+2 could only start once softmax j had
+// finished, and its latency was exposed: the stall samples of `ncu` showed the softmax warps waiting for S 40 % of
+// their time (profiles/r02_summary.md).  A third K buffer lets K(j+2) arrive a whole softmax period earlier; V(j+2)
+// is not needed before P V of tile j+2 and does with two.
+// Shared memory: Q 32 KiB + 3 x 16 KiB + 2 x 16 KiB = 112 KiB -> still two CTAs per SM (exactly: the launch falls
+// back to NK = 2 where the driver says two do not fit), whose softmax and MMA phases overlap; TMEM: 256 columns.
 #include <cuda.h>
+
+#include <cstdio>
+#include <cstdlib>
+#include <mutex>
 
 #include "common.cuh"
 #include "ptx.cuh"
@@ -31,11 +40,17 @@ namespace {
 constexpr int D = 128;
 constexpr int BQ = 128;
 constexpr int BKV = 64;
-constexpr int KV_STAGES = 2;
+constexpr int V_STAGES = 2;
+constexpr int MAX_K_STAGES = 3;
 constexpr int Q_BYTES = BQ * D * 2;                  // 32 KiB: two [128 x 64] sub-tiles
 constexpr int KSUB_BYTES = BKV * 64 * 2;             // 8 KiB: one [64 keys x 64 d] sub-tile
-constexpr int STAGE_BYTES = 4 * KSUB_BYTES;          // K sub0, K sub1, V sub0, V sub1
-constexpr int SMEM_BYTES = Q_BYTES + KV_STAGES * STAGE_BYTES + 256 + 1024;
+constexpr int TILE_BYTES = 2 * KSUB_BYTES;           // one K (or P) tile, one V tile: sub0, sub1
+constexpr int BARRIER_BYTES = 256;
+// Shared memory a CTA uses, from the first 1 KiB boundary (the 128B swizzle needs it) of its dynamic allocation on.
+// Two CTAs per SM have 2 x 113 KiB between them: NK = 3 leaves 768 bytes for lining up, so the launch asks for what
+// the device's allocations really need (measured once by a probe kernel: 0 on B200) and the kernel traps if the
+// buffers would not fit what it was given.
+constexpr int smem_used(int nk) { return Q_BYTES + (nk + V_STAGES) * TILE_BYTES + BARRIER_BYTES; }
 constexpr int THREADS = 192;
 constexpr int TMEM_COLS = 256;
 constexpr int S_COL = 0, O_COL = 128;  // S: two buffers of 64 columns at 0 and 64; O: 128 columns
@@ -48,6 +63,7 @@ __device__ __forceinline__ float ex2_approx(float x) {  // 2^x, one MUFU op; 2^-
     return y;
 }
 
+template <int NK>
 __global__ void __launch_bounds__(THREADS, 2)
 attention_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant__ CUtensorMap tmap_kv,
                          int n_q_heads, int n_kv_heads, const AttnTile* __restrict__ tiles, __half* __restrict__ out,
@@ -55,15 +71,21 @@ attention_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_q, const __gri
     extern __shared__ uint8_t smem_raw[];
     uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
     uint8_t* sQ = smem;
-    uint8_t* sKV = smem + Q_BYTES;
-    uint64_t* q_full = reinterpret_cast<uint64_t*>(smem + Q_BYTES + KV_STAGES * STAGE_BYTES);
-    uint64_t* kv_full = q_full + 1;
-    uint64_t* kv_empty = kv_full + KV_STAGES;
-    uint64_t* s_full = kv_empty + KV_STAGES;   // [2]: S buffer b = tile & 1 is complete
+    uint8_t* sK = smem + Q_BYTES;                  // NK tiles: K(j), later P(j), in buffer j % NK
+    uint8_t* sV = sK + NK * TILE_BYTES;            // V(j) in buffer j % V_STAGES
+    uint64_t* q_full = reinterpret_cast<uint64_t*>(sV + V_STAGES * TILE_BYTES);
+    uint64_t* k_full = q_full + 1;
+    uint64_t* k_empty = k_full + MAX_K_STAGES;
+    uint64_t* v_full = k_empty + MAX_K_STAGES;
+    uint64_t* v_empty = v_full + V_STAGES;
+    uint64_t* s_full = v_empty + V_STAGES;     // [2]: S buffer b = tile & 1 is complete
     uint64_t* p_ready = s_full + 2;
     uint64_t* pv_done = p_ready + 1;           // O += P V of a tile has retired
     uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(pv_done + 1);
 
+    uint32_t dyn_bytes;
+    asm("mov.u32 %0, %%dynamic_smem_size;" : "=r"(dyn_bytes));
+    if (reinterpret_cast<uint8_t*>(tmem_slot + 1) > smem_raw + dyn_bytes) __trap();   // buffers do not fit
     const int warp_idx = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const AttnTile t = tiles[blockIdx.x];
     const int head = blockIdx.y;
@@ -83,9 +105,13 @@ attention_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_q, const __gri
             ptx::prefetch_tensormap(&tmap_q);
             ptx::prefetch_tensormap(&tmap_kv);
             ptx::mbar_init(q_full, 1);
-            for (int i = 0; i < KV_STAGES; ++i) {
-                ptx::mbar_init(&kv_full[i], 1);
-                ptx::mbar_init(&kv_empty[i], 1);
+            for (int i = 0; i < NK; ++i) {
+                ptx::mbar_init(&k_full[i], 1);
+                ptx::mbar_init(&k_empty[i], 1);
+            }
+            for (int i = 0; i < V_STAGES; ++i) {
+                ptx::mbar_init(&v_full[i], 1);
+                ptx::mbar_init(&v_empty[i], 1);
             }
             ptx::mbar_init(&s_full[0], 1);
             ptx::mbar_init(&s_full[1], 1);
@@ -108,16 +134,21 @@ attention_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_q, const __gri
             ptx::mbar_arrive_expect_tx(q_full, Q_BYTES);
             ptx::tma_load_2d(sQ, &tmap_q, q_full, q_col, t.q_row);
             ptx::tma_load_2d(sQ + Q_BYTES / 2, &tmap_q, q_full, q_col + 64, t.q_row);
+            // K(j) and V(j-1) wait for the same event when NK = 3 (P V of tile j-3 retired), K(j) and V(j) when
+            // NK = 2, so issuing the loads in this one order never holds a load back behind a later release.
             for (int j = 0; j < n_tiles; ++j) {
-                const int stage = j % KV_STAGES;
-                ptx::mbar_wait(&kv_empty[stage], ((j / KV_STAGES) & 1) ^ 1);
+                const int ks = j % NK, vs = j % V_STAGES;
                 const int row = j < n0 ? t.seg0_row + j * BKV : t.seg1_row + (j - n0) * BKV;
-                uint8_t* st = sKV + stage * STAGE_BYTES;
-                ptx::mbar_arrive_expect_tx(&kv_full[stage], STAGE_BYTES);
-                ptx::tma_load_2d(st, &tmap_kv, &kv_full[stage], k_col, row);
-                ptx::tma_load_2d(st + KSUB_BYTES, &tmap_kv, &kv_full[stage], k_col + 64, row);
-                ptx::tma_load_2d(st + 2 * KSUB_BYTES, &tmap_kv, &kv_full[stage], v_col, row);
-                ptx::tma_load_2d(st + 3 * KSUB_BYTES, &tmap_kv, &kv_full[stage], v_col + 64, row);
+                ptx::mbar_wait(&k_empty[ks], ((j / NK) & 1) ^ 1);
+                uint8_t* kb = sK + ks * TILE_BYTES;
+                ptx::mbar_arrive_expect_tx(&k_full[ks], TILE_BYTES);
+                ptx::tma_load_2d(kb, &tmap_kv, &k_full[ks], k_col, row);
+                ptx::tma_load_2d(kb + KSUB_BYTES, &tmap_kv, &k_full[ks], k_col + 64, row);
+                ptx::mbar_wait(&v_empty[vs], ((j / V_STAGES) & 1) ^ 1);
+                uint8_t* vb = sV + vs * TILE_BYTES;
+                ptx::mbar_arrive_expect_tx(&v_full[vs], TILE_BYTES);
+                ptx::tma_load_2d(vb, &tmap_kv, &v_full[vs], v_col, row);
+                ptx::tma_load_2d(vb + KSUB_BYTES, &tmap_kv, &v_full[vs], v_col + 64, row);
             }
         }
     } else if (warp_idx == 1) {
@@ -129,9 +160,9 @@ attention_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_q, const __gri
             ptx::mbar_wait(q_full, 0);
             // S(j) = Q K(j)^T into S buffer j & 1: d = 128 -> 8 K-steps, 4 per 64-wide sub-tile
             auto issue_qk = [&](int j) {
-                const int stage = j % KV_STAGES;
-                const uint32_t st = ptx::smem_u32(sKV + stage * STAGE_BYTES);
-                ptx::mbar_wait(&kv_full[stage], (j / KV_STAGES) & 1);
+                const int ks = j % NK;
+                const uint32_t st = ptx::smem_u32(sK + ks * TILE_BYTES);
+                ptx::mbar_wait(&k_full[ks], (j / NK) & 1);
                 ptx::tc_fence_after_sync();
 #pragma unroll
                 for (int k = 0; k < D / 16; ++k) {
@@ -145,19 +176,21 @@ attention_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_q, const __gri
             for (int j = 0; j < n_tiles; ++j) {
                 // the next tile's scores are computed while the softmax warps work on this one
                 if (j + 1 < n_tiles) issue_qk(j + 1);
-                const int stage = j % KV_STAGES;
-                const uint32_t st = ptx::smem_u32(sKV + stage * STAGE_BYTES);
+                const int ks = j % NK, vs = j % V_STAGES;
+                const uint32_t st = ptx::smem_u32(sK + ks * TILE_BYTES);
+                const uint32_t vt = ptx::smem_u32(sV + vs * TILE_BYTES);
                 // O += P V : P (fp16, K-major) now lies where K(j) was; V is MN-major as loaded
+                ptx::mbar_wait(&v_full[vs], (j / V_STAGES) & 1);
                 ptx::mbar_wait(p_ready, j & 1);
                 ptx::tc_fence_after_sync();
 #pragma unroll
                 for (int k = 0; k < BKV / 16; ++k) {
                     const uint64_t da = ptx::umma_smem_desc_sw128(st) + 2 * k;
-                    const uint64_t db =
-                        ptx::umma_smem_desc_sw128_mn(st + 2 * KSUB_BYTES + k * 16 * 128, KSUB_BYTES, 1024);
+                    const uint64_t db = ptx::umma_smem_desc_sw128_mn(vt + k * 16 * 128, KSUB_BYTES, 1024);
                     ptx::umma_f16<1>(tmem_base + O_COL, da, db, idesc_pv, (j | k) != 0);
                 }
-                ptx::umma_commit(&kv_empty[stage]);
+                ptx::umma_commit(&k_empty[ks]);
+                ptx::umma_commit(&v_empty[vs]);
                 ptx::umma_commit(pv_done);
             }
         }
@@ -178,7 +211,7 @@ attention_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_q, const __gri
         float m_run = -INFINITY, l_run = 0.f;
         const float thr = RESCALE_THRESHOLD / scale_log2e;
         for (int j = 0; j < n_tiles; ++j) {
-            const int stage = j % KV_STAGES;
+            const int ks = j % NK;
             ptx::mbar_wait(&s_full[j & 1], (j >> 1) & 1);
             ptx::tc_fence_after_sync();
             uint32_t sr[2][32];
@@ -237,7 +270,7 @@ attention_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_q, const __gri
                 }
             }
             // P -> shared memory over the (dead) K tile: [128 rows][64 keys] fp16, 128B swizzle
-            uint8_t* sp = sKV + stage * STAGE_BYTES + i * 128;
+            uint8_t* sp = sK + ks * TILE_BYTES + i * 128;
 #pragma unroll
             for (int c = 0; c < 8; ++c)
                 *reinterpret_cast<uint4*>(sp + ((c ^ (i & 7)) << 4)) =
@@ -298,28 +331,93 @@ attention_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_q, const __gri
     }
 }
 
-}  // namespace
+// Offset of a launch's dynamic shared memory from the next 1 KiB boundary (no static shared memory, as above).
+__global__ void smem_base_probe_kernel(uint32_t* misalign) {
+    extern __shared__ uint8_t probe_raw[];
+    *misalign = (1024u - (ptx::smem_u32(probe_raw) & 1023u)) & 1023u;
+}
 
-int attention_sm100_init() {
-    FLS_CUDA(cudaFuncSetAttribute(attention_tcgen05_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_BYTES));
+std::mutex g_attn_mu;
+int g_auto_k_stages[64] = {};   // per device: 0 = not decided yet
+int g_smem_lead[64] = {};       // per device: bytes from the start of a dynamic allocation to the next 1 KiB boundary
+
+template <int NK>
+int launch_nk(const CUtensorMap& tq, const CUtensorMap& tkv, int n_q_heads, int n_kv_heads, const AttnTile* tiles,
+              int n_tiles, __half* out, int ld_out, float scale_log2e, int smem_lead, cudaStream_t s) {
+    attention_tcgen05_kernel<NK><<<dim3(n_tiles, n_q_heads), THREADS, smem_used(NK) + smem_lead, s>>>(
+        tq, tkv, n_q_heads, n_kv_heads, tiles, out, ld_out, scale_log2e);
+    FLS_CUDA(cudaGetLastError());
     return kOk;
 }
 
+}  // namespace
+
+// Runs once per context, on the context's device.  Measures where dynamic shared memory starts relative to a 1 KiB
+// boundary and decides how many K buffers a CTA gets there: three if two such CTAs still share an SM, else two.
+int attention_sm100_init() {
+    std::lock_guard<std::mutex> lock(g_attn_mu);
+    constexpr int kMax = smem_used(MAX_K_STAGES) + 1023;
+    FLS_CUDA(cudaFuncSetAttribute(attention_tcgen05_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, kMax));
+    FLS_CUDA(cudaFuncSetAttribute(attention_tcgen05_kernel<3>, cudaFuncAttributeMaxDynamicSharedMemorySize, kMax));
+    FLS_CUDA(cudaFuncSetAttribute(attention_tcgen05_kernel<2>, cudaFuncAttributePreferredSharedMemoryCarveout,
+                                  cudaSharedmemCarveoutMaxShared));
+    FLS_CUDA(cudaFuncSetAttribute(attention_tcgen05_kernel<3>, cudaFuncAttributePreferredSharedMemoryCarveout,
+                                  cudaSharedmemCarveoutMaxShared));
+    int dev = 0;
+    FLS_CUDA(cudaGetDevice(&dev));
+    if (dev < 0 || dev >= 64) return fail(kErrInvalid, "attention: device index %d", dev);
+    if (g_auto_k_stages[dev] == 0) {
+        uint32_t* d_mis = nullptr;
+        uint32_t mis = 1023;
+        FLS_CUDA(cudaFuncSetAttribute(smem_base_probe_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kMax));
+        FLS_CUDA(cudaMalloc(&d_mis, sizeof(uint32_t)));
+        smem_base_probe_kernel<<<1, 1, smem_used(MAX_K_STAGES)>>>(d_mis);
+        cudaError_t e = cudaMemcpy(&mis, d_mis, sizeof(uint32_t), cudaMemcpyDeviceToHost);
+        cudaFree(d_mis);
+        if (e != cudaSuccess) return fail(kErrCuda, "attention: shared memory probe failed: %s", cudaGetErrorString(e));
+        // Two CTAs share an SM when each one's allocation (dynamic + the driver's reserved bytes) fits half of the SM's
+        // shared memory.  (cudaOccupancyMaxActiveBlocksPerMultiprocessor answers 1 for this kernel at every size,
+        // although `ncu` shows two resident CTAs - launch__occupancy_limit_shared_mem 2 at 114 944 bytes - so the
+        // device attributes decide: profiles/r02_occ_probe.txt.)
+        int per_sm = 0, reserved = 0;
+        FLS_CUDA(cudaDeviceGetAttribute(&per_sm, cudaDevAttrMaxSharedMemoryPerMultiprocessor, dev));
+        FLS_CUDA(cudaDeviceGetAttribute(&reserved, cudaDevAttrReservedSharedMemoryPerBlock, dev));
+        const int need = smem_used(3) + static_cast<int>(mis);
+        g_smem_lead[dev] = static_cast<int>(mis);
+        g_auto_k_stages[dev] = 2 * (need + reserved) <= per_sm ? 3 : 2;
+        if (getenv("FLS_DEBUG_ATTENTION"))
+            fprintf(stderr, "[fls] attention on device %d: dynamic shared memory starts %u bytes before a 1 KiB boundary; "
+                    "3 K buffers need %d + %d bytes per CTA, the SM has %d -> %d K buffers\n", dev, mis, need, reserved,
+                    per_sm, g_auto_k_stages[dev]);
+    }
+    return kOk;
+}
+
+int attention_sm100_k_stages() {
+    int dev = 0;
+    if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64) return 0;
+    return g_auto_k_stages[dev];
+}
+
 int attention_sm100_launch(const __half* qkv, int ld, int n_rows, int n_q_heads, int n_kv_heads, const AttnTile* tiles,
-                           int n_tiles, __half* out, int ld_out, cudaStream_t s) {
+                           int n_tiles, __half* out, int ld_out, cudaStream_t s, int k_stages) {
     if (n_tiles <= 0) return kOk;
     if (ld_out % 8) return fail(kErrInvalid, "attention: ld_out must be a multiple of 8");
     if (n_kv_heads <= 0 || n_q_heads % n_kv_heads)
         return fail(kErrInvalid, "attention: heads %d / kv heads %d", n_q_heads, n_kv_heads);
+    int dev = 0;
+    FLS_CUDA(cudaGetDevice(&dev));
+    if (dev < 0 || dev >= 64 || g_auto_k_stages[dev] == 0) return fail(kErrState, "attention_sm100_init() has not run");
+    if (k_stages == 0) k_stages = g_auto_k_stages[dev];
+    const int lead = g_smem_lead[dev];
+    if (k_stages != 2 && k_stages != 3) return fail(kErrState, "attention: %d K buffers (init has not run?)", k_stages);
     CUtensorMap tq, tkv;
     const int cols = (n_q_heads + 2 * n_kv_heads) * D;
     FLS_TRY(encode_tmap_2d(&tq, qkv, n_rows, cols, ld, BQ));
     FLS_TRY(encode_tmap_2d(&tkv, qkv, n_rows, cols, ld, BKV));
     const float scale_log2e = 1.4426950408889634f / sqrtf(static_cast<float>(D));
-    attention_tcgen05_kernel<<<dim3(n_tiles, n_q_heads), THREADS, SMEM_BYTES, s>>>(tq, tkv, n_q_heads, n_kv_heads, tiles,
-                                                                                  out, ld_out, scale_log2e);
-    FLS_CUDA(cudaGetLastError());
-    return kOk;
+    return k_stages == 3 ? launch_nk<3>(tq, tkv, n_q_heads, n_kv_heads, tiles, n_tiles, out, ld_out, scale_log2e, lead, s)
+                         : launch_nk<2>(tq, tkv, n_q_heads, n_kv_heads, tiles, n_tiles, out, ld_out, scale_log2e, lead, s);
 }
 
 }  // namespace fls

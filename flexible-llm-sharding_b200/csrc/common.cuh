@@ -120,9 +120,11 @@ int attention_launch(const __half* qkv, int ld, int n_q_heads, int n_kv_heads, i
                      int n_tiles, __half* out, int ld_out, cudaStream_t s);
 int attention_init();
 // tcgen05 version (head_dim 128); n_rows = rows of the qkv buffer (bounds the TMA tensor map)
+// k_stages: K buffers per CTA - 0 = what attention_sm100_init chose for this device (3 where two CTAs still fit an SM), 2, 3
 int attention_sm100_launch(const __half* qkv, int ld, int n_rows, int n_q_heads, int n_kv_heads, const AttnTile* tiles,
-                           int n_tiles, __half* out, int ld_out, cudaStream_t s);
+                           int n_tiles, __half* out, int ld_out, cudaStream_t s, int k_stages = 0);
 int attention_sm100_init();
+int attention_sm100_k_stages();   // the choice made for the current device (0 before init)
 
 // TMA descriptor over a row-major fp16 matrix [rows, cols] (row stride ld), box = 64 columns x box_rows,
 // 128-byte swizzle (gemm_sm100.cu).

@@ -326,7 +326,8 @@ int fls_get_profile(fls_ctx* ctx, fls_kernel_profile* out);
 
 /* Tuning knobs.  "gemm_cta_group": 2 (default; CTA pairs share a 256x256 tile through
  * tcgen05 cta_group::2) or 1 (one CTA per 128x256 tile).  "attention_impl": 1 (default; tcgen05
- * kernel for head_dim 128) or 0 (mma.sync kernel).  "fuse_rope": 1 (default; rotary embedding applied in the
+ * kernel for head_dim 128) or 0 (mma.sync kernel).  "attention_k_stages": K buffers per CTA of the tcgen05 attention -
+ * 0 (default: 3 where two such CTAs still share an SM, else 2), 2 or 3; the results do not depend on it.  "fuse_rope": 1 (default; rotary embedding applied in the
  * QKV GEMM epilogue when head_dim is 128 and the GEMM runs 256 x 256 tiles), 2 (also with 256 x 512 tiles) or 0
  * (separate kernel).  "paced_weight_stream": see fls_prefetch_pump.
  * "gemm_wide_tiles": with cta_group 2, 256 x 512 tiles per CTA pair (one staged A slice feeds both TMEM

@@ -172,9 +172,10 @@ def test_embed_exact(env):
     assert torch.equal(out, table[ids.long()])
 
 
-@pytest.mark.parametrize("nq,nkv,d,impl", [(4, 4, 128, 1), (4, 2, 128, 1), (4, 2, 128, 0), (8, 2, 64, 0)])
+@pytest.mark.parametrize("nq,nkv,d,impl,k_stages", [(4, 4, 128, 1, 0), (4, 2, 128, 1, 3), (4, 2, 128, 1, 2),
+                                                    (4, 2, 128, 0, 0), (8, 2, 64, 0, 0)])
 @pytest.mark.parametrize("prefix_causal", [False, True])
-def test_attention_matches_oracle(env, nq, nkv, d, impl, prefix_causal):
+def test_attention_matches_oracle(env, nq, nkv, d, impl, k_stages, prefix_causal):
     """Prefix + shared-prefix suffix attention for several prompts against the oracle's eager
     attention (softmax in fp32, probabilities rounded to fp16, GQA by repeat_kv)."""
     from oracle import llama_oracle as O
@@ -182,6 +183,7 @@ def test_attention_matches_oracle(env, nq, nkv, d, impl, prefix_causal):
     shapes = [(70, 3, 9), (1, 2, 5), (129, 4, 33), (64, 1, 64), (200, 2, 70), (384, 4, 32), (30, 2, 150)]
     rows = sum(lp + S * ls for lp, S, ls in shapes)                                   # (len_p, S, len_s)
     ctx.call("fls_set_option", b"attention_impl", impl)
+    ctx.call("fls_set_option", b"attention_k_stages", k_stages)      # K buffers per CTA: this device's default, 3, 2
     ld = (nq + 2 * nkv) * d
     qkv = _rand((rows, ld), 1.0, 13, dev)
     tiles, base = [], 0
@@ -194,6 +196,7 @@ def test_attention_matches_oracle(env, nq, nkv, d, impl, prefix_causal):
              _sp())
     torch.cuda.synchronize()
     ctx.call("fls_set_option", b"attention_impl", 1)
+    ctx.call("fls_set_option", b"attention_k_stages", 0)
     assert torch.isfinite(out).all()
 
     q_all, k_all, v_all = qkv.cpu().float().split([nq * d, nkv * d, nkv * d], dim=1)
