@@ -100,6 +100,23 @@ attention_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_q, const __gri
     const int n1 = t.mode == kAttnSuffix ? (t.seg1_len + BKV - 1) / BKV : 0;
     const int n_tiles = n0 + n1;
 
+    auto load_k = [&](int j) {      // K(j) -> buffer j % NK (the caller has made sure it is free)
+        const int ks = j % NK;
+        const int row = j < n0 ? t.seg0_row + j * BKV : t.seg1_row + (j - n0) * BKV;
+        uint8_t* kb = sK + ks * TILE_BYTES;
+        ptx::mbar_arrive_expect_tx(&k_full[ks], TILE_BYTES);
+        ptx::tma_load_2d(kb, &tmap_kv, &k_full[ks], k_col, row);
+        ptx::tma_load_2d(kb + KSUB_BYTES, &tmap_kv, &k_full[ks], k_col + 64, row);
+    };
+    auto load_v = [&](int j) {
+        const int vs = j % V_STAGES;
+        const int row = j < n0 ? t.seg0_row + j * BKV : t.seg1_row + (j - n0) * BKV;
+        uint8_t* vb = sV + vs * TILE_BYTES;
+        ptx::mbar_arrive_expect_tx(&v_full[vs], TILE_BYTES);
+        ptx::tma_load_2d(vb, &tmap_kv, &v_full[vs], v_col, row);
+        ptx::tma_load_2d(vb + KSUB_BYTES, &tmap_kv, &v_full[vs], v_col + 64, row);
+    };
+
     if (warp_idx == 0) {
         if (ptx::elect_one()) {
             ptx::prefetch_tensormap(&tmap_q);
@@ -118,6 +135,15 @@ attention_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_q, const __gri
             ptx::mbar_init(p_ready, 4);  // one arrive per softmax warp
             ptx::mbar_init(pv_done, 1);
             ptx::fence_mbar_init();
+            // Q and the first key tiles (every buffer is free) are requested right here, before the TMEM allocation and
+            // the CTA-wide barrier: their latency is the longest thing a short-lived CTA waits for.
+            ptx::mbar_arrive_expect_tx(q_full, Q_BYTES);
+            ptx::tma_load_2d(sQ, &tmap_q, q_full, q_col, t.q_row);
+            ptx::tma_load_2d(sQ + Q_BYTES / 2, &tmap_q, q_full, q_col + 64, t.q_row);
+            for (int j = 0; j < min(n_tiles, NK); ++j) {
+                load_k(j);
+                if (j < V_STAGES) load_v(j);
+            }
         }
         __syncwarp();
         ptx::tmem_alloc<1>(tmem_slot, TMEM_COLS);
@@ -129,26 +155,17 @@ attention_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_q, const __gri
     const uint32_t tmem_base = *tmem_slot;
 
     if (warp_idx == 0) {
-        // ------------------------------------------------------------------ TMA producer
+        // ------------------------------------------------------------------ TMA producer (the rest of the key tiles)
+        // K(j) and V(j-1) wait for the same event when NK = 3 (P V of tile j-3 retired), K(j) and V(j) when NK = 2, so
+        // issuing the loads in this one order never holds a load back behind a later release.
         if (ptx::elect_one()) {
-            ptx::mbar_arrive_expect_tx(q_full, Q_BYTES);
-            ptx::tma_load_2d(sQ, &tmap_q, q_full, q_col, t.q_row);
-            ptx::tma_load_2d(sQ + Q_BYTES / 2, &tmap_q, q_full, q_col + 64, t.q_row);
-            // K(j) and V(j-1) wait for the same event when NK = 3 (P V of tile j-3 retired), K(j) and V(j) when
-            // NK = 2, so issuing the loads in this one order never holds a load back behind a later release.
-            for (int j = 0; j < n_tiles; ++j) {
-                const int ks = j % NK, vs = j % V_STAGES;
-                const int row = j < n0 ? t.seg0_row + j * BKV : t.seg1_row + (j - n0) * BKV;
-                ptx::mbar_wait(&k_empty[ks], ((j / NK) & 1) ^ 1);
-                uint8_t* kb = sK + ks * TILE_BYTES;
-                ptx::mbar_arrive_expect_tx(&k_full[ks], TILE_BYTES);
-                ptx::tma_load_2d(kb, &tmap_kv, &k_full[ks], k_col, row);
-                ptx::tma_load_2d(kb + KSUB_BYTES, &tmap_kv, &k_full[ks], k_col + 64, row);
-                ptx::mbar_wait(&v_empty[vs], ((j / V_STAGES) & 1) ^ 1);
-                uint8_t* vb = sV + vs * TILE_BYTES;
-                ptx::mbar_arrive_expect_tx(&v_full[vs], TILE_BYTES);
-                ptx::tma_load_2d(vb, &tmap_kv, &v_full[vs], v_col, row);
-                ptx::tma_load_2d(vb + KSUB_BYTES, &tmap_kv, &v_full[vs], v_col + 64, row);
+            for (int j = V_STAGES; j < n_tiles; ++j) {
+                if (j >= NK) {
+                    ptx::mbar_wait(&k_empty[j % NK], ((j / NK) & 1) ^ 1);
+                    load_k(j);
+                }
+                ptx::mbar_wait(&v_empty[j % V_STAGES], ((j / V_STAGES) & 1) ^ 1);
+                load_v(j);
             }
         }
     } else if (warp_idx == 1) {
@@ -229,9 +246,10 @@ attention_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_q, const __gri
                     if (key < lo || key > hi) sr[c >> 5][c & 31] = 0xff800000u;  // -inf
                 }
             }
-            float mx = -INFINITY;
+            float mx4[4] = {-INFINITY, -INFINITY, -INFINITY, -INFINITY};   // four short chains instead of one long one
 #pragma unroll
-            for (int c = 0; c < 64; ++c) mx = fmaxf(mx, __uint_as_float(sr[c >> 5][c & 31]));
+            for (int c = 0; c < 64; ++c) mx4[c & 3] = fmaxf(mx4[c & 3], __uint_as_float(sr[c >> 5][c & 31]));
+            const float mx = fmaxf(fmaxf(mx4[0], mx4[1]), fmaxf(mx4[2], mx4[3]));
             // lazy rescale: keep the old reference max unless the new one is much larger
             float m_new = m_run;
             if (mx > m_run + thr) m_new = mx;
