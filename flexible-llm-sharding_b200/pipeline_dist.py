@@ -158,12 +158,25 @@ class IpcRing:
         if slot_bytes < self.slot_bytes:
             slot_bytes = self.slot_bytes                     # never shrink: the downstream mapping stays valid
         need = max(depths[self.rank] * slot_bytes, self.capacity)
-        retired = None
+        retired, failed = None, None
         if need > self.capacity or self.slots is None:
-            retired = self.slots
-            self.slots, self.slots_handle = self._alloc(need)
-            self.capacity, self.version = need, self.version + 1
-        infos = self.coll.all_gather((self.version, self.slots_handle, self.capacity))
+            try:
+                fresh = self._alloc(need)
+            except _lib.FlsError as e:                       # reported to every rank below: nobody is left waiting
+                failed = (f"rank {self.rank}: no room in HBM for an inbound ring of {depths[self.rank]} micro-batches "
+                          f"({need / 1e9:.2f} GB): {e}")
+            else:
+                retired = self.slots
+                self.slots, self.slots_handle = fresh
+                self.capacity, self.version = need, self.version + 1
+        infos = self.coll.all_gather((self.version, self.slots_handle, self.capacity, failed))
+        problems = [f for _, _, _, f in infos if f]
+        if problems:
+            raise RuntimeError("; ".join(problems) + ".  The layer pipeline hands activations from GPU to GPU and keeps "
+                               "them in HBM; score fewer prompts per call (--num_batch), use more GPUs, or run "
+                               "--data_parallel True, whose activations can live in host memory or on disk "
+                               "(--storage_location cpu|disk)")
+        infos = [i[:3] for i in infos]
         nv, nh, ncap = infos[(self.rank + 1) % self.G]
         remap = nv != self.next_version
         if remap:

@@ -19,6 +19,7 @@ import hashlib
 import json
 import os
 import threading
+import warnings
 from collections import defaultdict
 from time import perf_counter
 
@@ -451,6 +452,11 @@ class ShardedLlama:
     def run(self, inputs, want_probs=True, answer_ids=None, packed=None, return_device=False):
         shards, num_gpu, rank, dp = self._plan()
         if not dp:
+            if self.args.storage_location != "gpu" and not getattr(self, "_mp_tier_noted", False):
+                self._mp_tier_noted = True
+                warnings.warn(f"--storage_location {self.args.storage_location}: the layer pipeline across GPUs hands "
+                              "activations from GPU to GPU and keeps them in HBM; the host and disk tiers apply to "
+                              "data-parallel passes (--data_parallel True)", stacklevel=3)
             if getattr(self.device_manager, "distributed", False):    # one process per GPU (torchrun)
                 from .pipeline_dist import run_model_parallel_distributed
                 return run_model_parallel_distributed(self, inputs, shards, num_gpu, rank, want_probs, answer_ids,

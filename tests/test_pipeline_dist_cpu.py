@@ -105,7 +105,31 @@ def _worker(rank, world, port, q):
     args = types.SimpleNamespace(model_path=".", data_parallel=False)
     dm = M.distributed_device_manager(args)
     dp = M.distributed_device_manager(types.SimpleNamespace(model_path=".", data_parallel=True))
-    q.put((rank, got, verdicts, dm.devices, dm.distributed, dp.devices, dp.distributed))
+    # An inbound ring that does not fit on ONE rank is an error on EVERY rank (nobody is left waiting in a collective).
+    import ctypes as C
+    from flexible_llm_sharding_b200 import _lib
+
+    class FakeCtx:                      # stands in for the CUDA side: hands out addresses, rank 1 has no room for 1 GB
+        def __init__(self):
+            self.next = 0x10000
+        def call(self, name, *a):
+            if name == "fls_ipc_alloc":
+                if rank == 1 and a[0].value > (1 << 30):
+                    raise _lib.FlsError(3, "cudaMalloc failed: out of memory")
+                a[1]._obj.value = self.next
+                self.next += 0x10000
+                a[2][0] = rank + 1
+            elif name == "fls_ipc_open":
+                a[1]._obj.value = 0x900000 + a[0][0]
+    ring = PD.IpcRing(FakeCtx(), coll)
+    ring.ensure([4, 3], 1 << 20, lambda: None)
+    small_ok = ring.capacity == 4 << 20 if rank == 0 else ring.capacity == 3 << 20
+    try:
+        ring.ensure([4, 3], 1 << 29, lambda: None)        # rank 0 needs 2 GB (granted), rank 1 1.5 GB (refused)
+        big = "no error"
+    except RuntimeError as e:
+        big = str(e)
+    q.put((rank, got, verdicts, dm.devices, dm.distributed, dp.devices, dp.distributed, small_ok, big))
     coll.barrier()
     dist.destroy_process_group()
 
@@ -122,7 +146,9 @@ def test_two_rank_host_agreement_over_gloo():
     for p in procs:
         p.join(timeout=60)
         assert p.exitcode == 0
-    for rank, got, verdicts, devices, distributed, dp_devices, dp_distributed in res:
+    for rank, got, verdicts, devices, distributed, dp_devices, dp_distributed, small_ok, big in res:
+        assert small_ok
+        assert "rank 1: no room in HBM" in big and "--data_parallel True" in big, big
         assert got == {"tok": [1, 2, 3]}
         assert verdicts == ["load", "save", "no", "no"]       # all-or-nothing, identical on both ranks
         assert devices == ["cuda:0", "cuda:1"] and distributed is True        # every rank's GPU, in rank order
