@@ -147,10 +147,10 @@ def test_cross_process_pipeline_with_prefix_kv_cache(tiny_gqa):
     assert [n[0] for n in res[0][1]] == ["save", "load", "load"] == [n[0] for n in res[1][1]]
 
 
-def _cli_worker(rank, world, port, argv, q):
+def _cli_worker(rank, world, port, argv, q, env=None):
     import os
     os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port), RANK=str(rank), WORLD_SIZE=str(world),
-                      LOCAL_RANK=str(rank), LOCAL_WORLD_SIZE=str(world))
+                      LOCAL_RANK=str(rank), LOCAL_WORLD_SIZE=str(world), **(env or {}))
     os.environ.pop("FLS_STAGE_DIR", None)
     from flexible_llm_sharding_b200 import main as M
     from flexible_llm_sharding_b200 import _lib
@@ -161,11 +161,13 @@ def _cli_worker(rank, world, port, argv, q):
     dist.destroy_process_group()
 
 
-@pytest.mark.parametrize("data_parallel", [True, False])
-def test_torchrun_cli_on_two_gpus(tiny, tmp_path, data_parallel):
+@pytest.mark.parametrize("data_parallel,storage", [(True, "gpu"), (False, "gpu"), (True, "disk")])
+def test_torchrun_cli_on_two_gpus(tiny, tmp_path, data_parallel, storage):
     """`torchrun --nproc-per-node 2 main.py ...` as the user would run it: with --data_parallel the disk-resident
     layer files are staged once on tmpfs (and the staging directory is gone afterwards), without it the two ranks form
-    the layer pipeline; the pickles rank 0 writes hold the single-GPU scores, bit for bit."""
+    the layer pipeline; the pickles rank 0 writes hold the single-GPU scores, bit for bit.  With the disk tier forced
+    both ranks write their per-prompt `.npy` files into ONE folder at the same time: the file tag is the global rank,
+    so they do not collide, and the folder is empty afterwards."""
     _need_two()
     import pickle
     import socket
@@ -175,13 +177,15 @@ def test_torchrun_cli_on_two_gpus(tiny, tmp_path, data_parallel):
     with open(pp, "wb") as f:
         pickle.dump(tiny["prompts"], f)
     argv = ["--model_path", tiny["layer_dir"], "--prompt_pickle", str(pp), "--output_file", str(outp),
-            "--storage_location", "gpu", "--layer_num_per_shard", "2"] + (["--data_parallel", "True"] if data_parallel else [])
+            "--storage_location", storage, "--disk_folder", str(tmp_path / "act"), "--layer_num_per_shard", "2"] \
+        + (["--data_parallel", "True"] if data_parallel else [])
+    env = dict(FLS_FORCE_STORAGE="1", FLS_MAX_ROWS="200") if storage == "disk" else None
     with socket.socket() as s:
         s.bind(("127.0.0.1", 0))
         port = s.getsockname()[1]
     ctx = mp.get_context("spawn")
     q = ctx.Queue()
-    procs = [ctx.Process(target=_cli_worker, args=(r, 2, port, argv, q)) for r in range(2)]
+    procs = [ctx.Process(target=_cli_worker, args=(r, 2, port, argv, q, env)) for r in range(2)]
     for p in procs:
         p.start()
     res = dict()
@@ -193,6 +197,8 @@ def test_torchrun_cli_on_two_gpus(tiny, tmp_path, data_parallel):
         assert p.exitcode == 0
     assert res[0] == len(base) and res[1] is None
     assert not os.path.isdir(f"/dev/shm/fls_stage_{os.getuid()}_{port}")     # the automatic staging directory is gone
+    if storage == "disk":
+        assert not [f for f in os.listdir(tmp_path / "act") if f.endswith(".npy")]
     with open(outp, "rb") as f:
         scores = pickle.load(f)
     for a, b in zip(scores, base):
