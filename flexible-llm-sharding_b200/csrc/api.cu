@@ -108,7 +108,8 @@ struct fls_ctx {
     bool cuda_poisoned = false;
     unsigned long long peer_enabled_mask = 0;
     int gemm_cg = 2;  // tcgen05 cta_group of the GEMM kernels (2 = CTA pairs, 1 = single CTA)
-    int attn_impl = 1;  // 1 = tcgen05 attention (head_dim 128), 0 = mma.sync attention
+    int attn_impl = 2;  // head_dim 128: 2 = tcgen05 attention with persistent CTAs (default); 1 = one CTA per (query tile, head); 0 = mma.sync attention
+    uint32_t* attn_work = nullptr;  // work counter of the persistent attention (two uint32, zero between launches)
     int attn_k_stages = 0;  // K buffers per CTA of the tcgen05 attention: 0 = chosen per device at init (3 where two CTAs fit an SM), 2, 3
     std::vector<cudaEvent_t> pace_events;
     size_t pace_next = 0;
@@ -282,6 +283,9 @@ inline __half* H(uint16_t* p) { return reinterpret_cast<__half*>(p); }
 
 int attention_dispatch(fls_ctx* c, const __half* qkv, int ld, int n_rows, int n_q_heads, int n_kv_heads, int head_dim,
                        const AttnTile* tiles, int n_tiles, __half* out, int ld_out, cudaStream_t st) {
+    if (c->attn_impl == 2 && head_dim == 128)
+        return attention_sm100_launch_persistent(qkv, ld, n_rows, n_q_heads, n_kv_heads, tiles, n_tiles, out, ld_out, st,
+                                                 c->attn_work, c->num_sms);
     if (c->attn_impl == 1 && head_dim == 128)
         return attention_sm100_launch(qkv, ld, n_rows, n_q_heads, n_kv_heads, tiles, n_tiles, out, ld_out, st,
                                       c->attn_k_stages);
@@ -391,6 +395,13 @@ int fls_create(const fls_model_desc* d, int device, fls_ctx** out) {
         delete c;
         return fail(kErrCuda, "cudaStreamCreate: %s", cudaGetErrorString(e));
     }
+    e = cudaMalloc(reinterpret_cast<void**>(&c->attn_work), 2 * sizeof(uint32_t));
+    if (e == cudaSuccess) e = cudaMemset(c->attn_work, 0, 2 * sizeof(uint32_t));
+    if (e != cudaSuccess) {
+        cudaStreamDestroy(c->copy_stream);
+        delete c;
+        return fail(kErrCuda, "attention work counter: %s", cudaGetErrorString(e));
+    }
     *out = c;
     return kOk;
 }
@@ -411,6 +422,7 @@ int fls_destroy(fls_ctx* c) {
     free_workspace(c);
     if (c->rope_cos) cudaFree(c->rope_cos);
     if (c->rope_sin) cudaFree(c->rope_sin);
+    if (c->attn_work) cudaFree(c->attn_work);
     if (c->copy_stream) cudaStreamDestroy(c->copy_stream);
     for (void* p : c->ipc_mapped) cudaIpcCloseMemHandle(p);
     for (void* p : c->ipc_owned) cudaFree(p);
@@ -1103,7 +1115,7 @@ int fls_set_option(fls_ctx* c, const char* name, int value) {
         return kOk;
     }
     if (strcmp(name, "attention_impl") == 0) {
-        if (value != 0 && value != 1) return ctx_fail(c, fail(kErrInvalid, "attention_impl must be 0 or 1"));
+        if (value < 0 || value > 2) return ctx_fail(c, fail(kErrInvalid, "attention_impl must be 0, 1 or 2"));
         c->attn_impl = value;
         return kOk;
     }

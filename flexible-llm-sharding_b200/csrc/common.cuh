@@ -123,6 +123,10 @@ int attention_init();
 // k_stages: K buffers per CTA - 0 = what attention_sm100_init chose for this device (3 where two CTAs still fit an SM), 2, 3
 int attention_sm100_launch(const __half* qkv, int ld, int n_rows, int n_q_heads, int n_kv_heads, const AttnTile* tiles,
                            int n_tiles, __half* out, int ld_out, cudaStream_t s, int k_stages = 0);
+// persistent CTAs fetching (tile, head) items from `work_ctr` (two zeroed uint32 of the caller's context)
+int attention_sm100_launch_persistent(const __half* qkv, int ld, int n_rows, int n_q_heads, int n_kv_heads,
+                                      const AttnTile* tiles, int n_tiles, __half* out, int ld_out, cudaStream_t s,
+                                      uint32_t* work_ctr, int num_sms);
 int attention_sm100_init();
 int attention_sm100_k_stages();   // the choice made for the current device (0 before init)
 

@@ -265,8 +265,9 @@ int fls_op_rmsnorm(fls_ctx* ctx, const uint16_t* x_dev, const uint16_t* delta_de
                    void* stream);
 int fls_op_rope(fls_ctx* ctx, uint16_t* qkv_dev, int ld, int n_rows, int n_q_heads, int n_kv_heads, int head_dim,
                 const int32_t* row_pos_dev, void* stream);
-/* n_rows = rows of the qkv buffer.  head_dim 128 runs the tcgen05 kernel (option "attention_impl" = 1,
- * default) or the mma.sync kernel (0); head_dim 64 always the latter. */
+/* n_rows = rows of the qkv buffer.  head_dim 128 runs the tcgen05 kernel (option "attention_impl" = 2, the default:
+ * persistent CTAs; 1: one CTA per query tile and head) or the mma.sync kernel (0); head_dim 64 always the latter.
+ * With "attention_impl" = 2 two launches through the same context must not run concurrently. */
 int fls_op_attention(fls_ctx* ctx, const uint16_t* qkv_dev, int ld, int n_rows, int n_q_heads, int n_kv_heads,
                      int head_dim, const fls_attn_tile* tiles_dev, int n_tiles, uint16_t* out_dev, int ld_out,
                      void* stream);
@@ -325,8 +326,9 @@ int fls_set_profiling(fls_ctx* ctx, int enabled);
 int fls_get_profile(fls_ctx* ctx, fls_kernel_profile* out);
 
 /* Tuning knobs.  "gemm_cta_group": 2 (default; CTA pairs share a 256x256 tile through
- * tcgen05 cta_group::2) or 1 (one CTA per 128x256 tile).  "attention_impl": 1 (default; tcgen05
- * kernel for head_dim 128) or 0 (mma.sync kernel).  "attention_k_stages": K buffers per CTA of the tcgen05 attention -
+ * tcgen05 cta_group::2) or 1 (one CTA per 128x256 tile).  "attention_impl" (head_dim 128): 2 (default; tcgen05 kernel
+ * with persistent CTAs that fetch (query tile, head) items from a counter owned by the context - launches of ONE context
+ * must therefore not overlap each other), 1 (the same kernel launched as one CTA per item) or 0 (mma.sync kernel).  "attention_k_stages": K buffers per CTA of the tcgen05 attention -
  * 0 (default: 3 where two such CTAs still share an SM, else 2), 2 or 3; the results do not depend on it.  "fuse_rope": 1 (default; rotary embedding applied in the
  * QKV GEMM epilogue when head_dim is 128 and the GEMM runs 256 x 256 tiles), 2 (also with 256 x 512 tiles) or 0
  * (separate kernel).  "paced_weight_stream": see fls_prefetch_pump.

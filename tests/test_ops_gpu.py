@@ -173,6 +173,7 @@ def test_embed_exact(env):
 
 
 @pytest.mark.parametrize("nq,nkv,d,impl,k_stages", [(4, 4, 128, 1, 0), (4, 2, 128, 1, 3), (4, 2, 128, 1, 2),
+                                                    (4, 4, 128, 2, 0), (4, 2, 128, 2, 0),     # persistent CTAs
                                                     (4, 2, 128, 0, 0), (8, 2, 64, 0, 0)])
 @pytest.mark.parametrize("prefix_causal", [False, True])
 def test_attention_matches_oracle(env, nq, nkv, d, impl, k_stages, prefix_causal):
@@ -195,7 +196,7 @@ def test_attention_matches_oracle(env, nq, nkv, d, impl, k_stages, prefix_causal
     ctx.call("fls_op_attention", qkv.data_ptr(), ld, rows, nq, nkv, d, t.data_ptr(), len(tiles), out.data_ptr(), nq * d,
              _sp())
     torch.cuda.synchronize()
-    ctx.call("fls_set_option", b"attention_impl", 1)
+    ctx.call("fls_set_option", b"attention_impl", 2)
     ctx.call("fls_set_option", b"attention_k_stages", 0)
     assert torch.isfinite(out).all()
 

@@ -186,8 +186,9 @@ def test_gemm_at_model_shapes(big_ctx, M, N, K, epi):
     assert mismatched / (M * N) < 0.10
 
 
+@pytest.mark.parametrize("impl", [1, 2])          # one CTA per (query tile, head) / persistent CTAs
 @pytest.mark.parametrize("nq,nkv", [(64, 8), (40, 40), (32, 32)])
-def test_attention_at_model_head_counts(big_ctx, nq, nkv):
+def test_attention_at_model_head_counts(big_ctx, nq, nkv, impl):
     """Shared-prefix attention with 70B / 13B / 7B head counts (GQA 8:1 at 70B) on the benchmark's prompt shapes
     (384 + 4 x 32 and 1792 + 4 x 64 rows) against the oracle's eager attention evaluated in fp32 on the GPU."""
     from flexible_llm_sharding_b200 import planner
@@ -203,9 +204,11 @@ def test_attention_at_model_head_counts(big_ctx, nq, nkv):
         base += lp + S * ls
     t = torch.tensor(tiles, dtype=torch.int32, device="cuda:0")
     out = torch.full((rows, nq * d), float("nan"), dtype=torch.float16, device="cuda:0")
+    big_ctx.call("fls_set_option", b"attention_impl", impl)
     big_ctx.call("fls_op_attention", qkv.data_ptr(), ld, rows, nq, nkv, d, t.data_ptr(), len(tiles), out.data_ptr(),
                  nq * d, _sp())
     torch.cuda.synchronize()
+    big_ctx.call("fls_set_option", b"attention_impl", 2)
     assert torch.isfinite(out).all()
     q_all, k_all, v_all = qkv.float().split([nq * d, nkv * d, nkv * d], dim=1)
     mask_full = (torch.finfo(torch.float32).min * torch.ones((2048, 2048), device="cuda:0")).triu(1)[None, None]

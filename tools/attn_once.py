@@ -1,5 +1,6 @@
-"""One launch of the tcgen05 attention per K-buffer count (3, then 2) on the 7B micro-batch shape - the target of
-`ncu` captures:  ncu --set full --import-source on -k regex:attention_tcgen05 python tools/attn_once.py"""
+"""Two launches of each tcgen05 attention form (persistent CTAs; grid form with 3 and with 2 K buffers) on the 7B (or, with
+`70b`, the 70B) micro-batch shape - the target of `ncu` captures:
+    ncu --set full --import-source on -k regex:attention_ python tools/attn_once.py"""
 import ctypes as C
 import os
 import sys
@@ -20,9 +21,10 @@ qkv = (torch.randn((base, ld), device="cuda") * 1.28).half()
 t = torch.tensor(tiles, dtype=torch.int32, device="cuda")
 out = torch.empty((base, nq * d), dtype=torch.float16, device="cuda")
 sp = C.c_void_p(torch.cuda.current_stream().cuda_stream)
-for ks in (3, 2):
+for impl, ks in ((2, 0), (1, 3), (1, 2)):           # persistent CTAs; one CTA per (tile, head) with 3 / 2 K buffers
+    ctx.call("fls_set_option", b"attention_impl", impl)
     ctx.call("fls_set_option", b"attention_k_stages", ks)
     for _ in range(2):
         ctx.call("fls_op_attention", qkv.data_ptr(), ld, base, nq, nkv, d, t.data_ptr(), len(tiles), out.data_ptr(), nq * d, sp)
     torch.cuda.synchronize()
-    print("launched with", ks, "K buffers", flush=True)
+    print("launched impl", impl, "with", ks, "K buffers", flush=True)
