@@ -379,7 +379,7 @@ struct WorkItem {
 
 __global__ void __launch_bounds__(THREADS, 2)
 attention_persistent_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant__ CUtensorMap tmap_kv,
-                            int n_q_heads, int n_kv_heads, const AttnTile* __restrict__ tiles, int n_tile_desc,
+                            const __grid_constant__ CUtensorMap tmap_o, int n_q_heads, int n_kv_heads, const AttnTile* __restrict__ tiles, int n_tile_desc,
                             __half* __restrict__ out, int ld_out, float scale_log2e, uint32_t* __restrict__ work_ctr) {
     constexpr int NK = 3;
     extern __shared__ uint8_t smem_raw[];
@@ -411,6 +411,7 @@ attention_persistent_kernel(const __grid_constant__ CUtensorMap tmap_q, const __
         if (ptx::elect_one()) {
             ptx::prefetch_tensormap(&tmap_q);
             ptx::prefetch_tensormap(&tmap_kv);
+            ptx::prefetch_tensormap(&tmap_o);
             ptx::mbar_init(q_full, 1);
             ptx::mbar_init(q_empty, 1);
             for (int i = 0; i < NK; ++i) {
@@ -664,6 +665,9 @@ attention_persistent_kernel(const __grid_constant__ CUtensorMap tmap_q, const __
             ptx::tc_fence_after_sync();
             const float inv = l_run > 0.f ? 1.f / l_run : 0.f;
             uint8_t* stage = sK + (g_last % NK) * TILE_BYTES + quarter * 4096;
+            // A warp whose 32 rows all belong to the tile hands its staged [32 x 64] piece to one TMA store (the staging
+            // layout IS the 128B swizzle); a warp with fewer valid rows copies them out itself, row by row.
+            const bool whole = rows_here == 32;
 #pragma unroll 1
             for (int hcol = 0; hcol < D; hcol += 64) {
 #pragma unroll
@@ -684,17 +688,29 @@ attention_persistent_kernel(const __grid_constant__ CUtensorMap tmap_q, const __
                             make_uint4(wv[0], wv[1], wv[2], wv[3]);
                     }
                 }
-                __syncwarp();
-#pragma unroll
-                for (int rr = 0; rr < 32; rr += 4) {
-                    const int r = rr + (lane >> 3);
-                    if (r < rows_here) {
-                        const uint4 v4 = *reinterpret_cast<const uint4*>(stage + r * 128 + (((lane & 7) ^ (r & 7)) << 4));
-                        *reinterpret_cast<uint4*>(out + static_cast<size_t>(t.q_row + quarter * 32 + r) * ld_out +
-                                                  head * D + hcol + (lane & 7) * 8) = v4;
+                if (whole) {
+                    ptx::fence_proxy_async_smem();
+                    __syncwarp();
+                    if (lane == 0) {
+                        ptx::tma_store_2d(&tmap_o, stage, head * D + hcol, t.q_row + quarter * 32);
+                        ptx::bulk_commit_group();
+                        ptx::bulk_wait_group_read<0>();      // the piece is re-used by the next half / handed back below
                     }
+                    __syncwarp();
+                } else {
+                    __syncwarp();
+#pragma unroll
+                    for (int rr = 0; rr < 32; rr += 4) {
+                        const int r = rr + (lane >> 3);
+                        if (r < rows_here) {
+                            const uint4 v4 =
+                                *reinterpret_cast<const uint4*>(stage + r * 128 + (((lane & 7) ^ (r & 7)) << 4));
+                            *reinterpret_cast<uint4*>(out + static_cast<size_t>(t.q_row + quarter * 32 + r) * ld_out +
+                                                      head * D + hcol + (lane & 7) * 8) = v4;
+                        }
+                    }
+                    __syncwarp();
                 }
-                __syncwarp();
             }
             // O has been read (the next item's first P V may overwrite it once p_ready says so) and so has the staging
             // buffer: the fourth warp to get here returns it to the producer
@@ -823,11 +839,13 @@ int attention_sm100_launch_persistent(const __half* qkv, int ld, int n_rows, int
     const int cols = (n_q_heads + 2 * n_kv_heads) * D;
     FLS_TRY(encode_tmap_2d(&tq, qkv, n_rows, cols, ld, BQ));
     FLS_TRY(encode_tmap_2d(&tkv, qkv, n_rows, cols, ld, BKV));
+    CUtensorMap tout;                                       // [n_rows, heads x 128] output, pieces of 32 rows x 64 columns
+    FLS_TRY(encode_tmap_2d(&tout, out, n_rows, n_q_heads * D, ld_out, 32));
     const float scale_log2e = 1.4426950408889634f / sqrtf(static_cast<float>(D));
     const long long n_items = static_cast<long long>(n_tiles) * n_q_heads;
     const int grid = static_cast<int>(std::min<long long>(n_items, 2LL * (num_sms > 0 ? num_sms : 148)));
     attention_persistent_kernel<<<grid, THREADS, PERSIST_SMEM_USED + g_smem_lead[dev], s>>>(
-        tq, tkv, n_q_heads, n_kv_heads, tiles, n_tiles, out, ld_out, scale_log2e, work_ctr);
+        tq, tkv, tout, n_q_heads, n_kv_heads, tiles, n_tiles, out, ld_out, scale_log2e, work_ctr);
     FLS_CUDA(cudaGetLastError());
     return kOk;
 }
