@@ -3,7 +3,10 @@
 // Same contract as attention.cu (see there and include/fls_b200.h: fls_attn_tile); replaces the
 // reference's two eager attention calls per layer (reference utils.py:272 and :275-279).
 //
-// One CTA = one query tile (<= 128 rows) x one head, 192 threads:
+// Two kernels with the same arithmetic: attention_tcgen05_kernel<NK> launches one CTA per work item (query tile x head);
+// attention_persistent_kernel (further down, the default) keeps two CTAs per SM resident and lets them fetch items.
+//
+// One work item = one query tile (<= 128 rows) x one head, handled by a CTA of 192 threads:
 //   warp 0      TMA producer: Q tile once (2 x [128 x 64] sub-tiles, 128B swizzle), then K and V tiles of
 //               64 keys (each 2 x [64 x 64] sub-tiles) through two rings: NK = 3 buffers for K (which later
 //               hold P), 2 for V.  A key tile never straddles the two key segments (prefix rows / option rows).
