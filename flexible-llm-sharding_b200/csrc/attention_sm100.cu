@@ -60,12 +60,156 @@ constexpr int THREADS = 192;
 constexpr int TMEM_COLS = 256;
 constexpr int S_COL = 0, O_COL = 128;  // S: two buffers of 64 columns at 0 and 64; O: 128 columns
 constexpr float RESCALE_THRESHOLD = 8.0f;  // log2 units
-constexpr int OST_ROW_BYTES = 144;         // epilogue staging (in the dead Q buffer): 64 fp16 per row + 16 B pad
 
 __device__ __forceinline__ float ex2_approx(float x) {  // 2^x, one MUFU op; 2^-inf = 0
     float y;
     asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
     return y;
+}
+
+// ---- pieces shared by the two kernels (one thread = one query row of the tile) ------------------------------------
+// Visible keys of query row `i` of tile `t`: segment 0 keys [0, lim0), segment 1 keys [lo1, hi1].
+struct RowKeys {
+    int lim0, lo1, hi1;
+};
+__device__ __forceinline__ RowKeys row_keys(const AttnTile& t, int i) {
+    RowKeys r;
+    r.lim0 = t.mode == kAttnPrefixCausal ? min(t.seg0_len, t.q_seq0 + i + 1) : t.seg0_len;
+    r.lo1 = 0;
+    r.hi1 = -1;
+    if (t.mode == kAttnSuffix) {
+        const int qa = (t.q_row - t.seg1_row) + i, L = t.q_seq0;
+        r.lo1 = (qa / L) * L;
+        r.hi1 = min(qa, t.seg1_len - 1);           // own option, positions <= own
+    }
+    return r;
+}
+
+// One key tile of the online softmax, from "S is complete" to "P is published":
+//   s_addr / o_addr  this warp's lanes of the S buffer / of O in TMEM
+//   kbase, lo, hi    first key of the tile and this row's visible range, all in the key segment's own numbering
+//   m_run, l_run     running reference max (RAW score units; p = exp2(s * c - m_run * c), c = scale * log2 e) and sum
+//   p_row            this row's 128 bytes of the P tile (= the dead K tile), `i` = the row (128B swizzle by i & 7)
+//   prev_pv          barrier of the previous tile's P V (nullptr for an item's first tile) and its parity: O may be
+//                    rescaled only once that has retired
+__device__ __forceinline__ void softmax_key_tile(uint32_t s_addr, uint32_t o_addr, int kbase, int lo, int hi,
+                                                 float scale_log2e, float thr, float& m_run, float& l_run, uint8_t* p_row,
+                                                 int i, uint64_t* prev_pv, uint32_t prev_parity, uint64_t* p_ready,
+                                                 int lane) {
+    uint32_t sr[2][32];
+    ptx::tmem_ld_32x32(s_addr, sr[0]);
+    ptx::tmem_ld_32x32(s_addr + 32, sr[1]);
+    ptx::tmem_ld_wait();
+    // masking only where a row of this warp has an invisible key in the tile (warp-uniform branch)
+    if (__any_sync(0xffffffffu, kbase < lo || kbase + BKV - 1 > hi)) {
+#pragma unroll
+        for (int c = 0; c < 64; ++c) {
+            const int key = kbase + c;
+            if (key < lo || key > hi) sr[c >> 5][c & 31] = 0xff800000u;  // -inf
+        }
+    }
+    float mx4[4] = {-INFINITY, -INFINITY, -INFINITY, -INFINITY};   // four short chains instead of one long one
+#pragma unroll
+    for (int c = 0; c < 64; ++c) mx4[c & 3] = fmaxf(mx4[c & 3], __uint_as_float(sr[c >> 5][c & 31]));
+    const float mx = fmaxf(fmaxf(mx4[0], mx4[1]), fmaxf(mx4[2], mx4[3]));
+    // lazy rescale: keep the old reference max unless the new one is much larger
+    float m_new = m_run;
+    if (mx > m_run + thr) m_new = mx;
+    const bool changed = m_new != m_run;
+    const float m_use = m_new == -INFINITY ? 0.f : m_new;
+    const float alpha = changed ? ex2_approx((m_run - m_use) * scale_log2e) : 1.f;   // m_run = -inf -> 0
+    m_run = m_new;
+    const float mc = m_use * scale_log2e;
+    float sum = 0.f;
+    uint32_t pk[32];
+#pragma unroll
+    for (int c = 0; c < 64; c += 2) {
+        const float p0 = ex2_approx(fmaf(__uint_as_float(sr[c >> 5][c & 31]), scale_log2e, -mc));
+        const float p1 = ex2_approx(fmaf(__uint_as_float(sr[(c + 1) >> 5][(c + 1) & 31]), scale_log2e, -mc));
+        sum += p0 + p1;
+        const __half2 h = __floats2half2_rn(p0, p1);
+        pk[c >> 1] = *reinterpret_cast<const uint32_t*>(&h);
+    }
+    l_run = l_run * alpha + sum;
+    // P -> shared memory over the (dead) K tile: [128 rows][64 keys] fp16, 128B swizzle.  Issued before the wait below
+    // so that the stores complete under it; the fence that publishes them comes after.
+#pragma unroll
+    for (int c = 0; c < 8; ++c)
+        *reinterpret_cast<uint4*>(p_row + ((c ^ (i & 7)) << 4)) =
+            make_uint4(pk[c * 4], pk[c * 4 + 1], pk[c * 4 + 2], pk[c * 4 + 3]);
+    if (prev_pv) {
+        // O is touched by the tensor core until P V of the previous tile has retired
+        ptx::mbar_wait(prev_pv, prev_parity);
+        ptx::tc_fence_after_sync();
+        // rescale this row of O (TMEM) if any row of the warp moved its reference max
+        if (__any_sync(0xffffffffu, changed)) {
+#pragma unroll 1
+            for (int c = 0; c < D / 32; ++c) {
+                uint32_t o[32];
+                ptx::tmem_ld_32x32(o_addr + c * 32, o);
+                ptx::tmem_ld_wait();
+#pragma unroll
+                for (int e = 0; e < 32; ++e) o[e] = __float_as_uint(__uint_as_float(o[e]) * alpha);
+                ptx::tmem_st_32x32(o_addr + c * 32, o);
+            }
+            ptx::tmem_st_wait();
+        }
+    }
+    ptx::fence_proxy_async_smem();   // generic-proxy writes -> visible to the tensor core's async proxy
+    ptx::tc_fence_before_sync();
+    __syncwarp();
+    if (lane == 0) ptx::mbar_arrive(p_ready);
+}
+
+// O / l -> fp16 -> global for this warp's 32 query rows, 64 columns at a time, staged in `stage` (4 KiB on a 1 KiB
+// boundary; 16-byte pieces XOR-swizzled by row = the TMA 128B swizzle).  A warp whose 32 rows all belong to the tile
+// hands the staged piece to one TMA store when it has a tensor map of the output (`tmap_o`, box 64 columns x 32 rows);
+// otherwise it copies the valid rows out itself as full 128-byte lines, 4 rows per store instruction.
+__device__ __forceinline__ void write_out(uint32_t o_addr, float inv, uint8_t* stage, int rows_here, __half* out_rows,
+                                          int ld_out, int lane, const CUtensorMap* tmap_o, int o_col, int o_row) {
+    const bool by_tma = tmap_o != nullptr && rows_here == 32;
+#pragma unroll 1
+    for (int hcol = 0; hcol < D; hcol += 64) {
+#pragma unroll
+        for (int c = 0; c < 2; ++c) {
+            uint32_t o[32];
+            ptx::tmem_ld_32x32(o_addr + hcol + c * 32, o);
+            ptx::tmem_ld_wait();
+#pragma unroll
+            for (int v = 0; v < 4; ++v) {
+                uint32_t wv[4];
+#pragma unroll
+                for (int e = 0; e < 4; ++e) {
+                    const __half2 h = __floats2half2_rn(__uint_as_float(o[v * 8 + e * 2]) * inv,
+                                                        __uint_as_float(o[v * 8 + e * 2 + 1]) * inv);
+                    wv[e] = *reinterpret_cast<const uint32_t*>(&h);
+                }
+                *reinterpret_cast<uint4*>(stage + lane * 128 + (((c * 4 + v) ^ (lane & 7)) << 4)) =
+                    make_uint4(wv[0], wv[1], wv[2], wv[3]);
+            }
+        }
+        if (by_tma) {
+            ptx::fence_proxy_async_smem();
+            __syncwarp();
+            if (lane == 0) {
+                ptx::tma_store_2d(tmap_o, stage, o_col + hcol, o_row);
+                ptx::bulk_commit_group();
+                ptx::bulk_wait_group_read<0>();      // the piece is written again by the next half / by its next owner
+            }
+            __syncwarp();
+        } else {
+            __syncwarp();
+#pragma unroll
+            for (int rr = 0; rr < 32; rr += 4) {
+                const int r = rr + (lane >> 3);                     // row inside this warp's 32
+                if (r < rows_here) {
+                    const uint4 v4 = *reinterpret_cast<const uint4*>(stage + r * 128 + (((lane & 7) ^ (r & 7)) << 4));
+                    *reinterpret_cast<uint4*>(out_rows + static_cast<size_t>(r) * ld_out + hcol + (lane & 7) * 8) = v4;
+                }
+            }
+            __syncwarp();
+        }
+    }
 }
 
 template <int NK>
@@ -221,129 +365,23 @@ attention_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_q, const __gri
         const int quarter = warp_idx & 3;             // TMEM lanes [32*quarter, +32) belong to this warp
         const int i = quarter * 32 + lane;            // query row inside the tile
         const uint32_t lane_addr = tmem_base + (static_cast<uint32_t>(quarter * 32) << 16);
-        // visible key ranges of this row, per segment
-        const int lim0 = t.mode == kAttnPrefixCausal ? min(t.seg0_len, t.q_seq0 + i + 1) : t.seg0_len;
-        int lo1 = 0, hi1 = -1;
-        if (t.mode == kAttnSuffix) {
-            const int qa = (t.q_row - t.seg1_row) + i, L = t.q_seq0;
-            lo1 = (qa / L) * L;
-            hi1 = min(qa, t.seg1_len - 1);           // own option, positions <= own
-        }
-        // running reference max m_run is kept in RAW score units; p = exp2(s * c - m_run * c), c = scale * log2(e)
+        const RowKeys rk = row_keys(t, i);
         float m_run = -INFINITY, l_run = 0.f;
         const float thr = RESCALE_THRESHOLD / scale_log2e;
         for (int j = 0; j < n_tiles; ++j) {
-            const int ks = j % NK;
             ptx::mbar_wait(&s_full[j & 1], (j >> 1) & 1);
             ptx::tc_fence_after_sync();
-            uint32_t sr[2][32];
-            ptx::tmem_ld_32x32(lane_addr + S_COL + (j & 1) * BKV, sr[0]);
-            ptx::tmem_ld_32x32(lane_addr + S_COL + (j & 1) * BKV + 32, sr[1]);
-            ptx::tmem_ld_wait();
             const bool in0 = j < n0;
-            const int kbase = in0 ? j * BKV : (j - n0) * BKV;
-            const int lo = in0 ? 0 : lo1, hi = in0 ? lim0 - 1 : hi1;
-            // masking only where a row of this warp has an invisible key in the tile (warp-uniform branch)
-            if (__any_sync(0xffffffffu, kbase < lo || kbase + BKV - 1 > hi)) {
-#pragma unroll
-                for (int c = 0; c < 64; ++c) {
-                    const int key = kbase + c;
-                    if (key < lo || key > hi) sr[c >> 5][c & 31] = 0xff800000u;  // -inf
-                }
-            }
-            float mx4[4] = {-INFINITY, -INFINITY, -INFINITY, -INFINITY};   // four short chains instead of one long one
-#pragma unroll
-            for (int c = 0; c < 64; ++c) mx4[c & 3] = fmaxf(mx4[c & 3], __uint_as_float(sr[c >> 5][c & 31]));
-            const float mx = fmaxf(fmaxf(mx4[0], mx4[1]), fmaxf(mx4[2], mx4[3]));
-            // lazy rescale: keep the old reference max unless the new one is much larger
-            float m_new = m_run;
-            if (mx > m_run + thr) m_new = mx;
-            const bool changed = m_new != m_run;
-            const float m_use = m_new == -INFINITY ? 0.f : m_new;
-            const float alpha = changed ? ex2_approx((m_run - m_use) * scale_log2e) : 1.f;   // m_run = -inf -> 0
-            m_run = m_new;
-            const float mc = m_use * scale_log2e;
-            float sum = 0.f;
-            uint32_t pk[32];
-#pragma unroll
-            for (int c = 0; c < 64; c += 2) {
-                const float p0 = ex2_approx(fmaf(__uint_as_float(sr[c >> 5][c & 31]), scale_log2e, -mc));
-                const float p1 = ex2_approx(fmaf(__uint_as_float(sr[(c + 1) >> 5][(c + 1) & 31]), scale_log2e, -mc));
-                sum += p0 + p1;
-                const __half2 h = __floats2half2_rn(p0, p1);
-                pk[c >> 1] = *reinterpret_cast<const uint32_t*>(&h);
-            }
-            l_run = l_run * alpha + sum;
-            // P -> shared memory over the (dead) K tile: [128 rows][64 keys] fp16, 128B swizzle.  Issued before the wait
-            // below so that the stores complete under it; the fence that publishes them comes after.
-            uint8_t* sp = sK + ks * TILE_BYTES + i * 128;
-#pragma unroll
-            for (int c = 0; c < 8; ++c)
-                *reinterpret_cast<uint4*>(sp + ((c ^ (i & 7)) << 4)) =
-                    make_uint4(pk[c * 4], pk[c * 4 + 1], pk[c * 4 + 2], pk[c * 4 + 3]);
-            if (j > 0) {
-                // O is touched by the tensor core until P V of the previous tile has retired
-                ptx::mbar_wait(pv_done, (j - 1) & 1);
-                ptx::tc_fence_after_sync();
-                // rescale this row of O (TMEM) if any row of the warp moved its reference max
-                if (__any_sync(0xffffffffu, changed)) {
-#pragma unroll 1
-                    for (int c = 0; c < D / 32; ++c) {
-                        uint32_t o[32];
-                        ptx::tmem_ld_32x32(lane_addr + O_COL + c * 32, o);
-                        ptx::tmem_ld_wait();
-#pragma unroll
-                        for (int e = 0; e < 32; ++e) o[e] = __float_as_uint(__uint_as_float(o[e]) * alpha);
-                        ptx::tmem_st_32x32(lane_addr + O_COL + c * 32, o);
-                    }
-                    ptx::tmem_st_wait();
-                }
-            }
-            ptx::fence_proxy_async_smem();   // generic-proxy writes -> visible to the tensor core's async proxy
-            ptx::tc_fence_before_sync();
-            __syncwarp();
-            if (lane == 0) ptx::mbar_arrive(p_ready);
+            softmax_key_tile(lane_addr + S_COL + (j & 1) * BKV, lane_addr + O_COL, in0 ? j * BKV : (j - n0) * BKV,
+                             in0 ? 0 : rk.lo1, in0 ? rk.lim0 - 1 : rk.hi1, scale_log2e, thr, m_run, l_run,
+                             sK + (j % NK) * TILE_BYTES + i * 128, i, j > 0 ? pv_done : nullptr, (j - 1) & 1, p_ready, lane);
         }
-        // ---- epilogue: O / l -> fp16 -> global
+        // ---- write-out.  Every Q K^T has retired by now, so the Q buffer is free: each warp stages its rows there.
         if (n_tiles > 0) ptx::mbar_wait(pv_done, (n_tiles - 1) & 1);
         ptx::tc_fence_after_sync();
         const float inv = l_run > 0.f ? 1.f / l_run : 0.f;
-        // Every Q K^T has retired by now, so the Q buffer is free: each warp stages its own 32 rows there
-        // (64 columns at a time) and writes them out as full 128-byte lines, 4 rows per store instruction.
-        uint8_t* my_row = sQ + i * OST_ROW_BYTES;
-        const int rows_here = min(32, t.n_q - quarter * 32);      // valid rows of this warp (may be <= 0)
-#pragma unroll 1
-        for (int hcol = 0; hcol < D; hcol += 64) {
-#pragma unroll
-            for (int c = 0; c < 2; ++c) {
-                uint32_t o[32];
-                ptx::tmem_ld_32x32(lane_addr + O_COL + hcol + c * 32, o);
-                ptx::tmem_ld_wait();
-#pragma unroll
-                for (int v = 0; v < 4; ++v) {
-                    uint32_t wv[4];
-#pragma unroll
-                    for (int e = 0; e < 4; ++e) {
-                        const __half2 h = __floats2half2_rn(__uint_as_float(o[v * 8 + e * 2]) * inv,
-                                                            __uint_as_float(o[v * 8 + e * 2 + 1]) * inv);
-                        wv[e] = *reinterpret_cast<const uint32_t*>(&h);
-                    }
-                    *reinterpret_cast<uint4*>(my_row + c * 64 + v * 16) = make_uint4(wv[0], wv[1], wv[2], wv[3]);
-                }
-            }
-            __syncwarp();
-#pragma unroll
-            for (int rr = 0; rr < 32; rr += 4) {
-                const int r = rr + (lane >> 3);                     // row inside this warp's 32
-                if (r < rows_here) {
-                    const uint4 v4 = *reinterpret_cast<const uint4*>(sQ + (quarter * 32 + r) * OST_ROW_BYTES +
-                                                                     (lane & 7) * 16);
-                    *reinterpret_cast<uint4*>(out + static_cast<size_t>(t.q_row + quarter * 32 + r) * ld_out +
-                                              head * D + hcol + (lane & 7) * 8) = v4;
-                }
-            }
-            __syncwarp();
-        }
+        write_out(lane_addr + O_COL, inv, sQ + quarter * 4096, min(32, t.n_q - quarter * 32),
+                  out + static_cast<size_t>(t.q_row + quarter * 32) * ld_out + head * D, ld_out, lane, nullptr, 0, 0);
     }
 
     ptx::tc_fence_before_sync();
@@ -584,137 +622,29 @@ attention_persistent_kernel(const __grid_constant__ CUtensorMap tmap_q, const __
                             make_uint4(0, 0, 0, 0);
                 continue;
             }
-            const int lim0 = t.mode == kAttnPrefixCausal ? min(t.seg0_len, t.q_seq0 + i + 1) : t.seg0_len;
-            int lo1 = 0, hi1 = -1;
-            if (t.mode == kAttnSuffix) {
-                const int qa = (t.q_row - t.seg1_row) + i, L = t.q_seq0;
-                lo1 = (qa / L) * L;
-                hi1 = min(qa, t.seg1_len - 1);
-            }
+            const RowKeys rk = row_keys(t, i);
             float m_run = -INFINITY, l_run = 0.f;
             const float thr = RESCALE_THRESHOLD / scale_log2e;
             for (int j = 0; j < n_tiles; ++j) {
                 const uint32_t g = gt + j;
-                const int ks = g % NK;
                 ptx::mbar_wait(&s_full[g & 1], (g >> 1) & 1);
                 ptx::tc_fence_after_sync();
-                uint32_t sr[2][32];
-                ptx::tmem_ld_32x32(lane_addr + S_COL + (g & 1) * BKV, sr[0]);
-                ptx::tmem_ld_32x32(lane_addr + S_COL + (g & 1) * BKV + 32, sr[1]);
-                ptx::tmem_ld_wait();
                 const bool in0 = j < n0;
-                const int kbase = in0 ? j * BKV : (j - n0) * BKV;
-                const int lo = in0 ? 0 : lo1, hi = in0 ? lim0 - 1 : hi1;
-                if (__any_sync(0xffffffffu, kbase < lo || kbase + BKV - 1 > hi)) {
-#pragma unroll
-                    for (int c = 0; c < 64; ++c) {
-                        const int key = kbase + c;
-                        if (key < lo || key > hi) sr[c >> 5][c & 31] = 0xff800000u;  // -inf
-                    }
-                }
-                float mx4[4] = {-INFINITY, -INFINITY, -INFINITY, -INFINITY};
-#pragma unroll
-                for (int c = 0; c < 64; ++c) mx4[c & 3] = fmaxf(mx4[c & 3], __uint_as_float(sr[c >> 5][c & 31]));
-                const float mx = fmaxf(fmaxf(mx4[0], mx4[1]), fmaxf(mx4[2], mx4[3]));
-                float m_new = m_run;
-                if (mx > m_run + thr) m_new = mx;
-                const bool changed = m_new != m_run;
-                const float m_use = m_new == -INFINITY ? 0.f : m_new;
-                const float alpha = changed ? ex2_approx((m_run - m_use) * scale_log2e) : 1.f;
-                m_run = m_new;
-                const float mc = m_use * scale_log2e;
-                float sum = 0.f;
-                uint32_t pk[32];
-#pragma unroll
-                for (int c = 0; c < 64; c += 2) {
-                    const float p0 = ex2_approx(fmaf(__uint_as_float(sr[c >> 5][c & 31]), scale_log2e, -mc));
-                    const float p1 = ex2_approx(fmaf(__uint_as_float(sr[(c + 1) >> 5][(c + 1) & 31]), scale_log2e, -mc));
-                    sum += p0 + p1;
-                    const __half2 h = __floats2half2_rn(p0, p1);
-                    pk[c >> 1] = *reinterpret_cast<const uint32_t*>(&h);
-                }
-                l_run = l_run * alpha + sum;
-                uint8_t* sp = sK + ks * TILE_BYTES + i * 128;
-#pragma unroll
-                for (int c = 0; c < 8; ++c)
-                    *reinterpret_cast<uint4*>(sp + ((c ^ (i & 7)) << 4)) =
-                        make_uint4(pk[c * 4], pk[c * 4 + 1], pk[c * 4 + 2], pk[c * 4 + 3]);
-                if (j > 0) {
-                    ptx::mbar_wait(pv_done, (g - 1) & 1);
-                    ptx::tc_fence_after_sync();
-                    if (__any_sync(0xffffffffu, changed)) {
-#pragma unroll 1
-                        for (int c = 0; c < D / 32; ++c) {
-                            uint32_t o[32];
-                            ptx::tmem_ld_32x32(lane_addr + O_COL + c * 32, o);
-                            ptx::tmem_ld_wait();
-#pragma unroll
-                            for (int e = 0; e < 32; ++e) o[e] = __float_as_uint(__uint_as_float(o[e]) * alpha);
-                            ptx::tmem_st_32x32(lane_addr + O_COL + c * 32, o);
-                        }
-                        ptx::tmem_st_wait();
-                    }
-                }
-                ptx::fence_proxy_async_smem();
-                ptx::tc_fence_before_sync();
-                __syncwarp();
-                if (lane == 0) ptx::mbar_arrive(p_ready);
+                softmax_key_tile(lane_addr + S_COL + (g & 1) * BKV, lane_addr + O_COL, in0 ? j * BKV : (j - n0) * BKV,
+                                 in0 ? 0 : rk.lo1, in0 ? rk.lim0 - 1 : rk.hi1, scale_log2e, thr, m_run, l_run,
+                                 sK + (g % NK) * TILE_BYTES + i * 128, i, j > 0 ? pv_done : nullptr, (g - 1) & 1, p_ready,
+                                 lane);
             }
-            // ---- write-out: O / l -> fp16 -> global, staged (64 columns at a time, 16-byte pieces XOR-swizzled by row)
-            // in this warp's quarter of the K/P buffer of the item's last key tile, whose P V has retired by then
+            // ---- write-out, staged in this warp's quarter of the K/P buffer of the item's last key tile, whose P V has
+            // retired by then
             const uint32_t g_last = gt + n_tiles - 1;
             gt += n_tiles;
             ptx::mbar_wait(pv_done, g_last & 1);
             ptx::tc_fence_after_sync();
             const float inv = l_run > 0.f ? 1.f / l_run : 0.f;
-            uint8_t* stage = sK + (g_last % NK) * TILE_BYTES + quarter * 4096;
-            // A warp whose 32 rows all belong to the tile hands its staged [32 x 64] piece to one TMA store (the staging
-            // layout IS the 128B swizzle); a warp with fewer valid rows copies them out itself, row by row.
-            const bool whole = rows_here == 32;
-#pragma unroll 1
-            for (int hcol = 0; hcol < D; hcol += 64) {
-#pragma unroll
-                for (int c = 0; c < 2; ++c) {
-                    uint32_t o[32];
-                    ptx::tmem_ld_32x32(lane_addr + O_COL + hcol + c * 32, o);
-                    ptx::tmem_ld_wait();
-#pragma unroll
-                    for (int v = 0; v < 4; ++v) {
-                        uint32_t wv[4];
-#pragma unroll
-                        for (int e = 0; e < 4; ++e) {
-                            const __half2 h = __floats2half2_rn(__uint_as_float(o[v * 8 + e * 2]) * inv,
-                                                                __uint_as_float(o[v * 8 + e * 2 + 1]) * inv);
-                            wv[e] = *reinterpret_cast<const uint32_t*>(&h);
-                        }
-                        *reinterpret_cast<uint4*>(stage + lane * 128 + (((c * 4 + v) ^ (lane & 7)) << 4)) =
-                            make_uint4(wv[0], wv[1], wv[2], wv[3]);
-                    }
-                }
-                if (whole) {
-                    ptx::fence_proxy_async_smem();
-                    __syncwarp();
-                    if (lane == 0) {
-                        ptx::tma_store_2d(&tmap_o, stage, head * D + hcol, t.q_row + quarter * 32);
-                        ptx::bulk_commit_group();
-                        ptx::bulk_wait_group_read<0>();      // the piece is re-used by the next half / handed back below
-                    }
-                    __syncwarp();
-                } else {
-                    __syncwarp();
-#pragma unroll
-                    for (int rr = 0; rr < 32; rr += 4) {
-                        const int r = rr + (lane >> 3);
-                        if (r < rows_here) {
-                            const uint4 v4 =
-                                *reinterpret_cast<const uint4*>(stage + r * 128 + (((lane & 7) ^ (r & 7)) << 4));
-                            *reinterpret_cast<uint4*>(out + static_cast<size_t>(t.q_row + quarter * 32 + r) * ld_out +
-                                                      head * D + hcol + (lane & 7) * 8) = v4;
-                        }
-                    }
-                    __syncwarp();
-                }
-            }
+            write_out(lane_addr + O_COL, inv, sK + (g_last % NK) * TILE_BYTES + quarter * 4096, rows_here,
+                      out + static_cast<size_t>(t.q_row + quarter * 32) * ld_out + head * D, ld_out, lane, &tmap_o,
+                      head * D, t.q_row + quarter * 32);
             // O has been read (the next item's first P V may overwrite it once p_ready says so) and so has the staging
             // buffer: the fourth warp to get here returns it to the producer
             ptx::tc_fence_before_sync();
