@@ -425,3 +425,13 @@ def test_length_bucketed_packing_limits_and_refusals():
     assert planner.pack_prompts(tok, max_rows=4096, max_head_rows=64, cached_prefix=True, bucketed=True).order is None
     # one prompt, and no prompts
     assert planner.pack_prompts(tok[:1], max_rows=4096, max_head_rows=64, bucketed=True).order is None
+
+
+def test_every_tuning_option_is_documented_in_the_public_header():
+    """`fls_set_option` names accepted by csrc/api.cu all appear, quoted, in include/fls_b200.h."""
+    with open(os.path.join(ROOT, "flexible-llm-sharding_b200", "csrc", "api.cu")) as f:
+        accepted = set(re.findall(r'strcmp\(name, "([a-z_]+)"\)', f.read()))
+    with open(os.path.join(ROOT, "include", "fls_b200.h")) as f:
+        header = f.read()
+    assert len(accepted) >= 10
+    assert not [o for o in sorted(accepted) if f'"{o}"' not in header]
