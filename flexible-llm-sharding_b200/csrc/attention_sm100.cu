@@ -500,6 +500,14 @@ attention_persistent_kernel(const __grid_constant__ CUtensorMap tmap_q, const __
                 if (have) {
                     w.t = tiles[it % static_cast<uint32_t>(n_tile_desc)];     // tile fastest, as the grid form launches
                     w.head = static_cast<int32_t>(it / static_cast<uint32_t>(n_tile_desc));
+                    // A tile that sees no key at all (the planner never makes one) is not handed on: the other warps
+                    // synchronise with each other through an item's key tiles, and it has none.  Its rows stay unwritten.
+                    int e0, e1;
+                    tiles_of(w.t, e0, e1);
+                    if (e0 + e1 == 0) {
+                        --m;
+                        continue;
+                    }
                 }
                 // the slot (and the Q buffer) of two items / one item ago are free once the last Q K^T of item m-1
                 // has retired

@@ -67,7 +67,9 @@ typedef struct fls_model_desc {
  *   mode 1  prefix queries, causal: key t visible iff t <= q_seq0 + i (q_seq0 = index of the first query)
  *   mode 2  option queries: the tile covers rows of whole options of length q_seq0 (= len_s) that
  *           start at seg1_row; a query sees all prefix keys and the keys of its own option at
- *           positions <= its own (== the mask slice of utils.py:276 with position offset len_p). */
+ *           positions <= its own (== the mask slice of utils.py:276 with position offset len_p).
+ * Every tile must see at least one key (seg0_len + seg1_len > 0; the host scheduler never builds another kind): the
+ * output rows of a tile without keys are not defined. */
 #define FLS_ATTN_PREFIX 0
 #define FLS_ATTN_PREFIX_CAUSAL 1
 #define FLS_ATTN_SUFFIX 2
