@@ -262,6 +262,17 @@ def balanced_bins(tok: list[TokenizedPrompt], max_rows: int, max_head_rows: int)
     return bins
 
 
+def _in_order_count(tok: list[TokenizedPrompt], max_rows: int, max_head_rows: int) -> int:
+    """Micro-batches that filling them in the caller's order would make (each takes what fits)."""
+    n, rows, heads = 0, max_rows + 1, 0
+    for t in tok:
+        if rows + t.rows > max_rows or heads + t.n_options > max_head_rows:
+            n, rows, heads = n + 1, 0, 0
+        rows += t.rows
+        heads += t.n_options
+    return n
+
+
 def pack_prompts(tok: list[TokenizedPrompt], max_rows: int, max_head_rows: int,
                  prefix_causal: bool = False, cached_prefix: bool = False, bucketed: bool = False) -> PackedPrompts:
     """Packs the prompts' token rows and cuts them into micro-batches of <= max_rows rows.
@@ -277,14 +288,17 @@ def pack_prompts(tok: list[TokenizedPrompt], max_rows: int, max_head_rows: int,
             if t.rows > max_rows:
                 raise ValueError(f"prompt {i} has {t.rows} token rows; raise max_rows (currently {max_rows})")
         bins = balanced_bins(tok, max_rows, max_head_rows)
-        flat = [i for b in bins for i in b]
-        if flat != list(range(len(tok))):
-            order = np.asarray(flat, dtype=np.int64)
-            tok = [tok[i] for i in flat]
-        ranges, k = [], 0
-        for b in bins:
-            ranges.append((k, k + len(b)))
-            k += len(b)
+        if len(bins) <= _in_order_count(tok, max_rows, max_head_rows):
+            flat = [i for b in bins for i in b]
+            if flat != list(range(len(tok))):
+                order = np.asarray(flat, dtype=np.int64)
+                tok = [tok[i] for i in flat]
+            ranges, k = [], 0
+            for b in bins:
+                ranges.append((k, k + len(b)))
+                k += len(b)
+        # else: longest-first into the emptiest micro-batch is a heuristic; the rare prompt mix it packs into MORE
+        # micro-batches than filling them in order does is packed in order
     n = len(tok)
     prompt_row = np.zeros(n + 1, dtype=np.int64)
     head_row = np.zeros(n + 1, dtype=np.int64)

@@ -435,3 +435,25 @@ def test_every_tuning_option_is_documented_in_the_public_header():
         header = f.read()
     assert len(accepted) >= 10
     assert not [o for o in sorted(accepted) if f'"{o}"' not in header]
+
+
+def test_length_bucketed_packing_never_makes_more_micro_batches_than_in_order():
+    """Longest-first into the emptiest micro-batch is a heuristic: rows 5,5,4,3,3 under a cap of 10 would take three
+    micro-batches where the given order takes two.  Such a mix is packed in order."""
+    tok = _tok([(1, 1, 4), (1, 1, 4), (1, 1, 3), (1, 1, 2), (1, 1, 2)])          # rows 5, 5, 4, 3, 3
+    assert [t.rows for t in tok] == [5, 5, 4, 3, 3]
+    assert len(planner.balanced_bins(tok, 10, 64)) == 3
+    buck = planner.pack_prompts(tok, max_rows=10, max_head_rows=64, bucketed=True)
+    assert buck.order is None and [mb.n_rows for mb in buck.micro_batches] == [10, 10]
+    rng = np.random.default_rng(11)
+    for _ in range(300):
+        shapes = [(int(rng.integers(1, 40)), int(rng.integers(1, 4)), int(rng.integers(1, 12))) for _ in range(int(rng.integers(2, 30)))]
+        tok = _tok(shapes, 3)
+        cap = max(t.rows for t in tok) + int(rng.integers(0, 120))
+        heads = int(rng.integers(3, 20))
+        plain = planner.pack_prompts(tok, max_rows=cap, max_head_rows=heads)
+        buck = planner.pack_prompts(tok, max_rows=cap, max_head_rows=heads, bucketed=True)
+        assert len(buck.micro_batches) <= len(plain.micro_batches)
+        assert planner._in_order_count(tok, cap, heads) == len(plain.micro_batches)
+        assert all(mb.n_rows <= cap and mb.n_head <= heads for mb in buck.micro_batches)
+        assert sorted(buck.prompt_index(p) for p in range(len(tok))) == list(range(len(tok)))
